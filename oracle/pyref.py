@@ -1,0 +1,179 @@
+"""oracle/pyref.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+ctypes bindings for the two CPU checkers:
+  * oracle/_ref/libref_cl.so  -- the reference's own .cl text compiled as C++ (kind "reference")
+  * oracle/librt_oracle.so    -- the plain-C restatement in oracle/rt_oracle.c (kind "port")
+plus small scene/camera/texture helpers shared by tests/ and bench.py's cpu_baseline leg.
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this.
+"""
+import ctypes as C
+import os
+import struct
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF_SO = os.path.join(HERE, "_ref", "libref_cl.so")
+PORT_SO = os.path.join(HERE, "librt_oracle.so")
+
+u8p = C.POINTER(C.c_uint8)
+u32p = C.POINTER(C.c_uint32)
+u64p = C.POINTER(C.c_uint64)
+f32p = C.POINTER(C.c_float)
+
+_RENDER_ARGS = [C.c_int, f32p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
+                C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, u8p, C.c_int, C.c_int, C.c_int, u8p, C.c_int,
+                C.c_int, u32p, u32p, C.c_int]
+
+
+def _ptr(a, t):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+class Scene:
+    """Wire-format scene: raw rsphere[96 B] / rplane[96 B] / rlight[48 B] arrays + RGBA8 texture arrays."""
+
+    def __init__(self, spheres, planes, lights, tex, sky):
+        self.spheres = np.ascontiguousarray(np.frombuffer(spheres, np.uint8)) if len(spheres) else np.zeros(0, np.uint8)
+        self.planes = np.ascontiguousarray(np.frombuffer(planes, np.uint8)) if len(planes) else np.zeros(0, np.uint8)
+        self.lights = np.ascontiguousarray(np.frombuffer(lights, np.uint8)) if len(lights) else np.zeros(0, np.uint8)
+        self.S, self.P, self.L = len(spheres) // 96, len(planes) // 96, len(lights) // 48
+        self.tex = np.ascontiguousarray(tex, np.uint8)  # (layers, h, w, 4)
+        self.sky = np.ascontiguousarray(sky, np.uint8)  # (1, h, w, 4)
+        assert self.tex.ndim == 4 and self.sky.ndim == 4 and self.sky.shape[0] == 1
+
+
+def load_map(path):
+    """Parse the reference's .map archive (src/cpu_obj.c:76-101): count byte + raw struct array, x3."""
+    d = open(path, "rb").read()
+    o = 0
+    out = []
+    for sz in (96, 96, 48):
+        n = d[o]
+        o += 1
+        out.append(d[o:o + n * sz])
+        o += n * sz
+    assert o == len(d)
+    return out
+
+
+def load_png_layers(paths):
+    """What cl_wrap_load_images builds (src/opencl_wrap.c:189-349): RGB8 -> RGBA8 (A=255), layers stacked."""
+    from PIL import Image
+    ims = []
+    for p in paths:
+        im = Image.open(p)
+        assert im.mode == "RGB", p
+        a = np.asarray(im)
+        ims.append(np.concatenate([a, np.full(a.shape[:2] + (1,), 255, np.uint8)], axis=2))
+    return np.stack(ims)
+
+
+def default_textures(root=ROOT):
+    tex = load_png_layers([os.path.join(root, "assets", n + ".png") for n in ("cobblestone", "sand", "check", "grass")])
+    sky = load_png_layers([os.path.join(root, "assets", "bg", "stormydays.png")])
+    return tex, sky
+
+
+def render_map_scene(root=ROOT):
+    s, p, l = load_map(os.path.join(root, "scenes", "render.map"))
+    tex, sky = default_textures(root)
+    return Scene(s, p, l, tex, sky)
+
+
+class _Lib:
+    def __init__(self, path, prefix):
+        if not os.path.exists(path):
+            raise FileNotFoundError(path + " missing: run `make -C oracle` (or __graft_entry__.build())")
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        self.render_fn = getattr(self.lib, prefix + "_render")
+        self.render_fn.argtypes = _RENDER_ARGS
+        self.render_fn.restype = C.c_int
+
+    def render(self, scene, cam, W, H, y0=0, y1=None, wide=False, threads=0, want_hit=True):
+        """Returns (rgb uint32[H*W], hit uint32[H*W] or None); only rows [y0,y1) are written."""
+        y1 = H if y1 is None else y1
+        cam = np.ascontiguousarray(cam, np.float32)
+        assert cam.size == 14
+        out = np.zeros(W * H, np.uint32)
+        hit = np.zeros(W * H, np.uint32) if want_hit else None
+        if threads <= 0:
+            threads = os.cpu_count() or 1
+        rc = self.render_fn(int(wide), _ptr(cam, f32p), W, H, y0, y1, scene.spheres.ctypes.data, scene.S,
+                            scene.planes.ctypes.data, scene.P, scene.lights.ctypes.data, scene.L,
+                            _ptr(scene.tex, u8p), scene.tex.shape[2], scene.tex.shape[1], scene.tex.shape[0],
+                            _ptr(scene.sky, u8p), scene.sky.shape[2], scene.sky.shape[1], _ptr(out, u32p),
+                            _ptr(hit, u32p), threads)
+        if rc != 0:
+            raise ValueError("%s_render rejected its arguments (rc=%d)" % (self.prefix, rc))
+        return out, hit
+
+
+_cache = {}
+
+
+def ref():
+    """The reference .cl text compiled as C++ (oracle/_ref)."""
+    if "ref" not in _cache:
+        _cache["ref"] = _Lib(REF_SO, "ref")
+    return _cache["ref"]
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+def camera(origin, look, fov, focal, W, H, normalize_look=True):
+    """float32 restatement of rinit_camera + rgen_perspective (src/cpu_ray.c:8-35,42-106).
+
+    Returns the 14 floats {corner, origin, up, right, w_factor, h_factor} the raygen kernel takes
+    (src/cl/raygen.cl:5-7).  Mixed float/double steps follow the C usual arithmetic conversions.
+    """
+    f = np.float32
+    o = [f(v) for v in origin]
+    d = [f(v) for v in look]
+    if normalize_look:  # cpu_ray.c:8-19: float number = 1/sqrt(double(float sum))
+        s = f(f(f(d[0] * d[0]) + f(d[1] * d[1])) + f(d[2] * d[2]))
+        num = f(1.0 / np.sqrt(np.float64(s)))
+        d = [f(v * num) for v in d]
+    fov, focal = f(fov), f(focal)
+    half = f(np.float64(f(fov / f(360.0))) * np.pi)          # :65
+    aspect = f(f(H) / f(W))                                    # :66
+    fov_tan = f(np.tan(np.float64(half)))                      # :67
+    iw = f(f(fov_tan * focal) * f(2))                          # :69
+    ih = f(aspect * iw)                                        # :70
+    wf, hf = f(iw / f(W)), f(ih / f(H))                        # :72-73
+    fw = [f(-v) for v in d]                                    # :76-79
+    top = [f(0), f(1), f(0)]
+
+    def cross(a, b):
+        return [f(f(a[1] * b[2]) - f(a[2] * b[1])), f(f(a[2] * b[0]) - f(a[0] * b[2])),
+                f(f(a[0] * b[1]) - f(a[1] * b[0]))]
+    right = cross(top, fw)                                     # :82-86
+    up = cross(fw, right)                                      # :87-91
+    center = [f(f(-v) * focal) for v in fw]                    # :94-98
+    corner = [f(f(center[i] - f(f(right[i] * iw) / f(2))) + f(f(up[i] * ih) / f(2))) for i in range(3)]  # :101-105
+    return np.array(corner + o + up + right + [wf, hf], np.float32)
+
+
+RAYPNG_CAMERA = dict(origin=(0.8, 2.5, -8.0), look=(0.2, 0.0, 1.0), fov=90.0, focal=1.0)  # raypng.c:17-21
+
+
+def unpack_rgb(buf, W, H):
+    """0x00RRGGBB words -> (H, W, 3) uint8 (src/cpu_ray.c:141-145)."""
+    b = np.asarray(buf, np.uint32).reshape(H, W)
+    return np.stack([(b >> 16) & 255, (b >> 8) & 255, b & 255], axis=2).astype(np.uint8)
+
+
+def compare_frames(a, b, W, H):
+    """Tolerance metrics of BASELINE.json: fraction of pixels within 1 LSB (all channels), PSNR in dB."""
+    A = unpack_rgb(a, W, H).astype(np.int32)
+    B = unpack_rgb(b, W, H).astype(np.int32)
+    d = np.abs(A - B)
+    within1 = float((d.max(axis=2) <= 1).mean())
+    exact = float((d.max(axis=2) == 0).mean())
+    mse = float((d.astype(np.float64) ** 2).mean())
+    psnr = float("inf") if mse == 0 else 10.0 * np.log10(255.0 ** 2 / mse)
+    return dict(within1=within1, exact=exact, psnr=psnr, max_abs=int(d.max()))
