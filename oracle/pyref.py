@@ -177,3 +177,46 @@ def compare_frames(a, b, W, H):
     mse = float((d.astype(np.float64) ** 2).mean())
     psnr = float("inf") if mse == 0 else 10.0 * np.log10(255.0 ** 2 / mse)
     return dict(within1=within1, exact=exact, psnr=psnr, max_abs=int(d.max()))
+
+
+class _Port(_Lib):
+    COUNTER_NAMES = ("segments", "shadow_rays", "sphere_tests", "sphere_dpos", "plane_tests", "texels")
+
+    def __init__(self):
+        super().__init__(PORT_SO, "rto")
+        self.counted_fn = self.lib.rto_render_counted
+        self.counted_fn.argtypes = _RENDER_ARGS + [u64p]
+        self.counted_fn.restype = C.c_int
+
+    def render_counted(self, scene, cam, W, H, y0=0, y1=None, wide=False, threads=0):
+        """Like render() but also returns the work counters as a dict (plus 'rays' and 'flop')."""
+        y1 = H if y1 is None else y1
+        cam = np.ascontiguousarray(cam, np.float32)
+        out = np.zeros(W * H, np.uint32)
+        hit = np.zeros(W * H, np.uint32)
+        cnt = np.zeros(8, np.uint64)
+        if threads <= 0:
+            threads = os.cpu_count() or 1
+        rc = self.counted_fn(int(wide), _ptr(cam, f32p), W, H, y0, y1, scene.spheres.ctypes.data, scene.S,
+                             scene.planes.ctypes.data, scene.P, scene.lights.ctypes.data, scene.L,
+                             _ptr(scene.tex, u8p), scene.tex.shape[2], scene.tex.shape[1], scene.tex.shape[0],
+                             _ptr(scene.sky, u8p), scene.sky.shape[2], scene.sky.shape[1], _ptr(out, u32p),
+                             _ptr(hit, u32p), threads, _ptr(cnt, u64p))
+        if rc != 0:
+            raise ValueError("rto_render_counted rejected its arguments")
+        c = {k: int(cnt[i]) for i, k in enumerate(self.COUNTER_NAMES)}
+        c["rays"] = c["segments"] + c["shadow_rays"]
+        c["flop"] = algorithmic_flop(c)
+        return out, hit, c
+
+
+def algorithmic_flop(c):
+    """21 flop per sphere test (+5 when D >= 0), 14 per plane test; nothing else counted."""
+    return 21 * c["sphere_tests"] + 5 * c["sphere_dpos"] + 14 * c["plane_tests"]
+
+
+def port():
+    """The plain-C restatement (oracle/rt_oracle.c)."""
+    if "port" not in _cache:
+        _cache["port"] = _Port()
+    return _cache["port"]
