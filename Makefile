@@ -1,0 +1,37 @@
+# Builds the product library in-tree (it travels to the GPU box with the snapshot):
+#   example-gui-opencl-raytracer_b200/librtb200.so   engine C ABI (include/rtb200.h) + cl_wrap_* drop-in (include/cuda_wrap.h)
+# The render kernels are compiled WITHOUT contraction (-fmad=false): parity contract, see rt_kernels.cu.
+PKG   := example-gui-opencl-raytracer_b200
+CSRC  := $(PKG)/csrc
+NVCC  ?= nvcc
+ARCH  := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xptxas -v
+KFLAGS  := -fmad=false -prec-div=true -prec-sqrt=true -ftz=false
+CFLAGS  := -O2 -std=gnu11 -fPIC -Wall -Wextra -ffp-contract=off -Iinclude -Iinclude/shim
+
+OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o
+
+all: $(PKG)/librtb200.so
+
+$(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h include/rtb200.h
+	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels.ptxas.log || (cat $(CSRC)/rt_kernels.ptxas.log; false)
+	@grep -E "registers|spill" $(CSRC)/rt_kernels.ptxas.log | sort | uniq -c | sort -rn | head -20
+
+$(CSRC)/rt_engine.o: $(CSRC)/rt_engine.cu $(CSRC)/rt_kernels.h include/rtb200.h
+	$(NVCC) $(ARCH) -O2 -lineinfo -std=c++17 -Xcompiler -fPIC -c $< -o $@
+
+$(CSRC)/cuda_wrap.o: $(CSRC)/cuda_wrap.c include/cuda_wrap.h include/rtb200.h $(CSRC)/png_io.h
+	gcc $(CFLAGS) -c $< -o $@
+
+$(CSRC)/png_io.o: $(CSRC)/png_io.c $(CSRC)/png_io.h
+	gcc $(CFLAGS) -c $< -o $@
+
+$(PKG)/librtb200.so: $(OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lz
+
+oracle:
+	$(MAKE) -C oracle
+
+clean:
+	rm -f $(OBJS) $(PKG)/librtb200.so $(CSRC)/*.ptxas.log
+.PHONY: all oracle clean

@@ -1,0 +1,173 @@
+/* png_io.c -- see png_io.h. */
+#include "png_io.h"
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <zlib.h>
+
+static const unsigned char kSig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+
+static uint32_t be32(const unsigned char* p) {
+    return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | (uint32_t)p[3];
+}
+
+typedef struct {
+    uint32_t w, h;
+    int depth, ctype, interlace;
+    unsigned char* idat; /* concatenated IDAT payloads (only when wanted) */
+    size_t idat_len;
+} png_file;
+
+static int parse(const char* path, png_file* pf, int want_idat) {
+    memset(pf, 0, sizeof *pf);
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return RTPNG_EOPEN;
+    unsigned char hdr[8];
+    if (fread(hdr, 1, 8, fp) != 8 || memcmp(hdr, kSig, 8) != 0) { fclose(fp); return RTPNG_ENOTPNG; }
+    int have_ihdr = 0, rc = RTPNG_ECORRUPT;
+    size_t cap = 0;
+    for (;;) {
+        unsigned char ch[8];
+        if (fread(ch, 1, 8, fp) != 8) break;
+        uint32_t len = be32(ch);
+        if (len > 0x7fffffffu) break;
+        if (!memcmp(ch + 4, "IHDR", 4)) {
+            unsigned char ih[13];
+            if (len != 13 || fread(ih, 1, 13, fp) != 13) break;
+            pf->w = be32(ih); pf->h = be32(ih + 4);
+            pf->depth = ih[8]; pf->ctype = ih[9]; pf->interlace = ih[12];
+            have_ihdr = 1;
+            if (fseek(fp, 4, SEEK_CUR)) break;
+            if (!want_idat) { rc = RTPNG_OK; break; }
+        } else if (!memcmp(ch + 4, "IDAT", 4) && want_idat) {
+            if (pf->idat_len + len > cap) {
+                cap = (pf->idat_len + len) * 2 + 4096;
+                unsigned char* n = (unsigned char*)realloc(pf->idat, cap);
+                if (!n) { rc = RTPNG_ENOMEM; break; }
+                pf->idat = n;
+            }
+            if (fread(pf->idat + pf->idat_len, 1, len, fp) != len) break;
+            pf->idat_len += len;
+            if (fseek(fp, 4, SEEK_CUR)) break;
+        } else if (!memcmp(ch + 4, "IEND", 4)) {
+            rc = have_ihdr ? RTPNG_OK : RTPNG_ECORRUPT;
+            break;
+        } else {
+            if (fseek(fp, (long)len + 4, SEEK_CUR)) break;
+        }
+    }
+    fclose(fp);
+    if (rc != RTPNG_OK) { free(pf->idat); pf->idat = NULL; }
+    return rc;
+}
+
+int rtpng_info(const char* path, uint32_t* w, uint32_t* h, int* bit_depth, int* colour_type, int* interlace) {
+    png_file pf;
+    int rc = parse(path, &pf, 0);
+    if (rc) return rc;
+    if (w) *w = pf.w;
+    if (h) *h = pf.h;
+    if (bit_depth) *bit_depth = pf.depth;
+    if (colour_type) *colour_type = pf.ctype;
+    if (interlace) *interlace = pf.interlace;
+    return RTPNG_OK;
+}
+
+static inline int paeth(int a, int b, int c) {
+    int p = a + b - c, pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+    return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+
+int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t h) {
+    png_file pf;
+    int rc = parse(path, &pf, 1);
+    if (rc) return rc;
+    if (pf.w != w || pf.h != h || pf.depth != 8 || pf.ctype != 2 || pf.interlace != 0) { free(pf.idat); return RTPNG_EFORMAT; }
+    const size_t stride = (size_t)w * 3, raw_len = (stride + 1) * h;
+    unsigned char* raw = (unsigned char*)malloc(raw_len ? raw_len : 1);
+    if (!raw) { free(pf.idat); return RTPNG_ENOMEM; }
+    z_stream zs;
+    memset(&zs, 0, sizeof zs);
+    if (inflateInit(&zs) != Z_OK) { free(raw); free(pf.idat); return RTPNG_ECORRUPT; }
+    size_t in_off = 0, out_off = 0;
+    int zr = Z_OK;
+    while (zr != Z_STREAM_END && out_off < raw_len) { /* feed in < 4 GiB pieces: avail_in/out are 32-bit */
+        size_t in_n = pf.idat_len - in_off, out_n = raw_len - out_off;
+        if (in_n > 0x40000000u) in_n = 0x40000000u;
+        if (out_n > 0x40000000u) out_n = 0x40000000u;
+        zs.next_in = pf.idat + in_off; zs.avail_in = (uInt)in_n;
+        zs.next_out = raw + out_off; zs.avail_out = (uInt)out_n;
+        zr = inflate(&zs, Z_NO_FLUSH);
+        in_off += in_n - zs.avail_in;
+        out_off += out_n - zs.avail_out;
+        if (zr != Z_OK && zr != Z_STREAM_END) break;
+        if (zr == Z_OK && in_n == 0) break;
+    }
+    inflateEnd(&zs);
+    free(pf.idat);
+    if (out_off != raw_len) { free(raw); return RTPNG_ECORRUPT; }
+    /* undo the five PNG filters in place (bpp = 3), expanding to RGBA as we go */
+    for (uint32_t y = 0; y < h; y++) {
+        unsigned char* cur = raw + (stride + 1) * y + 1;
+        const unsigned char* up = y ? raw + (stride + 1) * (y - 1) + 1 : NULL;
+        int ft = cur[-1];
+        if (ft > 4) { free(raw); return RTPNG_ECORRUPT; }
+        for (size_t i = 0; i < stride; i++) {
+            int a = i >= 3 ? cur[i - 3] : 0, b = up ? up[i] : 0, c = (up && i >= 3) ? up[i - 3] : 0;
+            int x = cur[i];
+            switch (ft) {
+                case 1: x += a; break;
+                case 2: x += b; break;
+                case 3: x += (a + b) >> 1; break;
+                case 4: x += paeth(a, b, c); break;
+                default: break;
+            }
+            cur[i] = (unsigned char)x;
+        }
+        uint8_t* o = dst + (size_t)y * w * 4;
+        for (uint32_t xx = 0; xx < w; xx++) {
+            o[4 * xx] = cur[3 * xx]; o[4 * xx + 1] = cur[3 * xx + 1]; o[4 * xx + 2] = cur[3 * xx + 2]; o[4 * xx + 3] = 255;
+        }
+    }
+    free(raw);
+    return RTPNG_OK;
+}
+
+static void put_chunk(FILE* fp, const char* type, const unsigned char* data, uint32_t len) {
+    unsigned char b[4] = {(unsigned char)(len >> 24), (unsigned char)(len >> 16), (unsigned char)(len >> 8), (unsigned char)len};
+    fwrite(b, 1, 4, fp);
+    fwrite(type, 1, 4, fp);
+    if (len) fwrite(data, 1, len, fp);
+    uLong crc = crc32(0L, (const Bytef*)type, 4);
+    if (len) crc = crc32(crc, data, len);
+    unsigned char c[4] = {(unsigned char)(crc >> 24), (unsigned char)(crc >> 16), (unsigned char)(crc >> 8), (unsigned char)crc};
+    fwrite(c, 1, 4, fp);
+}
+
+int rtpng_write_rgb8(const char* path, const uint8_t* rgb, uint32_t w, uint32_t h) {
+    const size_t stride = (size_t)w * 3, raw_len = (stride + 1) * h;
+    if (raw_len > 0x7ff00000u) return RTPNG_EFORMAT;
+    unsigned char* raw = (unsigned char*)malloc(raw_len ? raw_len : 1);
+    if (!raw) return RTPNG_ENOMEM;
+    for (uint32_t y = 0; y < h; y++) {
+        raw[(stride + 1) * y] = 0;
+        memcpy(raw + (stride + 1) * y + 1, rgb + stride * y, stride);
+    }
+    uLongf zcap = compressBound((uLong)raw_len);
+    unsigned char* z = (unsigned char*)malloc(zcap);
+    if (!z) { free(raw); return RTPNG_ENOMEM; }
+    if (compress2(z, &zcap, raw, (uLong)raw_len, 6) != Z_OK) { free(raw); free(z); return RTPNG_ECORRUPT; }
+    free(raw);
+    FILE* fp = fopen(path, "wb");
+    if (!fp) { free(z); return RTPNG_EOPEN; }
+    fwrite(kSig, 1, 8, fp);
+    unsigned char ih[13] = {(unsigned char)(w >> 24), (unsigned char)(w >> 16), (unsigned char)(w >> 8), (unsigned char)w,
+                            (unsigned char)(h >> 24), (unsigned char)(h >> 16), (unsigned char)(h >> 8), (unsigned char)h,
+                            8, 2, 0, 0, 0};
+    put_chunk(fp, "IHDR", ih, 13);
+    put_chunk(fp, "IDAT", z, (uint32_t)zcap);
+    put_chunk(fp, "IEND", NULL, 0);
+    free(z);
+    return fclose(fp) == 0 ? RTPNG_OK : RTPNG_EOPEN;
+}

@@ -1,0 +1,384 @@
+/* rt_engine.cu -- the C ABI of include/rtb200.h: device memory, uploads, launch bookkeeping.
+ * No CPU rendering path exists here: every render call ends in rt_launch_render (rt_kernels.cu). */
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/rtb200.h"
+#include "rt_kernels.h"
+
+namespace {
+
+thread_local char g_err[512] = "ok";
+
+int fail(int code, const char* what, cudaError_t ce = cudaSuccess) {
+    if (ce != cudaSuccess) snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(ce));
+    else snprintf(g_err, sizeof g_err, "%s", what);
+    return code;
+}
+#define CU(call, what)                                        \
+    do {                                                      \
+        cudaError_t ce_ = (call);                             \
+        if (ce_ != cudaSuccess) return fail(-2, what, ce_);   \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n) {
+        if (n <= cap && p) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n ? n : 16;
+        cudaError_t ce = cudaMalloc(&p, want);
+        if (ce != cudaSuccess) return fail(-2, "cudaMalloc", ce);
+        cap = want;
+        return 0;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace
+
+struct rtb_engine {
+    int device = 0;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+
+    DevBuf spheres, planes, lights; /* owned copies of the wire arrays */
+    const unsigned char *d_spheres = nullptr, *d_planes = nullptr, *d_lights = nullptr; /* owned or bound */
+    uint32_t S = 0, P = 0, L = 0;
+    DevBuf blob;
+    RtBlobLayout lay{};
+    bool have_scene = false;
+
+    DevBuf tex, sky;                             /* owned copies ... */
+    const void *d_tex = nullptr, *d_sky = nullptr; /* ... or arrays bound in place */
+    uint32_t tw = 0, th = 0, tl = 0, sw = 0, sh = 0;
+
+    float cam[14];
+    bool have_cam = false;
+
+    DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
+    rtb_launch_info last{};
+};
+
+extern "C" {
+
+const char* rtb_last_error(void) { return g_err; }
+
+int rtb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int rtb_create(rtb_engine** out, int device) {
+    if (!out) return fail(-1, "rtb_create: null out");
+    int n = 0;
+    CU(cudaGetDeviceCount(&n), "cudaGetDeviceCount");
+    if (device < 0 || device >= n) return fail(-1, "rtb_create: no such CUDA device");
+    CU(cudaSetDevice(device), "cudaSetDevice");
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+    if (prop.major < 10) return fail(-3, "rtb_create: this library is built for sm_100a only");
+    rtb_engine* e = new rtb_engine();
+    e->device = device;
+    e->sm_count = prop.multiProcessorCount;
+    e->smem_optin = prop.sharedMemPerBlockOptin;
+    CU(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    CU(cudaEventCreate(&e->ev0), "cudaEventCreate");
+    CU(cudaEventCreate(&e->ev1), "cudaEventCreate");
+    if (e->sched.ensure(256)) return -2;
+    CU(cudaMemset(e->sched.p, 0, 256), "cudaMemset");
+    memset(e->cam, 0, sizeof e->cam);
+    *out = e;
+    return 0;
+}
+
+void rtb_destroy(rtb_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
+    e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
+    cudaEventDestroy(e->ev0);
+    cudaEventDestroy(e->ev1);
+    cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+static int prep_scene(rtb_engine* e) {
+    e->lay = rt_blob_layout(e->S, e->P, e->L);
+    if (e->blob.ensure((size_t)e->lay.total * 16)) return -2;
+    CU(rt_launch_scene_prep(e->d_spheres, e->S, e->d_planes, e->P, e->d_lights, e->L, (float4*)e->blob.p, e->lay,
+                            e->stream),
+       "scene_prep launch");
+    e->have_scene = true;
+    return 0;
+}
+
+int rtb_upload_scene(rtb_engine* e, const void* spheres, uint32_t S, const void* planes, uint32_t P, const void* lights,
+                     uint32_t L) {
+    if (!e) return fail(-1, "null engine");
+    if ((S && !spheres) || (P && !planes) || (L && !lights)) return fail(-1, "rtb_upload_scene: null array with non-zero count");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaStreamSynchronize(e->stream), "sync before scene upload");
+    if (e->spheres.ensure((size_t)S * RT_SPHERE_BYTES) || e->planes.ensure((size_t)P * RT_PLANE_BYTES) ||
+        e->lights.ensure((size_t)L * RT_LIGHT_BYTES))
+        return -2;
+    if (S) CU(cudaMemcpyAsync(e->spheres.p, spheres, (size_t)S * RT_SPHERE_BYTES, cudaMemcpyHostToDevice, e->stream), "H2D spheres");
+    if (P) CU(cudaMemcpyAsync(e->planes.p, planes, (size_t)P * RT_PLANE_BYTES, cudaMemcpyHostToDevice, e->stream), "H2D planes");
+    if (L) CU(cudaMemcpyAsync(e->lights.p, lights, (size_t)L * RT_LIGHT_BYTES, cudaMemcpyHostToDevice, e->stream), "H2D lights");
+    e->d_spheres = (const unsigned char*)e->spheres.p;
+    e->d_planes = (const unsigned char*)e->planes.p;
+    e->d_lights = (const unsigned char*)e->lights.p;
+    e->S = S; e->P = P; e->L = L;
+    int rc = prep_scene(e);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(e->stream), "scene upload"); /* blocking, like clEnqueueWriteBuffer(CL_TRUE) */
+    return 0;
+}
+
+int rtb_bind_scene_device(rtb_engine* e, const void* d_spheres, uint32_t S, const void* d_planes, uint32_t P,
+                          const void* d_lights, uint32_t L) {
+    if (!e) return fail(-1, "null engine");
+    if ((S && !d_spheres) || (P && !d_planes) || (L && !d_lights)) return fail(-1, "rtb_bind_scene_device: null array");
+    if (((uintptr_t)d_spheres | (uintptr_t)d_planes | (uintptr_t)d_lights) & 15) return fail(-1, "rtb_bind_scene_device: arrays must be 16-byte aligned");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    e->d_spheres = (const unsigned char*)d_spheres;
+    e->d_planes = (const unsigned char*)d_planes;
+    e->d_lights = (const unsigned char*)d_lights;
+    e->S = S; e->P = P; e->L = L;
+    return prep_scene(e);
+}
+
+int rtb_upload_images(rtb_engine* e, int which, const uint8_t* rgba, uint32_t w, uint32_t h, uint32_t layers) {
+    if (!e) return fail(-1, "null engine");
+    if (which != 0 && which != 1) return fail(-1, "rtb_upload_images: which must be 0 (textures) or 1 (skybox)");
+    if (!rgba || !w || !h || !layers) return fail(-1, "rtb_upload_images: empty image array");
+    if (which == 1 && layers != 1) return fail(-1, "rtb_upload_images: the skybox is a 1-layer array");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaStreamSynchronize(e->stream), "sync before image upload");
+    size_t n = (size_t)w * h * layers * 4;
+    DevBuf& b = which ? e->sky : e->tex;
+    if (b.ensure(n)) return -2;
+    CU(cudaMemcpy(b.p, rgba, n, cudaMemcpyHostToDevice), "H2D images");
+    if (which) { e->sw = w; e->sh = h; e->d_sky = b.p; }
+    else { e->tw = w; e->th = h; e->tl = layers; e->d_tex = b.p; }
+    return 0;
+}
+
+int rtb_bind_images_device(rtb_engine* e, int which, const void* d_rgba, uint32_t w, uint32_t h, uint32_t layers) {
+    if (!e) return fail(-1, "null engine");
+    if (which != 0 && which != 1) return fail(-1, "rtb_bind_images_device: which must be 0 (textures) or 1 (skybox)");
+    if (!d_rgba || !w || !h || !layers) return fail(-1, "rtb_bind_images_device: empty image array");
+    if (which == 1 && layers != 1) return fail(-1, "rtb_bind_images_device: the skybox is a 1-layer array");
+    if ((uintptr_t)d_rgba & 3) return fail(-1, "rtb_bind_images_device: texels must be 4-byte aligned");
+    if (which) { e->sw = w; e->sh = h; e->d_sky = d_rgba; }
+    else { e->tw = w; e->th = h; e->tl = layers; e->d_tex = d_rgba; }
+    return 0;
+}
+
+int rtb_set_camera(rtb_engine* e, const float cam[14]) {
+    if (!e || !cam) return fail(-1, "rtb_set_camera: null argument");
+    memcpy(e->cam, cam, sizeof e->cam);
+    e->have_cam = true;
+    return 0;
+}
+
+uint32_t rtb_partition_rows(uint32_t H, const rtb_partition* p) {
+    if (!p || p->parts <= 1) return H;
+    if (!p->band_rows || p->part >= p->parts) return 0;
+    uint32_t bands = (H + p->band_rows - 1) / p->band_rows;
+    uint32_t rows = 0;
+    for (uint32_t b = p->part; b < bands; b += p->parts) {
+        uint32_t y0 = b * p->band_rows, y1 = y0 + p->band_rows;
+        rows += (y1 > H ? H : y1) - y0;
+    }
+    return rows;
+}
+
+static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
+                       uint32_t* d_hit, int want_hit, uint64_t* counters) {
+    if (!e) return fail(-1, "null engine");
+    if (!e->have_scene) return fail(-1, "rtb_render: no scene uploaded");
+    if (!e->have_cam) return fail(-1, "rtb_render: no camera set");
+    if (!e->d_sky) return fail(-1, "rtb_render: no skybox image uploaded (kernel arg 9)");
+    if (!W || !H) return fail(-1, "rtb_render: empty frame");
+    if ((uint64_t)W * H > 0xffffffffull) return fail(-1, "rtb_render: W*H exceeds the 32-bit pixel id (raygen.cl:10)");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+
+    rtb_partition whole = {H, 1, 0};
+    rtb_partition pp = part ? *part : whole;
+    if (pp.parts <= 1) { pp.parts = 1; pp.part = 0; pp.band_rows = H; }
+    if (!pp.band_rows || pp.part >= pp.parts) return fail(-1, "rtb_render: bad partition");
+    const uint32_t rows = rtb_partition_rows(H, &pp);
+
+    RtFrameParams fp;
+    memset(&fp, 0, sizeof fp);
+    memcpy(fp.corner, e->cam + 0, 12); memcpy(fp.origin, e->cam + 3, 12);
+    memcpy(fp.up, e->cam + 6, 12); memcpy(fp.right, e->cam + 9, 12);
+    fp.wf = e->cam[12]; fp.hf = e->cam[13];
+    fp.W = W; fp.H = H; fp.total = total;
+    fp.band_rows = pp.band_rows; fp.parts = pp.parts; fp.part = pp.part; fp.local_rows = rows;
+    fp.S = e->S; fp.P = e->P; fp.L = e->L; fp.lay = e->lay;
+    fp.blob = (const float4*)e->blob.p;
+    fp.raw_spheres = e->d_spheres; fp.raw_planes = e->d_planes;
+    /* a scene whose planes carry texture ids needs the texture array; without one, ids clamp onto a 1x1 dummy */
+    fp.tex = (const uchar4*)(e->d_tex ? e->d_tex : e->d_sky);
+    fp.tw = e->d_tex ? (int)e->tw : 1; fp.th = e->d_tex ? (int)e->th : 1; fp.tl = e->d_tex ? (int)e->tl : 1;
+    fp.sky = (const uchar4*)e->d_sky; fp.sw = (int)e->sw; fp.sh = (int)e->sh;
+
+    const size_t nbytes = (size_t)rows * W * 4;
+    if (!d_out) {
+        if (e->frame.ensure(nbytes)) return -2;
+        d_out = (uint32_t*)e->frame.p;
+    }
+    if (!d_hit && want_hit) {
+        if (e->hit.ensure(nbytes)) return -2;
+        d_hit = (uint32_t*)e->hit.p;
+    }
+    if (((uintptr_t)d_out & 15) || ((uintptr_t)d_hit & 15)) return fail(-1, "rtb_render: output buffers must be 16-byte aligned");
+    fp.out = d_out;
+    fp.hit = d_hit;
+    fp.tile_counter = (unsigned int*)e->sched.p;
+    fp.counters = (unsigned long long*)((char*)e->sched.p + 64);
+    fp.tiles_x = (W + 7) / 8;
+    fp.tiles_y = (rows + 3) / 4;
+
+    e->last.tiles = fp.tiles_x * fp.tiles_y;
+    if (rows == 0) { e->timed = false; return 0; }
+
+    CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter");
+    CU(cudaEventRecord(e->ev0, e->stream), "event record");
+    RtLaunchShape shape{};
+    CU(rt_launch_render(fp, counters != nullptr, e->sm_count, e->smem_optin, e->stream, &shape), "render_frame launch");
+    CU(cudaEventRecord(e->ev1, e->stream), "event record");
+    e->timed = true;
+    e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;
+    e->last.resident_scene = shape.resident;
+    if (counters) {
+        unsigned long long host[RTB_NCOUNTERS];
+        CU(cudaMemcpyAsync(host, fp.counters, sizeof host, cudaMemcpyDeviceToHost, e->stream), "D2H counters");
+        CU(cudaStreamSynchronize(e->stream), "render_frame (counted)");
+        for (int k = 0; k < RTB_NCOUNTERS; k++) counters[k] = host[k];
+    }
+    return 0;
+}
+
+int rtb_render(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
+               uint32_t* d_hit, int want_hit) {
+    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, nullptr);
+}
+int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
+                       uint32_t* d_hit, int want_hit, uint64_t* counters) {
+    if (!counters) return fail(-1, "rtb_render_counted: null counters");
+    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, counters);
+}
+
+int rtb_sync(rtb_engine* e) {
+    if (!e) return fail(-1, "null engine");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaStreamSynchronize(e->stream), "stream synchronize (a kernel may have faulted)");
+    return 0;
+}
+
+static int read_buf(rtb_engine* e, DevBuf& b, void* host, size_t nbytes, const char* what) {
+    if (!e || !host) return fail(-1, "null argument");
+    if (!b.p || nbytes > b.cap) return fail(-1, what);
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaMemcpyAsync(host, b.p, nbytes, cudaMemcpyDeviceToHost, e->stream), "D2H");
+    CU(cudaStreamSynchronize(e->stream), "D2H sync");
+    return 0;
+}
+int rtb_read_frame(rtb_engine* e, void* host, size_t nbytes) { return read_buf(e, e->frame, host, nbytes, "rtb_read_frame: no frame of that size"); }
+int rtb_read_hit(rtb_engine* e, void* host, size_t nbytes) { return read_buf(e, e->hit, host, nbytes, "rtb_read_hit: no hit buffer of that size"); }
+uint32_t* rtb_frame_ptr(rtb_engine* e) { return e ? (uint32_t*)e->frame.p : nullptr; }
+uint32_t* rtb_hit_ptr(rtb_engine* e) { return e ? (uint32_t*)e->hit.p : nullptr; }
+
+float rtb_last_render_ms(rtb_engine* e) {
+    if (!e || !e->timed) return -1.0f;
+    if (cudaSetDevice(e->device) != cudaSuccess) return -1.0f;
+    if (cudaEventSynchronize(e->ev1) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) != cudaSuccess) return -1.0f;
+    return ms;
+}
+void* rtb_stream(rtb_engine* e) { return e ? (void*)e->stream : nullptr; }
+
+int rtb_dev_alloc(rtb_engine* e, void** dptr, size_t nbytes) {
+    if (!e || !dptr) return fail(-1, "null argument");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaMalloc(dptr, nbytes ? nbytes : 16), "cudaMalloc");
+    return 0;
+}
+int rtb_dev_free(rtb_engine* e, void* dptr) {
+    if (!e) return fail(-1, "null engine");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaFree(dptr), "cudaFree");
+    return 0;
+}
+int rtb_dev_write(rtb_engine* e, void* dptr, const void* host, size_t nbytes) {
+    if (!e || !dptr || !host) return fail(-1, "null argument");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaMemcpyAsync(dptr, host, nbytes, cudaMemcpyHostToDevice, e->stream), "H2D");
+    CU(cudaStreamSynchronize(e->stream), "H2D sync");
+    return 0;
+}
+int rtb_dev_read(rtb_engine* e, void* host, const void* dptr, size_t nbytes) {
+    if (!e || !dptr || !host) return fail(-1, "null argument");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaMemcpyAsync(host, dptr, nbytes, cudaMemcpyDeviceToHost, e->stream), "D2H");
+    CU(cudaStreamSynchronize(e->stream), "D2H sync");
+    return 0;
+}
+int rtb_host_register(void* host, size_t nbytes) {
+    CU(cudaHostRegister(host, nbytes, cudaHostRegisterDefault), "cudaHostRegister");
+    return 0;
+}
+int rtb_host_unregister(void* host) {
+    CU(cudaHostUnregister(host), "cudaHostUnregister");
+    return 0;
+}
+
+int rtb_last_launch(rtb_engine* e, rtb_launch_info* info) {
+    if (!e || !info) return fail(-1, "null argument");
+    *info = e->last;
+    return 0;
+}
+
+double rtb_fp32_peak_tflops(rtb_engine* e, int iters) {
+    if (!e || iters < 1) return -1.0;
+    if (cudaSetDevice(e->device) != cudaSuccess) return -1.0;
+    float* sink = (float*)((char*)e->sched.p + 192);
+    const int threads = 256, blocks = e->sm_count * 8;
+    cudaEvent_t a, b;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return -1.0;
+    double best = -1.0;
+    for (int rep = 0; rep < 4; rep++) { /* first repetition warms up */
+        cudaEventRecord(a, e->stream);
+        if (rt_launch_fma_peak(sink, iters, blocks, threads, e->stream) != cudaSuccess) { best = -1.0; break; }
+        cudaEventRecord(b, e->stream);
+        if (cudaEventSynchronize(b) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, a, b);
+        double flop = 2.0 * 64.0 * (double)iters * (double)threads * (double)blocks;
+        double tf = flop / ((double)ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    return best;
+}
+
+}  // extern "C"

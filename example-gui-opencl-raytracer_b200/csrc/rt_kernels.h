@@ -1,0 +1,72 @@
+/* rt_kernels.h -- internal interface between the engine (rt_engine.cu) and the kernels (rt_kernels.cu).
+ * Not part of the C ABI (that is include/rtb200.h). */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+/* Wire sizes, reference src/cl/types.cl:4-42 (== src/cpu_obj.h:10-48). */
+#define RT_SPHERE_BYTES 96
+#define RT_PLANE_BYTES 96
+#define RT_LIGHT_BYTES 48
+#define RT_MATERIAL_OFFSET 32 /* rmaterial sits at byte 32 of rsphere and rplane */
+
+/* Compact geometry ("scene blob"), produced on the device by scene_prep and staged into shared memory
+ * by one TMA bulk copy per CTA.  Units are float4 records:
+ *   [sph_off  .. +S )   {cx, cy, cz, r*r}
+ *   [pln_off  .. +4P)   {n.xyz, -}, {p.xyz, -}, {basis0.xyz, texture_scale}, {basis1.xyz, texture_id bits}
+ *   [lit_off  .. +2L)   {o.xyz, r*r}, {rgb*intensity*M_1_PI_F, radius}
+ *   [flag_off .. +ceil(S/4)) one uint32 per sphere: material.transperent != 0
+ */
+struct RtBlobLayout {
+    uint32_t sph_off, pln_off, lit_off, flag_off, total; /* in float4 records */
+};
+static inline RtBlobLayout rt_blob_layout(uint32_t S, uint32_t P, uint32_t L) {
+    RtBlobLayout b;
+    b.sph_off = 0;
+    b.pln_off = S;
+    b.lit_off = b.pln_off + 4 * P;
+    b.flag_off = b.lit_off + 2 * L;
+    b.total = b.flag_off + (S + 3) / 4;
+    if (b.total == 0) b.total = 1;
+    return b;
+}
+
+struct RtFrameParams {
+    /* raygen.cl:5-8 scalar arguments */
+    float corner[3], origin[3], up[3], right[3], wf, hf;
+    uint32_t W, H, total;
+    /* row-band partition (rtb200.h) */
+    uint32_t band_rows, parts, part, local_rows;
+    /* scene */
+    uint32_t S, P, L;
+    RtBlobLayout lay;
+    const float4* blob;
+    const unsigned char* raw_spheres; /* wire arrays: materials are read in place */
+    const unsigned char* raw_planes;
+    /* image arrays */
+    const uchar4* tex; int tw, th, tl;
+    const uchar4* sky; int sw, sh;
+    /* outputs (compact: local_rows x W) */
+    uint32_t* out;
+    uint32_t* hit; /* may be NULL */
+    /* scheduling */
+    unsigned int* tile_counter; /* zeroed before launch */
+    uint32_t tiles_x, tiles_y;
+    unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
+};
+
+/* scene_prep: wire arrays -> blob. */
+cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, const unsigned char* d_planes, uint32_t P,
+                                 const unsigned char* d_lights, uint32_t L, float4* d_blob, RtBlobLayout lay,
+                                 cudaStream_t st);
+
+struct RtLaunchShape {
+    uint32_t grid, block, smem_bytes, resident;
+};
+/* Chooses the variant (geometry resident in shared memory or read through L1/L2; counted or not; AOV or not)
+ * and launches the fused raygen+raytracer kernel. */
+cudaError_t rt_launch_render(const RtFrameParams& fp, bool counted, int sm_count, size_t smem_optin,
+                             cudaStream_t st, RtLaunchShape* shape);
+cudaError_t rt_render_init(void); /* one-time function attribute setup */
+
+cudaError_t rt_launch_fma_peak(float* d_sink, int iters, int blocks, int threads, cudaStream_t st);

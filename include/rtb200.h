@@ -1,0 +1,128 @@
+/* include/rtb200.h -- C ABI of the B200 render engine (librtb200.so).
+ *
+ * This is the device half of the drop-in boundary: the `cl_wrap_*` entry points in cuda_wrap.h
+ * (which replace /root/reference/src/opencl_wrap.h:29-42) are a thin C layer over these calls.
+ * Plain pointers and sizes only; no C++ or torch types.  All functions return 0 on success and a
+ * negative code on failure; rtb_last_error() returns a static, human-readable reason.
+ *
+ * What one engine holds (all in HBM of one GPU):
+ *   - the raw wire arrays the host uploads, byte for byte (rsphere 96 B, rplane 96 B, rlight 48 B;
+ *     reference src/cl/types.cl:4-42 == src/cpu_obj.h:10-48),
+ *   - the two RGBA8 image arrays (what opencl_wrap.c:189-349 builds: layers x H x W x uchar4),
+ *   - a compact copy of the geometry produced on the device by the `scene_prep` kernel,
+ *   - the frame buffer (0x00RRGGBB words, raytracing.cl:193-194) and the optional primary hit-id buffer.
+ * The renderer fuses the reference's two kernels, `raygen` (src/cl/raygen.cl:5-25) and
+ * `raytracer` (src/cl/raytracing.cl:14-195).
+ */
+#ifndef RTB200_H
+#define RTB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rtb_engine rtb_engine;
+
+/* Hit-id encoding: 0 sky, 1+i sphere i, 1+S+j plane j, RTB_HIT_LIGHT|k light k. */
+#define RTB_HIT_LIGHT 0x80000000u
+
+/* Work counters filled by rtb_render_counted (same order as oracle/rt_oracle.h). */
+enum {
+    RTB_SEGMENTS = 0,     /* iterations of raytracing.cl:42 */
+    RTB_SHADOW_RAYS = 1,  /* testShadowPath calls, raytracing.cl:108 */
+    RTB_SPHERE_TESTS = 2, /* intersect_sphere calls (spheres and lights), primitives.cl:170 */
+    RTB_SPHERE_DPOS = 3,  /* ... of which had D >= 0 */
+    RTB_PLANE_TESTS = 4,  /* intersect_plane calls, primitives.cl:197 */
+    RTB_TEXELS = 5,       /* texel fetches the reference would make (primitives.cl:250, raytracing.cl:70) */
+    RTB_NCOUNTERS = 8
+};
+
+/* Row-band partition of a frame.  Bands of `band_rows` rows are dealt out
+ * cyclically: band b belongs to part (b % parts).  Part `part` renders its rows into a COMPACT
+ * buffer (local row lr <-> global row ((lr / band_rows) * parts + part) * band_rows + lr % band_rows)
+ * while pixel ids (RNG seed, raytracing.cl:33; raygen.cl:13-14) stay global.
+ * {band_rows = H, parts = 1, part = 0} is the whole frame. */
+typedef struct {
+    uint32_t band_rows;
+    uint32_t parts;
+    uint32_t part;
+} rtb_partition;
+
+const char* rtb_last_error(void);
+int rtb_device_count(void);
+
+/* Create an engine on CUDA device `device` (its own non-blocking stream). */
+int rtb_create(rtb_engine** out, int device);
+void rtb_destroy(rtb_engine* e);
+
+/* Upload the scene arrays in wire format (blocking H2D), then run scene_prep on the device.
+ * Pointers may be NULL when the count is 0.  Replaces any previous scene. */
+int rtb_upload_scene(rtb_engine* e, const void* spheres, uint32_t S, const void* planes, uint32_t P,
+                     const void* lights, uint32_t L);
+/* Same, but the wire arrays already live in this device's memory (not copied, must stay valid). */
+int rtb_bind_scene_device(rtb_engine* e, const void* d_spheres, uint32_t S, const void* d_planes, uint32_t P,
+                          const void* d_lights, uint32_t L);
+
+/* RGBA8 image arrays, layers*h*w*4 bytes, row 0 = top row.  which: 0 = plane textures (kernel arg 8),
+ * 1 = skybox (kernel arg 9, layers must be 1). */
+int rtb_upload_images(rtb_engine* e, int which, const uint8_t* rgba, uint32_t w, uint32_t h, uint32_t layers);
+/* Same, but the texels already live in this device's memory (not copied, must stay valid). */
+int rtb_bind_images_device(rtb_engine* e, int which, const void* d_rgba, uint32_t w, uint32_t h, uint32_t layers);
+
+/* The raygen kernel's scalar arguments (raygen.cl:5-8): corner, origin, up, right (xyz each), w_factor,
+ * h_factor.  Latched by value; takes effect at the next render. */
+int rtb_set_camera(rtb_engine* e, const float cam[14]);
+
+/* Number of rows part `part` owns in an H-row frame. */
+uint32_t rtb_partition_rows(uint32_t H, const rtb_partition* p);
+
+/* Launch one frame (asynchronously, on the engine's stream).  `total` is the raytracer kernel's
+ * total_size guard (raytracing.cl:23-26); pass W*H.  d_out / d_hit are DEVICE pointers to
+ * rows*W uint32 each, or NULL to use the engine's own buffers (d_hit NULL + want_hit 0 = no AOV). */
+int rtb_render(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
+               uint32_t* d_hit, int want_hit);
+/* Same launch with work counters (slower, for accounting only). counters[RTB_NCOUNTERS] is host memory;
+ * the call synchronises. */
+int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part,
+                       uint32_t* d_out, uint32_t* d_hit, int want_hit, uint64_t* counters);
+
+/* Wait for the engine's stream. */
+int rtb_sync(rtb_engine* e);
+/* Blocking D2H of the engine's own frame / hit buffers (nbytes from the start). */
+int rtb_read_frame(rtb_engine* e, void* host, size_t nbytes);
+int rtb_read_hit(rtb_engine* e, void* host, size_t nbytes);
+/* Device pointers of the engine's own buffers (valid until the next larger render). */
+uint32_t* rtb_frame_ptr(rtb_engine* e);
+uint32_t* rtb_hit_ptr(rtb_engine* e);
+
+/* Device time of the last render launch in milliseconds (CUDA events on the engine's stream;
+ * synchronises).  Negative on error. */
+float rtb_last_render_ms(rtb_engine* e);
+/* The engine's CUDA stream as a cudaStream_t cast to void* (for callers that enqueue their own
+ * work, e.g. a collective, behind the render). */
+void* rtb_stream(rtb_engine* e);
+
+/* Raw device memory helpers for callers without a CUDA runtime of their own (the cl_wrap layer). */
+int rtb_dev_alloc(rtb_engine* e, void** dptr, size_t nbytes);
+int rtb_dev_free(rtb_engine* e, void* dptr);
+int rtb_dev_write(rtb_engine* e, void* dptr, const void* host, size_t nbytes); /* blocking H2D */
+int rtb_dev_read(rtb_engine* e, void* host, const void* dptr, size_t nbytes);  /* blocking D2H */
+int rtb_host_register(void* host, size_t nbytes);   /* page-lock a caller buffer (optional fast path) */
+int rtb_host_unregister(void* host);
+
+/* Launch geometry the renderer chose for the last frame (for bench.py's accounting). */
+typedef struct {
+    uint32_t grid, block, smem_bytes, tiles, resident_scene; /* resident_scene: 1 = geometry staged in shared memory */
+} rtb_launch_info;
+int rtb_last_launch(rtb_engine* e, rtb_launch_info* info);
+
+/* FP32 pipe calibration: runs a dependent-FMA kernel for `iters` iterations per thread on the
+ * engine's device and returns the measured TFLOP/s (FMA = 2 flop), or a negative value on error. */
+double rtb_fp32_peak_tflops(rtb_engine* e, int iters);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
