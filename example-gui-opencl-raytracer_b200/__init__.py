@@ -182,11 +182,15 @@ class Engine:
 
     def read_frame(self, npixels):
         out = np.empty(npixels, np.uint32)
+        if npixels == 0:
+            return out
         _check(lib().rtb_read_frame(self._h, _host_ptr(out), out.nbytes), "rtb_read_frame")
         return out
 
     def read_hit(self, npixels):
         out = np.empty(npixels, np.uint32)
+        if npixels == 0:
+            return out
         _check(lib().rtb_read_hit(self._h, _host_ptr(out), out.nbytes), "rtb_read_hit")
         return out
 

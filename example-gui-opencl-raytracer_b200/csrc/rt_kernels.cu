@@ -649,9 +649,11 @@ cudaError_t launch_variant(const RtFrameParams& fp, uint32_t grid, uint32_t smem
 }
 template <bool R, bool C, bool A>
 cudaError_t prep_variant(size_t smem_optin, int* blocks_per_sm, uint32_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(render_frame<R, C, A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem_optin);
-    if (e != cudaSuccess) return e;
+    (void)smem_optin;
+    if (smem > 48u * 1024u) {
+        cudaError_t e = cudaFuncSetAttribute(render_frame<R, C, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_frame<R, C, A>, kBlock, smem);
 }
 
