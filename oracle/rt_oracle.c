@@ -73,6 +73,7 @@ static inline int f2i(float f) {
 /* per-thread work counters */
 typedef struct { uint64_t c[RTO_NCOUNTERS]; } counters_t;
 static __thread counters_t* tl_cnt = 0;
+static __thread uint32_t tl_pixel_segments = 0; /* segments of the pixel being traced (cost map) */
 #define COUNT(k) do { if (tl_cnt) tl_cnt->c[k]++; } while (0)
 
 /* clamp-to-edge texel fetch; ref: read_imagei at primitives.cl:250 / raytracing.cl:70 (Q10) */
@@ -315,6 +316,7 @@ static uint32_t trace_pixel(const float* cam, uint32_t W, uint32_t id, const sce
     entry_t st[STACK_MAX];
     uint32_t rng = id;                               /* :32-33, Q1 */
     uint32_t sz = 1;
+    tl_pixel_segments = 0;
     primary_ray(cam, W, id, &st[0].o, &st[0].d);
     st[0].rgb = mk(0, 0, 0); st[0].depth = 0; st[0].n = AIR_N; st[0].f = 1.0f;
 
@@ -331,6 +333,7 @@ static uint32_t trace_pixel(const float* cam, uint32_t W, uint32_t id, const sce
         while (st[sz - 1].depth < STACK_MAX) {
             entry_t* top = &st[sz - 1];
             COUNT(RTO_SEGMENTS);
+            tl_pixel_segments++;
             v3 lcol;
             if (find_light(top->o, top->d, sc, &lcol, 0)) {          /* :48-54 */
                 top->rgb = add(top->rgb, scl(lcol, top->f));
@@ -397,7 +400,7 @@ static uint32_t trace_pixel(const float* cam, uint32_t W, uint32_t id, const sce
                 ch->f = old_f * (1.0f - refl);
                 ch->rgb = mk(0, 0, 0);
                 ch->n = n2;
-                if (!bend_dir(n1, n2, incident, nrm, &ch->d)) continue;  /* TIR: child dropped, Q5 */
+                if (!bend_dir(n1, n2, incident, nrm, &ch->d) || ch->d.x != ch->d.x) continue;  /* TIR / isnan(dir.x): child dropped, Q5 */
                 sz++;
             }
         }
@@ -470,6 +473,19 @@ int rto_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t y0, 
                int threads) {
     return rto_render_counted(wide, cam, W, H, y0, y1, spheres, S, planes, P, lights, L, tex, tw, th, tl, sky, sw,
                               sh, out, hit, threads, 0);
+}
+
+/* Cost map: segments traced per pixel (single-threaded; for load-balance analysis, not a parity surface). */
+int rto_segment_map(const float* cam, uint32_t W, uint32_t H, const void* spheres, uint32_t S, const void* planes,
+                    uint32_t P, const void* lights, uint32_t L, const uint8_t* tex, int tw, int th, int tl,
+                    const uint8_t* sky, int sw, int sh, uint32_t* seg) {
+    scene_t sc = {(const w_sphere*)spheres, S, (const w_plane*)planes, P, (const w_light*)lights, L,
+                  tex, tw, th, tl, sky, sw, sh};
+    for (uint32_t id = 0; id < W * H; id++) {
+        (void)trace_pixel(cam, W, id, &sc, 0);
+        seg[id] = tl_pixel_segments;
+    }
+    return 0;
 }
 
 /* ---------- per-function known-answer entry points ---------- */

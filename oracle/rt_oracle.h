@@ -44,6 +44,11 @@ int rto_render_counted(int wide, const float* cam, uint32_t W, uint32_t H, uint3
                        uint32_t L, const uint8_t* tex, int tw, int th, int tl, const uint8_t* sky, int sw, int sh,
                        uint32_t* out, uint32_t* hit, int threads, uint64_t* counters);
 
+/* Segments traced per pixel (cost map for load-balance analysis; single-threaded). */
+int rto_segment_map(const float* cam, uint32_t W, uint32_t H, const void* spheres, uint32_t S, const void* planes,
+                    uint32_t P, const void* lights, uint32_t L, const uint8_t* tex, int tw, int th, int tl,
+                    const uint8_t* sky, int sw, int sh, uint32_t* seg);
+
 /* Per-function known-answer entry points (same names with the ref_ prefix exist in _ref/libref_cl.so). */
 float rto_xorshift32(uint32_t* state);
 void rto_map_to_cube(const float* dir, uint32_t face, int* uv);
