@@ -5,7 +5,7 @@ PKG   := example-gui-opencl-raytracer_b200
 CSRC  := $(PKG)/csrc
 NVCC  ?= nvcc
 ARCH  := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xptxas -v
+NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 --extended-lambda -Xcompiler -fPIC -Xptxas -v
 KFLAGS  := -fmad=false -prec-div=true -prec-sqrt=true -ftz=false
 CFLAGS  := -O2 -std=gnu11 -fPIC -Wall -Wextra -ffp-contract=off -Iinclude -Iinclude/shim
 
@@ -13,7 +13,7 @@ OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png
 
 all: $(PKG)/librtb200.so
 
-$(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h include/rtb200.h
+$(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels.ptxas.log || (cat $(CSRC)/rt_kernels.ptxas.log; false)
 	@grep -E "registers|spill" $(CSRC)/rt_kernels.ptxas.log | sort | uniq -c | sort -rn | head -20
 

@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "librtb200.so")
 
 HIT_LIGHT = 0x80000000
-COUNTER_NAMES = ("segments", "shadow_rays", "sphere_tests", "sphere_dpos", "plane_tests", "texels")
+COUNTER_NAMES = ("segments", "shadow_rays", "sphere_tests", "sphere_dpos", "plane_tests", "texels", "shadow_skipped")
 NCOUNTERS = 8
 
 # Every symbol include/rtb200.h and include/cuda_wrap.h declare (checked by tests/test_abi.py).
@@ -26,7 +26,7 @@ ENGINE_SYMBOLS = (
     "rtb_last_error", "rtb_device_count", "rtb_create", "rtb_destroy", "rtb_upload_scene", "rtb_bind_scene_device",
     "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
-    "rtb_last_render_ms", "rtb_stream", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
+    "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
     "rtb_host_register", "rtb_host_unregister", "rtb_last_launch", "rtb_fp32_peak_tflops",
 )
 WRAP_SYMBOLS = (
@@ -73,7 +73,10 @@ def lib():
             "rtb_set_camera": (i, [vp, C.POINTER(C.c_float)]),
             "rtb_partition_rows": (u32, [u32, pp]),
             "rtb_render": (i, [vp, u32, u32, u32, pp, vp, vp, i]),
-            "rtb_render_counted": (i, [vp, u32, u32, u32, pp, vp, vp, i, C.POINTER(C.c_uint64)]),
+            "rtb_render_counted": (i, [vp, u32, u32, u32, pp, vp, vp, i, i, C.POINTER(C.c_uint64)]),
+            "rtb_set_option": (i, [vp, C.c_char_p, i]),
+            "rtb_selftest_arith": (i, [vp, u32, u32, C.POINTER(u32)]),
+            "rtb_last_kernel_ms": (C.c_float, [vp]),
             "rtb_sync": (i, [vp]),
             "rtb_read_frame": (i, [vp, vp, sz]),
             "rtb_read_hit": (i, [vp, vp, sz]),
@@ -167,11 +170,12 @@ class Engine:
         _check(lib().rtb_render(self._h, W, H, total, C.byref(part) if part is not None else None, d_out, d_hit,
                                 int(bool(want_hit))), "rtb_render")
 
-    def render_counted(self, W, H, total=None, part=None, d_out=None, d_hit=None, want_hit=False):
+    def render_counted(self, W, H, total=None, part=None, d_out=None, d_hit=None, want_hit=False, executed=False):
+        """executed=False: literal trace, the reference's own work counts; True: what the production trace does."""
         total = W * H if total is None else total
         cnt = (C.c_uint64 * NCOUNTERS)()
         _check(lib().rtb_render_counted(self._h, W, H, total, C.byref(part) if part is not None else None, d_out,
-                                        d_hit, int(bool(want_hit)), cnt), "rtb_render_counted")
+                                        d_hit, int(bool(want_hit)), int(bool(executed)), cnt), "rtb_render_counted")
         c = {k: int(cnt[i]) for i, k in enumerate(COUNTER_NAMES)}
         c["rays"] = c["segments"] + c["shadow_rays"]
         c["flop"] = algorithmic_flop(c)
@@ -206,6 +210,20 @@ class Engine:
         if ms < 0:
             raise RtbError("no timed render")
         return ms
+
+    def last_kernel_ms(self):
+        ms = float(lib().rtb_last_kernel_ms(self._h))
+        if ms < 0:
+            raise RtbError("no timed render")
+        return ms
+
+    def set_option(self, name, value):
+        _check(lib().rtb_set_option(self._h, name.encode(), int(value)), "rtb_set_option")
+
+    def selftest_arith(self, seed=1, per_thread=2000):
+        out = (C.c_uint32 * 3)()
+        _check(lib().rtb_selftest_arith(self._h, seed, per_thread, out), "rtb_selftest_arith")
+        return {"div_mismatch": int(out[0]), "normalize_mismatch": int(out[1]), "sincos_max_dev_2p24": int(out[2])}
 
     def last_launch(self):
         info = LaunchInfo()

@@ -1,0 +1,243 @@
+/* rt_device.cuh -- device-side vocabulary shared by the trace variants (included only by rt_kernels.cu).
+ *
+ * Arithmetic contract (must equal oracle/cl_shim.hpp): binary32, round-to-nearest-even, NO contraction.
+ * The translation unit is compiled with -fmad=false -prec-div=true -prec-sqrt=true -ftz=false, so every
+ * + - * / sqrtf written below is one correctly rounded operation in source order; FMAs appear only where
+ * written explicitly (__fmaf_rn) inside routines whose RESULT is proven/tested to equal the IEEE operation.
+ * Reference citations: /root/reference/src/cl/{raygen,raytracing,primitives,types}.cl.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "../../include/rtb200.h"
+#include "rt_kernels.h"
+
+namespace rt {
+
+constexpr float kEps = 0.001f;                     /* primitives.cl:5  EPSILON */
+constexpr float kInvPi = 0.318309886183790671538f; /* primitives.cl:6  M_1_PI_F */
+constexpr float kGlassPass = 0.8f;                 /* primitives.cl:7  TRANSPERENT_THROUGH */
+constexpr float kAirN = 1.0f;                      /* raytracing.cl:7  DEFAULT_N */
+constexpr int kMaxDepth = 15;                      /* raytracing.cl:9  MAX_DEPTH */
+constexpr int kShadowSamples = 2;                  /* raytracing.cl:10 MAX_SOFT_SHADOWS */
+constexpr int kTileW = 8, kTileH = 4;              /* one warp */
+constexpr int kBlock = 128;
+constexpr double kTwoPi = 6.283185307179586476925286766559; /* 2*M_PI, a double in OpenCL C (raytracing.cl:99) */
+constexpr double kPi = 3.14159265358979323846264338327950288;
+
+struct V3 {
+    float x, y, z;
+};
+__device__ __forceinline__ V3 mk(float x, float y, float z) { return V3{x, y, z}; }
+__device__ __forceinline__ V3 xyz(float4 v) { return V3{v.x, v.y, v.z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+
+/* (int)f with the x86 cvttss2si result for out-of-range / NaN inputs. */
+__device__ __forceinline__ int f2i_x86(float f) {
+    return (f >= -2147483648.0f && f < 2147483648.0f) ? __float2int_rz(f) : (int)0x80000000;
+}
+/* primitives.cl:162-168 */
+__device__ __forceinline__ int emod(int a, int b) {
+    int m = a % b;
+    if (m < 0) m = (b < 0) ? m - b : m + b;
+    return m;
+}
+/* clamp(v, 0, 1) as min(max(v, 0), 1) with max(a,b) = a<b ? b : a, min(a,b) = b<a ? b : a (oracle/cl_shim.hpp) */
+__device__ __forceinline__ float clamp01(float v) {
+    float m = (v < 0.0f) ? 0.0f : v;
+    return (1.0f < m) ? 1.0f : m;
+}
+__device__ __forceinline__ int clampi(int v, int hi) { return v < 0 ? 0 : (v >= hi ? hi - 1 : v); }
+/* raytracing.cl:193-194 */
+__device__ __forceinline__ uint32_t pack_rgb(V3 rgb) {
+    float cr = clamp01(rgb.x) * 255.0f, cg = clamp01(rgb.y) * 255.0f, cb = clamp01(rgb.z) * 255.0f;
+    return ((uint32_t)cr << 16) | ((uint32_t)cg << 8) | (uint32_t)cb;
+}
+
+/* Work counters: a no-op unless COUNT. */
+template <bool COUNT>
+struct Tally {
+    uint32_t c[RTB_NCOUNTERS];
+    __device__ __forceinline__ void clear() {
+#pragma unroll
+        for (int i = 0; i < RTB_NCOUNTERS; i++) c[i] = 0;
+    }
+    __device__ __forceinline__ void add(int k, uint32_t n = 1) { c[k] += n; }
+    __device__ __forceinline__ uint32_t get(int k) const { return c[k]; }
+};
+template <>
+struct Tally<false> {
+    __device__ __forceinline__ void clear() {}
+    __device__ __forceinline__ void add(int, uint32_t = 1) {}
+    __device__ __forceinline__ uint32_t get(int) const { return 0; }
+};
+
+/* Geometry records (rt_kernels.h: RtBlobLayout), in shared memory when resident. */
+struct Geo {
+    const float4* sph;
+    const float4* pln;
+    const float4* lit;
+    const uint32_t* flag;
+    const float* lut255; /* i / 255.0f for i in 0..255 (IEEE division, filled once per CTA) */
+    uint32_t S, P, L;
+};
+
+/* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */
+__device__ __forceinline__ uint32_t xorshift_step(uint32_t x) {
+    x ^= x << 13;
+    x ^= x >> 17;
+    x ^= x << 5;
+    return x;
+}
+__device__ __forceinline__ float rng_next(uint32_t& s) {
+    s = xorshift_step(s);
+    return (float)s * 9.31322574615478515625e-10f;
+}
+
+/* primitives.cl:14-109: six independent tests, the last match wins; zero counts as negative. */
+__device__ __forceinline__ void cube_uv(V3 d, uint32_t face, int& u, int& v) {
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    bool px = d.x > 0.0f, py = d.y > 0.0f, pz = d.z > 0.0f;
+    float m = 0.0f, uc = 0.0f, vc = 0.0f;
+    uint32_t su = 0, sv = 0;
+    if (px && ax >= ay && ax >= az) { m = ax; uc = -d.z; vc = d.y; su = face * 2; sv = face; }
+    if (!px && ax >= ay && ax >= az) { m = ax; uc = d.z; vc = d.y; sv = face; }
+    if (py && ay >= ax && ay >= az) { m = ay; uc = d.x; vc = -d.z; su = face; sv = face * 2; }
+    if (!py && ay >= ax && ay >= az) { m = ay; uc = d.x; vc = d.z; su = face; }
+    if (pz && az >= ax && az >= ay) { m = az; uc = d.x; vc = d.y; su = face; sv = face; }
+    if (!pz && az >= ax && az >= ay) { m = az; uc = -d.x; vc = d.y; su = face * 3; sv = face; }
+    float fu = 0.5f * (uc / m + 1.0f);
+    float fv = 0.5f * (vc / m + 1.0f);
+    u = f2i_x86((float)su + fu * (float)face);
+    v = f2i_x86((float)sv + fv * (float)face);
+}
+
+/* read_imagei with clamp-to-edge (Q10) + the manual /255.0f of primitives.cl:252-256, raytracing.cl:72-76 */
+__device__ __forceinline__ V3 texel_rgb(const uchar4* base, int w, int h, int layers, int x, int y, int l,
+                                        const float* lut255) {
+    x = clampi(x, w);
+    y = clampi(y, h);
+    l = clampi(l, layers);
+    uchar4 p = __ldg(base + ((size_t)l * h + y) * w + x);
+    return mk(lut255[p.x], lut255[p.y], lut255[p.z]);
+}
+
+/* The 64-byte wire material (types.cl:4-19), read in place with four 16-byte loads. */
+struct Material {
+    V3 rgb;
+    float ambient, diffuse, specular;
+    uint32_t shininess, transperent, dielectric;
+    float n, reflectivity;
+    int texture_id;
+    float texture_scale;
+};
+__device__ __forceinline__ Material load_material(const unsigned char* rec) {
+    const float4* q = reinterpret_cast<const float4*>(rec + RT_MATERIAL_OFFSET);
+    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    Material m;
+    m.rgb = mk(a.x, a.y, a.z);
+    m.ambient = b.x; m.diffuse = b.y; m.specular = b.z; m.shininess = __float_as_uint(b.w);
+    m.transperent = __float_as_uint(c.x); m.dielectric = __float_as_uint(c.y); m.n = c.z; m.reflectivity = c.w;
+    m.texture_id = __float_as_int(d.x); m.texture_scale = d.y;
+    return m;
+}
+
+/* One suspended stack entry (raytracing.cl:28-30 keeps rray + n + f in three arrays). */
+struct Saved {
+    V3 o, d, rgb;
+    int depth;
+    float n, f;
+};
+
+/* raygen.cl:13-24 */
+__device__ __forceinline__ void primary_ray(const RtFrameParams& fp, uint32_t id, V3& o, V3& d) {
+    float w = (float)(id % fp.W);
+    float h = (float)(id / fp.W);
+    V3 corner = mk(fp.corner[0], fp.corner[1], fp.corner[2]);
+    V3 up = mk(fp.up[0], fp.up[1], fp.up[2]);
+    V3 right = mk(fp.right[0], fp.right[1], fp.right[2]);
+    V3 vec = (corner + (right * fp.wf) * w) - (up * fp.hf) * h;
+    d = vec / sqrtf(dot3(vec, vec));
+    o = mk(fp.origin[0], fp.origin[1], fp.origin[2]);
+}
+
+/* Schlick reflectance of primitives.cl:146-160 folded into raytracing.cl:146-150; cosI = -dot(N, I). */
+__device__ __forceinline__ float reflect_amount(const Material& m, float n1, float n2, float cosI) {
+    float refl = m.reflectivity;
+    if (m.dielectric) {
+        float r0 = (n1 - n2) / (n1 + n2);
+        r0 *= r0;
+        float cosX = cosI;
+        float fr;
+        bool tir = false;
+        if (n1 > n2) {
+            float nn = n1 / n2;
+            float sinT2 = nn * nn * (1.0f - cosX * cosX);
+            if (sinT2 > 1.0f) tir = true;
+            else cosX = sqrtf(1.0f - sinT2);
+        }
+        if (tir) fr = 1.0f;
+        else {
+            float x = 1.0f - cosX;
+            fr = r0 + (1.0f - r0) * x * x * x * x * x;
+        }
+        refl = m.reflectivity + (1.0f - m.reflectivity) * fr;
+    }
+    return refl;
+}
+
+/* The refracted child of raytracing.cl:161-179 + refract() of primitives.cl:132-144.
+ * Returns false when the child is dropped (total internal reflection or NaN direction). */
+__device__ __forceinline__ bool refract_child(V3 o, V3 nrm, V3 incident, float n1, float n2, V3& co, V3& cd) {
+    co = o;
+    V3 nn = nrm;
+    if (n1 < n2) co = o - nrm * (2.0f * kEps);
+    else nn = mk(-nrm.x, -nrm.y, -nrm.z);
+    float eta = n1 / n2;
+    float cI = -dot3(nn, incident);
+    float sinT2 = eta * eta * (1.0f - cI * cI);
+    if (sinT2 > 1.0f) return false;
+    float cosT = sqrtf(1.0f - sinT2);
+    cd = incident * eta + nn * (eta * cI - cosT);
+    return !(cd.x != cd.x);
+}
+
+/* ---- TMA bulk copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) ---- */
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+}  // namespace rt

@@ -51,7 +51,7 @@ struct rtb_engine {
     int sm_count = 0;
     size_t smem_optin = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, evk = nullptr, ev1 = nullptr;
     bool timed = false;
 
     DevBuf spheres, planes, lights; /* owned copies of the wire arrays */
@@ -69,6 +69,8 @@ struct rtb_engine {
     bool have_cam = false;
 
     DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
+    DevBuf tile_cost, tile_order, tile_hist;
+    int opt_trace = 0, opt_tile_order = 1;
     rtb_launch_info last{};
 };
 
@@ -98,6 +100,7 @@ int rtb_create(rtb_engine** out, int device) {
     CU(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking), "cudaStreamCreate");
     CU(cudaEventCreate(&e->ev0), "cudaEventCreate");
     CU(cudaEventCreate(&e->ev1), "cudaEventCreate");
+    CU(cudaEventCreate(&e->evk), "cudaEventCreate");
     if (e->sched.ensure(256)) return -2;
     CU(cudaMemset(e->sched.p, 0, 256), "cudaMemset");
     memset(e->cam, 0, sizeof e->cam);
@@ -111,8 +114,10 @@ void rtb_destroy(rtb_engine* e) {
     cudaStreamSynchronize(e->stream);
     e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
+    e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release();
     cudaEventDestroy(e->ev0);
     cudaEventDestroy(e->ev1);
+    cudaEventDestroy(e->evk);
     cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -209,7 +214,7 @@ uint32_t rtb_partition_rows(uint32_t H, const rtb_partition* p) {
 }
 
 static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
-                       uint32_t* d_hit, int want_hit, uint64_t* counters) {
+                       uint32_t* d_hit, int want_hit, int mode, uint64_t* counters) {
     if (!e) return fail(-1, "null engine");
     if (!e->have_scene) return fail(-1, "rtb_render: no scene uploaded");
     if (!e->have_cam) return fail(-1, "rtb_render: no camera set");
@@ -259,10 +264,20 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     e->last.tiles = fp.tiles_x * fp.tiles_y;
     if (rows == 0) { e->timed = false; return 0; }
 
-    CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter");
     CU(cudaEventRecord(e->ev0, e->stream), "event record");
+    CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter");
+    fp.order = nullptr;
+    if (e->opt_tile_order && e->last.tiles >= 4096) { /* small frames: the queue is short enough as it is */
+        const size_t nt = e->last.tiles;
+        if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 4) || e->tile_hist.ensure(1024)) return -2;
+        CU(rt_launch_tile_order(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
+                                e->stream),
+           "tile_order launch");
+        fp.order = (const uint32_t*)e->tile_order.p;
+    }
     RtLaunchShape shape{};
-    CU(rt_launch_render(fp, counters != nullptr, e->sm_count, e->smem_optin, e->stream, &shape), "render_frame launch");
+    CU(cudaEventRecord(e->evk, e->stream), "event record");
+    CU(rt_launch_render(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
     CU(cudaEventRecord(e->ev1, e->stream), "event record");
     e->timed = true;
     e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;
@@ -278,12 +293,31 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
 
 int rtb_render(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
                uint32_t* d_hit, int want_hit) {
-    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, nullptr);
+    if (!e) return fail(-1, "null engine");
+    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, e->opt_trace ? 1 : 0, nullptr);
 }
 int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
-                       uint32_t* d_hit, int want_hit, uint64_t* counters) {
+                       uint32_t* d_hit, int want_hit, int executed, uint64_t* counters) {
     if (!counters) return fail(-1, "rtb_render_counted: null counters");
-    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, counters);
+    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, executed ? 2 : 1, counters);
+}
+
+int rtb_set_option(rtb_engine* e, const char* name, int value) {
+    if (!e || !name) return fail(-1, "rtb_set_option: null argument");
+    if (!strcmp(name, "trace")) { e->opt_trace = value ? 1 : 0; return 0; }
+    if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
+    return fail(-1, "rtb_set_option: unknown option");
+}
+
+int rtb_selftest_arith(rtb_engine* e, uint32_t seed, uint32_t per_thread, uint32_t out[3]) {
+    if (!e || !out) return fail(-1, "rtb_selftest_arith: null argument");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    uint32_t* d = (uint32_t*)((char*)e->sched.p + 128);
+    CU(cudaMemsetAsync(d, 0, 12, e->stream), "memset");
+    CU(rt_launch_arith_selftest(seed, per_thread, d, e->stream), "arith_selftest launch");
+    CU(cudaMemcpyAsync(out, d, 12, cudaMemcpyDeviceToHost, e->stream), "D2H");
+    CU(cudaStreamSynchronize(e->stream), "arith_selftest");
+    return 0;
 }
 
 int rtb_sync(rtb_engine* e) {
@@ -312,6 +346,14 @@ float rtb_last_render_ms(rtb_engine* e) {
     if (cudaEventSynchronize(e->ev1) != cudaSuccess) return -1.0f;
     float ms = -1.0f;
     if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) != cudaSuccess) return -1.0f;
+    return ms;
+}
+float rtb_last_kernel_ms(rtb_engine* e) {
+    if (!e || !e->timed) return -1.0f;
+    if (cudaSetDevice(e->device) != cudaSuccess) return -1.0f;
+    if (cudaEventSynchronize(e->ev1) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventElapsedTime(&ms, e->evk, e->ev1) != cudaSuccess) return -1.0f;
     return ms;
 }
 void* rtb_stream(rtb_engine* e) { return e ? (void*)e->stream : nullptr; }

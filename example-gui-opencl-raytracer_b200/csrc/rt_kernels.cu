@@ -1,491 +1,40 @@
 /* rt_kernels.cu -- the hot path: fused camera-ray generation + Whitted trace + shade + pack, for sm_100a.
  *
  * Behavioural contract = the reference's two OpenCL kernels and their device library
- *   /root/reference/src/cl/raygen.cl:5-25, raytracing.cl:14-195, primitives.cl:14-442, types.cl:4-57
- * (cited below as raygen.cl / raytracing.cl / primitives.cl).  Nothing here is derived from that text
- * line by line; the design is:
- *   - persistent CTAs, one warp = one 8x4 pixel tile at a time, tiles handed out by an atomic counter
- *     (prefetched one tile ahead) so the glass-sphere hot spots do not leave a tail;
- *   - the geometry is first compacted on the device (scene_prep) into 16-byte records and then staged
- *     into shared memory with TMA bulk copies (cp.async.bulk + mbarrier); every intersection test is
- *     one broadcast LDS.128; the 64-byte material is read in place from the wire array, only for the
- *     closest hit;
- *   - the current ray lives in registers, the 14 suspended parents in a per-thread local-memory stack
- *     (touched only on push/pop);
- *   - per-ray invariants of the sphere test (dot(d,d), 4a, 2a, 2d) are hoisted, per-plane texture
- *     bases and per-light colour products are hoisted into scene_prep -- all bit-identical rewrites;
- *   - the frame buffer is written with 128-bit stores after a warp shuffle transpose.
- *
- * Arithmetic contract (must equal oracle/cl_shim.hpp): binary32, round-to-nearest-even, NO
- * contraction -- this file is compiled with -fmad=false -prec-div=true -prec-sqrt=true -ftz=false, so
- * every + - * / sqrt below is one correctly rounded operation in source order.  sinf/cosf/powf are
- * libdevice's (<= 2 ulp) where the oracle uses glibc's: that is the only source of colour
- * differences (tolerance: BASELINE.json).
+ *   /root/reference/src/cl/raygen.cl:5-25, raytracing.cl:14-195, primitives.cl:14-442, types.cl:4-57.
+ * Design (nothing here is a line-by-line translation):
+ *   - scene_prep compacts the wire arrays into 16-byte records once per scene (per-plane texture bases,
+ *     per-light colour products and r*r hoisted out of the per-ray code -- bit-identical rewrites);
+ *   - tile_cost + tile_order: a skeleton trace (no shading) of five rays per 8x4 tile estimates its cost and
+ *     a counting sort orders tiles heaviest-first, so the glass/mirror hot spots do not form a tail;
+ *   - render_frame: persistent CTAs; the record blob is staged into shared memory with TMA bulk copies
+ *     (cp.async.bulk + mbarrier, <= 32 KiB per copy); one warp = one 8x4 tile at a time, tiles pulled from
+ *     an atomic queue (prefetched one tile ahead); every intersection test is one broadcast LDS.128; the
+ *     current ray lives in registers, the 14 suspended parents in a local-memory stack touched only on
+ *     push/pop; the frame buffer is written with 128-bit stores after a warp shuffle transpose.
+ *   - two trace variants produce the same words: rt_trace_literal.cuh (reference control flow, used for
+ *     accounting) and rt_trace_fast.cuh (production).
+ * Compiled with -fmad=false -prec-div=true -prec-sqrt=true -ftz=false (see rt_device.cuh).
  */
 #include "rt_kernels.h"
 
-#include <math_constants.h>
+#include "rt_device.cuh"
+#include "rt_trace_fast.cuh"
+#include "rt_trace_literal.cuh"
 
-#include "../../include/rtb200.h"
-
-namespace {
-
-constexpr float kEps = 0.001f;                        /* primitives.cl:5  EPSILON */
-constexpr float kInvPi = 0.318309886183790671538f;    /* primitives.cl:6  M_1_PI_F */
-constexpr float kGlassPass = 0.8f;                    /* primitives.cl:7  TRANSPERENT_THROUGH */
-constexpr float kAirN = 1.0f;                         /* raytracing.cl:7  DEFAULT_N */
-constexpr int kMaxDepth = 15;                         /* raytracing.cl:9  MAX_DEPTH */
-constexpr int kShadowSamples = 2;                     /* raytracing.cl:10 MAX_SOFT_SHADOWS */
-constexpr int kTileW = 8, kTileH = 4;                 /* one warp */
-constexpr int kBlock = 128;
-
-struct V3 {
-    float x, y, z;
-};
-__device__ __forceinline__ V3 mk(float x, float y, float z) { return V3{x, y, z}; }
-__device__ __forceinline__ V3 xyz(float4 v) { return V3{v.x, v.y, v.z}; }
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
-__device__ __forceinline__ float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
-__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
-    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
-}
-
-/* (int)f with the x86 cvttss2si result for out-of-range / NaN inputs. */
-__device__ __forceinline__ int f2i_x86(float f) {
-    return (f >= -2147483648.0f && f < 2147483648.0f) ? __float2int_rz(f) : (int)0x80000000;
-}
-/* primitives.cl:162-168 */
-__device__ __forceinline__ int emod(int a, int b) {
-    int m = a % b;
-    if (m < 0) m = (b < 0) ? m - b : m + b;
-    return m;
-}
-/* clamp(v, 0, 1) as min(max(v, 0), 1) with max(a,b) = a<b ? b : a, min(a,b) = b<a ? b : a (oracle/cl_shim.hpp) */
-__device__ __forceinline__ float clamp01(float v) {
-    float m = (v < 0.0f) ? 0.0f : v;
-    return (1.0f < m) ? 1.0f : m;
-}
-__device__ __forceinline__ int clampi(int v, int hi) { return v < 0 ? 0 : (v >= hi ? hi - 1 : v); }
-
-/* The ray being traced plus the hoisted sphere-test invariants. */
-struct Ray {
-    V3 o, d;
-    V3 d2;       /* 2*d : dot(2*v, d) == dot(v, 2*d) bit for bit (scaling by 2 is exact) */
-    float a4, a2; /* 4*dot(d,d), 2*dot(d,d)  (primitives.cl:173,179,189) */
-};
-__device__ __forceinline__ void ray_setup(Ray& r, V3 o, V3 d) {
-    r.o = o;
-    r.d = d;
-    float a = dot3(d, d);
-    r.d2 = d * 2.0f;
-    r.a4 = 4.0f * a;
-    r.a2 = 2.0f * a;
-}
-
-template <bool COUNT>
-struct Tally {
-    uint32_t c[RTB_NCOUNTERS];
-    __device__ __forceinline__ void clear() {
-#pragma unroll
-        for (int i = 0; i < RTB_NCOUNTERS; i++) c[i] = 0;
-    }
-    __device__ __forceinline__ void add(int k) { c[k]++; }
-};
-template <>
-struct Tally<false> {
-    __device__ __forceinline__ void clear() {}
-    __device__ __forceinline__ void add(int) {}
-};
-
-/* primitives.cl:170-195 with g = {centre, r*r}.  Comparison forms are kept (NaN behaviour). */
-template <bool COUNT>
-__device__ __forceinline__ bool hit_sphere(const Ray& r, float4 g, float& t, Tally<COUNT>& tl) {
-    tl.add(RTB_SPHERE_TESTS);
-    float vx = r.o.x - g.x, vy = r.o.y - g.y, vz = r.o.z - g.z;
-    float b = (vx * r.d2.x + vy * r.d2.y) + vz * r.d2.z;
-    float c = ((vx * vx + vy * vy) + vz * vz) - g.w;
-    float D = b * b - r.a4 * c;
-    if (D < 0.0f) return false;
-    tl.add(RTB_SPHERE_DPOS);
-    D = sqrtf(D);
-    float nearT = (-b - D) / r.a2;
-    float t2 = (nearT < 0.0f) ? (-b + D) / r.a2 : nearT;
-    if (t2 <= 0.0f) return false;
-    t = t2;
-    return true;
-}
-/* primitives.cl:197-215 */
-template <bool COUNT>
-__device__ __forceinline__ bool hit_plane(const Ray& r, V3 n, V3 p, float& t, Tally<COUNT>& tl) {
-    tl.add(RTB_PLANE_TESTS);
-    float b = dot3(r.d, n);
-    if (b == 0.0f) return false;
-    float t2 = dot3(p - r.o, n) / b;
-    if (t2 <= 0.0f) return false;
-    t = t2;
-    return true;
-}
-
-struct Geo {
-    const float4* sph;
-    const float4* pln;
-    const float4* lit;
-    const uint32_t* flag;
-    uint32_t S, P, L;
-};
-
-/* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */
-__device__ __forceinline__ float rng_next(uint32_t& s) {
-    uint32_t x = s;
-    x ^= x << 13;
-    x ^= x >> 17;
-    x ^= x << 5;
-    s = x;
-    return (float)x * 9.31322574615478515625e-10f;
-}
-
-/* primitives.cl:14-109: six independent tests, the last match wins; zero counts as negative. */
-__device__ __forceinline__ void cube_uv(V3 d, uint32_t face, int& u, int& v) {
-    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-    bool px = d.x > 0.0f, py = d.y > 0.0f, pz = d.z > 0.0f;
-    float m = 0.0f, uc = 0.0f, vc = 0.0f;
-    uint32_t su = 0, sv = 0;
-    if (px && ax >= ay && ax >= az) { m = ax; uc = -d.z; vc = d.y; su = face * 2; sv = face; }
-    if (!px && ax >= ay && ax >= az) { m = ax; uc = d.z; vc = d.y; sv = face; }
-    if (py && ay >= ax && ay >= az) { m = ay; uc = d.x; vc = -d.z; su = face; sv = face * 2; }
-    if (!py && ay >= ax && ay >= az) { m = ay; uc = d.x; vc = d.z; su = face; }
-    if (pz && az >= ax && az >= ay) { m = az; uc = d.x; vc = d.y; su = face; sv = face; }
-    if (!pz && az >= ax && az >= ay) { m = az; uc = -d.x; vc = d.y; su = face * 3; sv = face; }
-    float fu = 0.5f * (uc / m + 1.0f);
-    float fv = 0.5f * (vc / m + 1.0f);
-    u = f2i_x86((float)su + fu * (float)face);
-    v = f2i_x86((float)sv + fv * (float)face);
-}
-
-__device__ __forceinline__ V3 texel_rgb(const uchar4* base, int w, int h, int layers, int x, int y, int l) {
-    x = clampi(x, w);
-    y = clampi(y, h);
-    l = clampi(l, layers);
-    uchar4 p = __ldg(base + ((size_t)l * h + y) * w + x);
-    return mk((float)p.x / 255.0f, (float)p.y / 255.0f, (float)p.z / 255.0f);
-}
-
-/* primitives.cl:396-442: 0 when an opaque sphere or any plane is nearer than the light sample, else
- * 0.8^(transparent spheres crossed). */
-template <bool COUNT>
-__device__ __forceinline__ float shadow_path(V3 to, V3 from, const Geo& g, Tally<COUNT>& tl) {
-    tl.add(RTB_SHADOW_RAYS);
-    V3 diff = to - from;
-    float len = sqrtf(dot3(diff, diff)); /* distance(to, from) and normalize() share it */
-    Ray r;
-    ray_setup(r, from, diff / len);
-    float opacity = 1.0f;
-    for (uint32_t i = 0; i < g.S; i++) {
-        float t1;
-        if (!hit_sphere(r, g.sph[i], t1, tl) || t1 >= len) continue;
-        if (g.flag[i]) { opacity *= kGlassPass; continue; }
-        return 0.0f;
-    }
-    for (uint32_t j = 0; j < g.P; j++) {
-        float t1;
-        if (!hit_plane(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) || t1 >= len) continue;
-        return 0.0f;
-    }
-    return opacity;
-}
-
-/* The 64-byte wire material (types.cl:4-19), read in place with four 16-byte loads. */
-struct Material {
-    V3 rgb;
-    float ambient, diffuse, specular;
-    uint32_t shininess, transperent, dielectric;
-    float n, reflectivity;
-    int texture_id;
-    float texture_scale;
-};
-__device__ __forceinline__ Material load_material(const unsigned char* rec) {
-    const float4* q = reinterpret_cast<const float4*>(rec + RT_MATERIAL_OFFSET);
-    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
-    Material m;
-    m.rgb = mk(a.x, a.y, a.z);
-    m.ambient = b.x; m.diffuse = b.y; m.specular = b.z; m.shininess = __float_as_uint(b.w);
-    m.transperent = __float_as_uint(c.x); m.dielectric = __float_as_uint(c.y); m.n = c.z; m.reflectivity = c.w;
-    m.texture_id = __float_as_int(d.x); m.texture_scale = d.y;
-    return m;
-}
-
-/* One suspended stack entry (raytracing.cl:28-30 keeps rray + n + f in three arrays). */
-struct Saved {
-    V3 o, d, rgb;
-    int depth;
-    float n, f;
-};
-
-template <bool COUNT, bool AOV>
-__device__ __forceinline__ uint32_t trace_pixel(const RtFrameParams& fp, const Geo& g, uint32_t id, uint32_t& hit_id,
-                                                Tally<COUNT>& tl) {
-    Saved st[kMaxDepth - 1];
-    uint32_t rng = id; /* raytracing.cl:32-33 */
-    uint32_t sz = 1;
-
-    /* raygen.cl:13-24 */
-    V3 o, d, rgb = mk(0.0f, 0.0f, 0.0f);
-    {
-        float w = (float)(id % fp.W);
-        float h = (float)(id / fp.W);
-        V3 corner = mk(fp.corner[0], fp.corner[1], fp.corner[2]);
-        V3 up = mk(fp.up[0], fp.up[1], fp.up[2]);
-        V3 right = mk(fp.right[0], fp.right[1], fp.right[2]);
-        V3 vec = (corner + (right * fp.wf) * w) - (up * fp.hf) * h;
-        d = vec / sqrtf(dot3(vec, vec));
-        o = mk(fp.origin[0], fp.origin[1], fp.origin[2]);
-    }
-    int depth = 0;
-    float n_cur = kAirN, f = 1.0f;
-    bool first = true;
-    if (AOV) hit_id = 0;
-
-    for (;;) {
-        if (depth >= kMaxDepth) { /* this entry is finished: fold it into its parent (raytracing.cl:183-190) */
-            if (sz == 1) break;
-            const Saved& p = st[sz - 2];
-            rgb = p.rgb + rgb;
-            o = p.o; d = p.d; depth = p.depth; n_cur = p.n; f = p.f;
-            sz--;
-            continue;
-        }
-        tl.add(RTB_SEGMENTS);
-        Ray r;
-        ray_setup(r, o, d);
-
-        /* ---- findLightIntersection, primitives.cl:262-318 ---- */
-        {
-            float tL = CUDART_INF_F;
-            int k = -1;
-            for (uint32_t i = 0; i < g.L; i++) {
-                float t1;
-                if (!hit_sphere(r, g.lit[2 * i], t1, tl) || t1 >= tL) continue;
-                tL = t1;
-                k = (int)i;
-            }
-            if (k >= 0) {
-                bool blocked = false;
-                for (uint32_t i = 0; i < g.S && !blocked; i++) {
-                    float t1;
-                    if (hit_sphere(r, g.sph[i], t1, tl) && t1 <= tL && !g.flag[i]) blocked = true;
-                }
-                for (uint32_t j = 0; j < g.P && !blocked; j++) {
-                    float t1;
-                    if (hit_plane(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) && t1 <= tL) blocked = true;
-                }
-                if (!blocked) {
-                    V3 ip = o + d * tL;
-                    V3 od = o - ip;
-                    float dd = sqrtf(dot3(od, od));
-                    V3 col = xyz(g.lit[2 * k + 1]) * (1.0f / dd * dd); /* (1/d)*d, primitives.cl:288 */
-                    rgb = rgb + col * f;
-                    if (AOV && first) hit_id = RTB_HIT_LIGHT | (uint32_t)k;
-                    depth = kMaxDepth; /* `break` of raytracing.cl:53 */
-                    first = false;
-                    continue;
-                }
-            }
-        }
-
-        /* ---- findSolidIntersection, primitives.cl:322-394 (strict `_t >= t` rejection) ---- */
-        float t = CUDART_INF_F;
-        int who = -1;
-        for (uint32_t i = 0; i < g.S; i++) {
-            float t1;
-            if (!hit_sphere(r, g.sph[i], t1, tl) || t1 >= t) continue;
-            t = t1;
-            who = (int)i;
-        }
-        int whop = -1;
-        for (uint32_t j = 0; j < g.P; j++) {
-            float t1;
-            if (!hit_plane(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) || t1 >= t) continue;
-            t = t1;
-            whop = (int)j;
-            if (COUNT && __float_as_int(g.pln[4 * j + 3].w) >= 0) tl.add(RTB_TEXELS);
-        }
-
-        if (who < 0 && whop < 0) { /* skybox, raytracing.cl:61-81 */
-            int u, v;
-            cube_uv(d, (uint32_t)(fp.sw / 4), u, v);
-            tl.add(RTB_TEXELS);
-            V3 px = texel_rgb(fp.sky, fp.sw, fp.sh, 1, u, fp.sh - v, 0);
-            rgb = rgb + px * f;
-            depth = kMaxDepth;
-            first = false;
-            continue;
-        }
-
-        V3 ip = o + d * t, nrm;
-        Material m;
-        if (whop >= 0) {
-            nrm = xyz(g.pln[4 * whop]);
-            m = load_material(fp.raw_planes + (size_t)whop * RT_PLANE_BYTES);
-            if (m.texture_id >= 0) { /* primitives.cl:217-259 with the per-plane basis from scene_prep */
-                float4 b0 = g.pln[4 * whop + 2], b1 = g.pln[4 * whop + 3];
-                float ui = dot3(xyz(b0), ip) * m.texture_scale;
-                float vi = dot3(xyz(b1), ip) * m.texture_scale;
-                m.rgb = texel_rgb(fp.tex, fp.tw, fp.th, fp.tl, emod(f2i_x86(ui), fp.tw), emod(f2i_x86(vi), fp.th),
-                                  m.texture_id);
-            }
-            if (AOV && first) hit_id = 1u + g.S + (uint32_t)whop;
-        } else {
-            V3 c = xyz(g.sph[who]);
-            V3 q = ip - c;
-            nrm = q / sqrtf(dot3(q, q));
-            m = load_material(fp.raw_spheres + (size_t)who * RT_SPHERE_BYTES);
-            if (AOV && first) hit_id = 1u + (uint32_t)who;
-        }
-        first = false;
-        ip = ip + nrm * kEps;
-
-        rgb = rgb + (m.rgb * f) * m.ambient; /* raytracing.cl:83-84 */
-
-        /* ---- direct light, raytracing.cl:87-136 ---- */
-        {
-            V3 vq = o - ip;
-            V3 vv = vq / sqrtf(dot3(vq, vq));
-            float shin = (float)m.shininess;
-            float fs = f * m.specular, fd = f * m.diffuse;
-            for (uint32_t i = 0; i < g.L; i++) {
-                float4 l0 = g.lit[2 * i], l1 = g.lit[2 * i + 1];
-                V3 lo = xyz(l0);
-                float radius = l1.w;
-                V3 ld = lo - ip;
-                float dist = sqrtf(dot3(ld, ld));
-                V3 sdir = ld / dist;
-                float soft = 0.0f;
-#pragma unroll 1
-                for (int j = 0; j < kShadowSamples; j++) {
-                    float theta = (float)(6.283185307179586476925286766559 * (double)rng_next(rng));
-                    float phi = (float)(3.14159265358979323846264338327950288 * (double)rng_next(rng));
-                    float sp, cp, sth, cth;
-                    sincosf(phi, &sp, &cp);
-                    sincosf(theta, &sth, &cth);
-                    float rs = radius * sp;
-                    V3 sample = lo + mk(rs * cth, rs * sth, radius * cp);
-                    soft += shadow_path(sample, ip, g, tl);
-                }
-                float ssr = soft / (float)kShadowSamples;
-                V3 lrgb = ((xyz(l1) * 1.0f) / (dist * dist)) * ssr;
-                V3 hq = vv + sdir;
-                V3 hh = hq / sqrtf(dot3(hq, hq));
-                float ndh = dot3(nrm, hh);
-                float spec = powf(0.0f < ndh ? ndh : 0.0f, shin);
-                rgb = rgb + (lrgb * fs) * spec;
-                float ndl = dot3(nrm, sdir);
-                float diff = 0.0f < ndl ? ndl : 0.0f;
-                rgb = rgb + (lrgb * fd) * diff;
-            }
-        }
-
-        /* ---- Fresnel, reflection, refraction child (raytracing.cl:138-179) ---- */
-        V3 incident = d;
-        float n1 = n_cur;
-        float n2 = (n1 == kAirN) ? m.n : kAirN;
-        float cosI = -dot3(nrm, incident);
-        float refl = m.reflectivity;
-        if (m.dielectric) { /* primitives.cl:146-160 */
-            float r0 = (n1 - n2) / (n1 + n2);
-            r0 *= r0;
-            float cosX = cosI;
-            float fr;
-            bool tir = false;
-            if (n1 > n2) {
-                float nn = n1 / n2;
-                float sinT2 = nn * nn * (1.0f - cosX * cosX);
-                if (sinT2 > 1.0f) tir = true;
-                else cosX = sqrtf(1.0f - sinT2);
-            }
-            if (tir) fr = 1.0f;
-            else {
-                float x = 1.0f - cosX;
-                fr = r0 + (1.0f - r0) * x * x * x * x * x;
-            }
-            refl = m.reflectivity + (1.0f - m.reflectivity) * fr;
-        }
-        float old_f = f;
-        f *= refl;
-        d = incident + nrm * (2.0f * cosI); /* primitives.cl:127-130 */
-        o = ip;
-        depth++;
-
-        if (m.transperent && sz < (uint32_t)kMaxDepth && refl < 1.0f) {
-            V3 co = o;
-            V3 nn = nrm;
-            if (n1 < n2) co = o - nrm * (2.0f * kEps);
-            else nn = mk(-nrm.x, -nrm.y, -nrm.z);
-            /* primitives.cl:132-144 */
-            float eta = n1 / n2;
-            float cI = -dot3(nn, incident);
-            float sinT2 = eta * eta * (1.0f - cI * cI);
-            if (!(sinT2 > 1.0f)) {
-                float cosT = sqrtf(1.0f - sinT2);
-                V3 cd = incident * eta + nn * (eta * cI - cosT);
-                if (!(cd.x != cd.x)) { /* isnan(dir.x) also drops the child, raytracing.cl:174 */
-                    Saved& p = st[sz - 1];
-                    p.o = o; p.d = d; p.rgb = rgb; p.depth = depth; p.n = n_cur; p.f = f;
-                    sz++;
-                    o = co; d = cd; rgb = mk(0.0f, 0.0f, 0.0f);
-                    f = old_f * (1.0f - refl);
-                    n_cur = n2;
-                    /* depth: the child starts at the parent's incremented depth (raytracing.cl:159,163) */
-                }
-            }
-        }
-    }
-
-    /* raytracing.cl:193-194 */
-    float cr = clamp01(rgb.x) * 255.0f;
-    float cg = clamp01(rgb.y) * 255.0f;
-    float cb = clamp01(rgb.z) * 255.0f;
-    return ((uint32_t)cr << 16) | ((uint32_t)cg << 8) | (uint32_t)cb;
-}
-
-/* ---- TMA bulk copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) ---- */
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
+namespace rt {
 
 extern __shared__ __align__(128) unsigned char rt_smem[];
 
-template <bool RESIDENT, bool COUNT, bool AOV>
+/* MODE: 0 = fast, 1 = literal + counters (reference accounting), 2 = fast + counters (executed work) */
+template <bool RESIDENT, int MODE, bool AOV>
 __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ RtFrameParams fp) {
+    constexpr bool COUNT = MODE != 0;
     __shared__ __align__(8) uint64_t bar;
+    __shared__ float lut255[256];
     Geo g;
     g.S = fp.S; g.P = fp.P; g.L = fp.L;
+    g.lut255 = lut255;
     if (RESIDENT) {
         const uint32_t bytes = fp.lay.total * 16u;
         if (threadIdx.x == 0) mbar_init(&bar, 1);
@@ -498,6 +47,9 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
                 tma_bulk_g2s(rt_smem + off, reinterpret_cast<const unsigned char*>(fp.blob) + off, nb, &bar);
             }
         }
+    }
+    for (uint32_t i = threadIdx.x; i < 256u; i += kBlock) lut255[i] = (float)i / 255.0f; /* overlaps the copy */
+    if (RESIDENT) {
         mbar_wait(&bar, 0);
         const float4* base = reinterpret_cast<const float4*>(rt_smem);
         g.sph = base + fp.lay.sph_off;
@@ -510,6 +62,7 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
         g.lit = fp.blob + fp.lay.lit_off;
         g.flag = reinterpret_cast<const uint32_t*>(fp.blob + fp.lay.flag_off);
     }
+    __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
@@ -520,9 +73,10 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
     uint32_t next = 0;
     if (lane == 0) next = atomicAdd(fp.tile_counter, 1u);
     for (;;) {
-        const uint32_t tile = __shfl_sync(0xffffffffu, next, 0);
-        if (tile >= ntiles) break;
+        const uint32_t slot = __shfl_sync(0xffffffffu, next, 0);
+        if (slot >= ntiles) break;
         if (lane == 0) next = atomicAdd(fp.tile_counter, 1u); /* prefetch: latency hides behind this tile */
+        const uint32_t tile = fp.order ? __ldg(fp.order + slot) : slot;
 
         const uint32_t tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
         const uint32_t x = tx * kTileW + (lane & 7u);
@@ -532,7 +86,10 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
         const bool live = x < fp.W && lr < fp.local_rows && y < fp.H && id < fp.total;
 
         uint32_t word = 0, hid = 0;
-        if (live) word = trace_pixel<COUNT, AOV>(fp, g, id, hid, tl);
+        if (live) {
+            if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);
+            else word = trace_pixel_fast<COUNT, AOV>(fp, g, id, hid, tl);
+        }
         __syncwarp();
 
         const size_t at = (size_t)lr * fp.W + x;
@@ -545,9 +102,8 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
                 if (live3) *reinterpret_cast<uint4*>(fp.out + at) = make_uint4(word, w1, w2, w3);
                 else { /* id >= total inside this quad: scalar tail */
                     fp.out[at] = word;
-                    uint32_t l1 = y * fp.W + x + 1 < fp.total, l2 = y * fp.W + x + 2 < fp.total;
-                    if (l1) fp.out[at + 1] = w1;
-                    if (l2) fp.out[at + 2] = w2;
+                    if (id + 1 < fp.total) fp.out[at + 1] = w1;
+                    if (id + 2 < fp.total) fp.out[at + 2] = w2;
                 }
             }
             if (AOV && fp.hit) {
@@ -558,8 +114,8 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
                     if (live3) *reinterpret_cast<uint4*>(fp.hit + at) = make_uint4(hid, h1, h2, h3);
                     else {
                         fp.hit[at] = hid;
-                        if (y * fp.W + x + 1 < fp.total) fp.hit[at + 1] = h1;
-                        if (y * fp.W + x + 2 < fp.total) fp.hit[at + 2] = h2;
+                        if (id + 1 < fp.total) fp.hit[at + 1] = h1;
+                        if (id + 2 < fp.total) fp.hit[at + 2] = h2;
                     }
                 }
             }
@@ -572,9 +128,7 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
     if (COUNT) {
 #pragma unroll
         for (int k = 0; k < RTB_NCOUNTERS; k++) {
-            uint32_t v = 0;
-            if (COUNT) v = reinterpret_cast<const uint32_t*>(&tl)[k];
-            unsigned long long s = v;
+            unsigned long long s = tl.get(k);
             for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
             if (lane == 0 && s) atomicAdd(fp.counters + k, s);
         }
@@ -611,8 +165,8 @@ __global__ void scene_prep(const unsigned char* __restrict__ spheres, uint32_t S
         float4* out = blob + lay.pln_off + 4 * i;
         out[0] = make_float4(n.x, n.y, n.z, 0.0f);
         out[1] = make_float4(p4.x, p4.y, p4.z, 0.0f);
-        out[2] = make_float4(b0.x, b0.y, b0.z, m3.y);  /* texture_scale */
-        out[3] = make_float4(b1.x, b1.y, b1.z, m3.x);  /* texture_id bits */
+        out[2] = make_float4(b0.x, b0.y, b0.z, m3.y); /* texture_scale */
+        out[3] = make_float4(b1.x, b1.y, b1.z, m3.x); /* texture_id bits */
     }
     if (i < L) {
         const float4* q = reinterpret_cast<const float4*>(lights + (size_t)i * RT_LIGHT_BYTES);
@@ -624,6 +178,107 @@ __global__ void scene_prep(const unsigned char* __restrict__ spheres, uint32_t S
         out[1] = make_float4(pre.x, pre.y, pre.z, radius);
     }
     if (i == 0 && S + P + L == 0) blob[0] = make_float4(0, 0, 0, 0);
+}
+
+/* ---- tile_cost: skeleton trace of five rays per tile (scheduling hint only; cannot change any pixel) ---- */
+constexpr uint32_t kCostBuckets = 64;
+
+__device__ uint32_t skeleton_cost(const RtFrameParams& fp, const Geo& g, uint32_t id) {
+    V3 o, d;
+    primary_ray(fp, id, o, d);
+    Tally<false> tl;
+    uint32_t cost = 0;
+    float n_cur = kAirN;
+    for (int depth = 0; depth < kMaxDepth && cost < kCostBuckets; depth++) {
+        RayF r;
+        ray_setup_fast(r, o, d);
+        float t = CUDART_INF_F;
+        int who = -1, whop = -1;
+        for_sphere_hits(r, g.sph, 1, g.S, tl, [&](uint32_t i, float t1) {
+            if (!(t1 >= t)) { t = t1; who = (int)i; }
+            return false;
+        });
+        for (uint32_t j = 0; j < g.P; j++) {
+            float t1;
+            if (!hit_plane_fast(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) || t1 >= t) continue;
+            t = t1;
+            whop = (int)j;
+        }
+        if (who < 0 && whop < 0) break;
+        V3 ip = o + d * t, nrm;
+        Material m;
+        if (whop >= 0) {
+            nrm = xyz(g.pln[4 * whop]);
+            m = load_material(fp.raw_planes + (size_t)whop * RT_PLANE_BYTES);
+        } else {
+            float ql;
+            nrm = normalize_len(ip - xyz(g.sph[who]), ql);
+            m = load_material(fp.raw_spheres + (size_t)who * RT_SPHERE_BYTES);
+        }
+        const bool shaded = (m.diffuse != 0.0f) || (m.specular != 0.0f);
+        cost += shaded ? 4u : 1u;
+        if (m.transperent) cost += 12u; /* a refraction subtree hangs off this hit */
+        ip = ip + nrm * kEps;
+        float cosI = -dot3(nrm, d);
+        float n2 = (n_cur == kAirN) ? m.n : kAirN;
+        (void)n2;
+        d = d + nrm * (2.0f * cosI);
+        o = ip;
+    }
+    return cost < kCostBuckets ? cost : kCostBuckets - 1u;
+}
+
+__global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __restrict__ cost_out,
+                          uint32_t* __restrict__ hist) {
+    __shared__ float lut255[256];
+    __shared__ uint32_t shist[kCostBuckets];
+    for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
+    __syncthreads();
+    Geo g;
+    g.S = fp.S; g.P = fp.P; g.L = fp.L;
+    g.lut255 = lut255;
+    g.sph = fp.blob + fp.lay.sph_off;
+    g.pln = fp.blob + fp.lay.pln_off;
+    g.lit = fp.blob + fp.lay.lit_off;
+    g.flag = reinterpret_cast<const uint32_t*>(fp.blob + fp.lay.flag_off);
+    const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile < ntiles) {
+        const uint32_t tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
+        const uint32_t px[5] = {0, kTileW - 1, 0, kTileW - 1, kTileW / 2};
+        const uint32_t py[5] = {0, 0, kTileH - 1, kTileH - 1, kTileH / 2};
+        uint32_t cost = 0;
+        for (int s = 0; s < 5; s++) {
+            uint32_t x = tx * kTileW + px[s], lr = ty * kTileH + py[s];
+            if (x >= fp.W) x = fp.W - 1;
+            if (lr >= fp.local_rows) lr = fp.local_rows - 1;
+            const uint32_t y = ((lr / fp.band_rows) * fp.parts + fp.part) * fp.band_rows + lr % fp.band_rows;
+            if (y >= fp.H) continue;
+            uint32_t c = skeleton_cost(fp, g, y * fp.W + x);
+            cost = c > cost ? c : cost;
+        }
+        cost_out[tile] = cost;
+        atomicAdd(&shist[cost], 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
+        if (shist[i]) atomicAdd(&hist[i], shist[i]);
+}
+
+/* counting sort, heaviest bucket first; order within a bucket is arbitrary (it cannot affect any pixel) */
+__global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __restrict__ hist,
+                           uint32_t* __restrict__ cursor, uint32_t* __restrict__ order, uint32_t ntiles) {
+    __shared__ uint32_t base[kCostBuckets];
+    if (threadIdx.x == 0) {
+        uint32_t acc = 0;
+        for (int b = (int)kCostBuckets - 1; b >= 0; b--) { base[b] = acc; acc += hist[b]; }
+    }
+    __syncthreads();
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile < ntiles) {
+        const uint32_t c = cost[tile];
+        order[base[c] + atomicAdd(&cursor[c], 1u)] = tile;
+    }
 }
 
 /* FP32 pipe calibration: 8 independent FMA chains per thread. */
@@ -642,24 +297,87 @@ __global__ void fma_peak(float* sink, int iters) {
     if (s == 123.456f) sink[0] = s;
 }
 
-template <bool R, bool C, bool A>
+/* Arithmetic self-test: the shared-reciprocal division / fast normalize / bounded sincos against the IEEE
+ * operators, on pseudo-random operands.  out[0] += mismatching divisions, out[1] += mismatching normalize
+ * components or lengths, out[2] = max |sincos_bounded - sincosf| in units of 2^-24 (as uint). */
+__global__ void arith_selftest(uint32_t seed, uint32_t per_thread, uint32_t* out) {
+    uint32_t s = seed ^ (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u;
+    if (s == 0) s = 1;
+    uint32_t bad_div = 0, bad_nrm = 0, worst = 0;
+    for (uint32_t it = 0; it < per_thread; it++) {
+        /* operands with exponents spread over [2^-40, 2^40] and full random mantissas */
+        float v[4];
+        for (int k = 0; k < 4; k++) {
+            s = xorshift_step(s);
+            uint32_t mant = s & 0x007fffffu, sign = s & 0x80000000u;
+            s = xorshift_step(s);
+            uint32_t e = 127u - 40u + (s % 81u);
+            if ((it & 7u) == 0u) e = 127u - 2u + (s % 5u); /* a share of near-unit operands, as in the renderer */
+            v[k] = __uint_as_float(sign | (e << 23) | mant);
+        }
+        const float b = v[3];
+        if (div_guard(b)) {
+            float r = refine_rcp(b);
+            for (int k = 0; k < 3; k++)
+                if (div_guard(v[k]) && __float_as_uint(div_with_rcp(v[k], b, r)) != __float_as_uint(v[k] / b)) bad_div++;
+        }
+        float len;
+        V3 q = normalize_len(mk(v[0], v[1], v[2]), len);
+        float dd = dot3(mk(v[0], v[1], v[2]), mk(v[0], v[1], v[2]));
+        float len_ref = sqrtf(dd);
+        if (__float_as_uint(len) != __float_as_uint(len_ref)) bad_nrm++;
+        if (__float_as_uint(q.x) != __float_as_uint(v[0] / len_ref)) bad_nrm++;
+        if (__float_as_uint(q.y) != __float_as_uint(v[1] / len_ref)) bad_nrm++;
+        if (__float_as_uint(q.z) != __float_as_uint(v[2] / len_ref)) bad_nrm++;
+        /* sampling angles: u in [0, 4] exactly as the renderer forms them */
+        s = xorshift_step(s);
+        float u = (float)s * 9.31322574615478515625e-10f;
+        float ang = (float)(kTwoPi * (double)u);
+        float ss, cc, rs, rc;
+        sincos_bounded(ang, ss, cc);
+        sincosf(ang, &rs, &rc);
+        float e1 = fabsf(ss - rs) * 16777216.0f, e2 = fabsf(cc - rc) * 16777216.0f;
+        uint32_t w = (uint32_t)(e1 > e2 ? e1 : e2);
+        worst = w > worst ? w : worst;
+    }
+    if (bad_div) atomicAdd(out + 0, bad_div);
+    if (bad_nrm) atomicAdd(out + 1, bad_nrm);
+    atomicMax(out + 2, worst);
+}
+
+template <bool R, int M, bool A>
 cudaError_t launch_variant(const RtFrameParams& fp, uint32_t grid, uint32_t smem, cudaStream_t st) {
-    render_frame<R, C, A><<<grid, kBlock, smem, st>>>(fp);
+    render_frame<R, M, A><<<grid, kBlock, smem, st>>>(fp);
     return cudaGetLastError();
 }
-template <bool R, bool C, bool A>
-cudaError_t prep_variant(size_t smem_optin, int* blocks_per_sm, uint32_t smem) {
-    (void)smem_optin;
+template <bool R, int M, bool A>
+cudaError_t prep_variant(int* blocks_per_sm, uint32_t smem) {
     if (smem > 48u * 1024u) {
-        cudaError_t e = cudaFuncSetAttribute(render_frame<R, C, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(render_frame<R, M, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_frame<R, C, A>, kBlock, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_frame<R, M, A>, kBlock, smem);
 }
 
-}  // namespace
+template <bool R, int M, bool A>
+cudaError_t go(const RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, RtLaunchShape* shape) {
+    int bps = 0;
+    cudaError_t e = prep_variant<R, M, A>(&bps, smem);
+    if (e != cudaSuccess) return e;
+    if (bps < 1) bps = 1;
+    const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
+    const uint32_t warps_per_cta = kBlock / 32;
+    uint32_t grid = (uint32_t)sm_count * (uint32_t)bps; /* persistent: every resident slot filled exactly once */
+    const uint32_t need = (ntiles + warps_per_cta - 1) / warps_per_cta;
+    if (grid > need) grid = need;
+    if (grid == 0) grid = 1;
+    if (shape) { shape->grid = grid; shape->block = kBlock; shape->smem_bytes = smem; shape->resident = R; }
+    return launch_variant<R, M, A>(fp, grid, smem, st);
+}
 
-cudaError_t rt_render_init(void) { return cudaSuccess; }
+}  // namespace rt
+
+using namespace rt;
 
 cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, const unsigned char* d_planes, uint32_t P,
                                  const unsigned char* d_lights, uint32_t L, float4* d_blob, RtBlobLayout lay,
@@ -671,45 +389,42 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
     return cudaGetLastError();
 }
 
-cudaError_t rt_launch_render(const RtFrameParams& fp, bool counted, int sm_count, size_t smem_optin, cudaStream_t st,
-                             RtLaunchShape* shape) {
+cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
+                                 cudaStream_t st) {
+    const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
+    cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, 2 * kCostBuckets * sizeof(uint32_t), st);
+    if (e != cudaSuccess) return e;
+    const uint32_t blocks = (ntiles + 127) / 128;
+    tile_cost<<<blocks, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    tile_order<<<blocks, 128, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles);
+    return cudaGetLastError();
+}
+
+cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape) {
     const uint32_t blob_bytes = fp.lay.total * 16u;
     /* keep the geometry resident while it leaves room for >= 2 CTAs per SM */
     const bool resident = blob_bytes <= 96u * 1024u;
     const uint32_t smem = resident ? blob_bytes : 0u;
     const bool aov = fp.hit != nullptr;
-    int bps = 0;
-    cudaError_t e;
-#define RT_DISPATCH(R, C, A)                                            \
-    do {                                                                \
-        e = prep_variant<R, C, A>(smem_optin, &bps, smem);              \
-        if (e != cudaSuccess) return e;                                 \
-    } while (0)
-    if (resident) {
-        if (counted) { if (aov) RT_DISPATCH(true, true, true); else RT_DISPATCH(true, true, false); }
-        else { if (aov) RT_DISPATCH(true, false, true); else RT_DISPATCH(true, false, false); }
-    } else {
-        if (counted) { if (aov) RT_DISPATCH(false, true, true); else RT_DISPATCH(false, true, false); }
-        else { if (aov) RT_DISPATCH(false, false, true); else RT_DISPATCH(false, false, false); }
-    }
-#undef RT_DISPATCH
-    if (bps < 1) bps = 1;
-    const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
-    const uint32_t warps_per_cta = kBlock / 32;
-    uint32_t grid = (uint32_t)sm_count * (uint32_t)bps; /* persistent: every resident slot filled exactly once */
-    const uint32_t need = (ntiles + warps_per_cta - 1) / warps_per_cta;
-    if (grid > need) grid = need;
-    if (grid == 0) grid = 1;
-    if (shape) { shape->grid = grid; shape->block = kBlock; shape->smem_bytes = smem; shape->resident = resident; }
-    if (resident) {
-        if (counted) return aov ? launch_variant<true, true, true>(fp, grid, smem, st) : launch_variant<true, true, false>(fp, grid, smem, st);
-        return aov ? launch_variant<true, false, true>(fp, grid, smem, st) : launch_variant<true, false, false>(fp, grid, smem, st);
-    }
-    if (counted) return aov ? launch_variant<false, true, true>(fp, grid, smem, st) : launch_variant<false, true, false>(fp, grid, smem, st);
-    return aov ? launch_variant<false, false, true>(fp, grid, smem, st) : launch_variant<false, false, false>(fp, grid, smem, st);
+#define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape)
+#define RT_GO_A(R, M) do { if (aov) RT_GO(R, M, true); else RT_GO(R, M, false); } while (0)
+#define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else RT_GO_A(R, 2); } while (0)
+    if (resident) RT_GO_M(true);
+    else RT_GO_M(false);
+#undef RT_GO
+#undef RT_GO_A
+#undef RT_GO_M
+    return cudaErrorInvalidValue;
 }
 
 cudaError_t rt_launch_fma_peak(float* d_sink, int iters, int blocks, int threads, cudaStream_t st) {
     fma_peak<<<blocks, threads, 0, st>>>(d_sink, iters);
+    return cudaGetLastError();
+}
+
+cudaError_t rt_launch_arith_selftest(uint32_t seed, uint32_t per_thread, uint32_t* d_out, cudaStream_t st) {
+    arith_selftest<<<148 * 4, 256, 0, st>>>(seed, per_thread, d_out);
     return cudaGetLastError();
 }

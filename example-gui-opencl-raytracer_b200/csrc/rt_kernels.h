@@ -51,6 +51,7 @@ struct RtFrameParams {
     uint32_t* hit; /* may be NULL */
     /* scheduling */
     unsigned int* tile_counter; /* zeroed before launch */
+    const uint32_t* order;      /* queue slot -> tile (heaviest first), or NULL for row-major order */
     uint32_t tiles_x, tiles_y;
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
 };
@@ -63,10 +64,14 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
 struct RtLaunchShape {
     uint32_t grid, block, smem_bytes, resident;
 };
-/* Chooses the variant (geometry resident in shared memory or read through L1/L2; counted or not; AOV or not)
- * and launches the fused raygen+raytracer kernel. */
-cudaError_t rt_launch_render(const RtFrameParams& fp, bool counted, int sm_count, size_t smem_optin,
-                             cudaStream_t st, RtLaunchShape* shape);
-cudaError_t rt_render_init(void); /* one-time function attribute setup */
+/* Launches the fused raygen+raytracer kernel.  mode: 0 = fast trace, 1 = literal trace + reference work
+ * counters, 2 = fast trace + executed-work counters.  Geometry is staged in shared memory when it fits. */
+cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
+
+/* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[128] (zeroed here), d_order[ntiles]. */
+cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
+                                 cudaStream_t st);
 
 cudaError_t rt_launch_fma_peak(float* d_sink, int iters, int blocks, int threads, cudaStream_t st);
+/* d_out[3] (zeroed by the caller): division mismatches, normalize mismatches, max sincos deviation in 2^-24 units */
+cudaError_t rt_launch_arith_selftest(uint32_t seed, uint32_t per_thread, uint32_t* d_out, cudaStream_t st);

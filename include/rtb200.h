@@ -36,6 +36,7 @@ enum {
     RTB_SPHERE_DPOS = 3,  /* ... of which had D >= 0 */
     RTB_PLANE_TESTS = 4,  /* intersect_plane calls, primitives.cl:197 */
     RTB_TEXELS = 5,       /* texel fetches the reference would make (primitives.cl:250, raytracing.cl:70) */
+    RTB_SHADOW_SKIPPED = 6, /* executed-work accounting only: shadow rays elided because their light term is exactly 0 */
     RTB_NCOUNTERS = 8
 };
 
@@ -84,9 +85,19 @@ uint32_t rtb_partition_rows(uint32_t H, const rtb_partition* p);
 int rtb_render(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
                uint32_t* d_hit, int want_hit);
 /* Same launch with work counters (slower, for accounting only). counters[RTB_NCOUNTERS] is host memory;
- * the call synchronises. */
+ * the call synchronises.  executed = 0: the literal trace, whose counts are the reference's own control
+ * flow (the definition of "rays" and algorithmic flop); executed = 1: the production
+ * trace, counting the work it really does (batched tests, elided shadow rays). */
 int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part,
-                       uint32_t* d_out, uint32_t* d_hit, int want_hit, uint64_t* counters);
+                       uint32_t* d_out, uint32_t* d_hit, int want_hit, int executed, uint64_t* counters);
+
+/* Engine options.  "trace": 0 = production trace (default), 1 = literal trace (reference control flow; same
+ * pixels, slower).  "tile_order": 1 = cost-ordered tile queue (default), 0 = row-major queue. */
+int rtb_set_option(rtb_engine* e, const char* name, int value);
+/* Brute-force check of the arithmetic routines against IEEE division / sqrt (trials per thread on 592x256
+ * threads).  out[0] = division mismatches, out[1] = normalize mismatches, out[2] = max |sincos - libdevice|
+ * in units of 2^-24. */
+int rtb_selftest_arith(rtb_engine* e, uint32_t seed, uint32_t per_thread, uint32_t out[3]);
 
 /* Wait for the engine's stream. */
 int rtb_sync(rtb_engine* e);
@@ -100,6 +111,8 @@ uint32_t* rtb_hit_ptr(rtb_engine* e);
 /* Device time of the last render launch in milliseconds (CUDA events on the engine's stream;
  * synchronises).  Negative on error. */
 float rtb_last_render_ms(rtb_engine* e);
+/* Same, for the render_frame kernel alone (without the tile-ordering pre-pass). */
+float rtb_last_kernel_ms(rtb_engine* e);
 /* The engine's CUDA stream as a cudaStream_t cast to void* (for callers that enqueue their own
  * work, e.g. a collective, behind the render). */
 void* rtb_stream(rtb_engine* e);

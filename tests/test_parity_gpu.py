@@ -81,3 +81,47 @@ def test_total_size_guard(engine, ref):
     part = engine.read_frame(W * H)
     assert np.array_equal(part[:total], full[:total])
     assert np.array_equal(part[total:], full[total:])  # untouched pixels keep the previous frame
+
+
+def test_arithmetic_selftest(engine):
+    """Shared-reciprocal division and the fast normalize must equal IEEE / and sqrtf on every trial."""
+    r = engine.selftest_arith(seed=12345, per_thread=4000)   # 592*256*4000 = 6e8 operand sets
+    print(r)
+    assert r["div_mismatch"] == 0
+    assert r["normalize_mismatch"] == 0
+    assert r["sincos_max_dev_2p24"] <= 4
+
+
+@pytest.mark.parametrize("W,H", [(640, 360), (203, 97)])
+def test_fast_trace_equals_literal_trace(engine, ref, W, H):
+    """The production trace and the reference-control-flow trace must agree on every word."""
+    engine.set_camera(ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA))
+    engine.set_option("trace", 1)
+    lit, lit_hit = engine.render_to_host(W, H, want_hit=True)
+    engine.set_option("trace", 0)
+    fast, fast_hit = engine.render_to_host(W, H, want_hit=True)
+    assert np.array_equal(lit_hit, fast_hit)
+    same = float((lit == fast).mean())
+    print("fast == literal on %.6f of pixels" % same)
+    c = ref.compare_frames(fast, lit, W, H)
+    assert c["within1"] >= 0.9999 and same >= 0.999   # the only non-identical routine is sincos (R6)
+
+
+def test_tile_order_does_not_change_pixels(engine, ref):
+    W, H = 1024, 512   # >= 4096 tiles, so the cost-ordered queue is active
+    engine.set_camera(ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA))
+    a, _ = engine.render_to_host(W, H, want_hit=False)
+    engine.set_option("tile_order", 0)
+    b, _ = engine.render_to_host(W, H, want_hit=False)
+    engine.set_option("tile_order", 1)
+    assert np.array_equal(a, b)
+
+
+def test_executed_counters_are_consistent(engine, ref):
+    W, H = 400, 300
+    engine.set_camera(ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA))
+    lit = engine.render_counted(W, H, executed=False)
+    fast = engine.render_counted(W, H, executed=True)
+    print(lit, fast)
+    assert fast["segments"] == lit["segments"]
+    assert fast["shadow_rays"] + fast["shadow_skipped"] == lit["shadow_rays"]
