@@ -317,7 +317,7 @@ def run_gpu_arm(args):
             for _ in range(min(args.steps, 10)):
                 flush.fill_(1)
                 eng.render(W, H, part=part, d_out=band_buf.data_ptr())
-                kernel_ms.append(eng.last_render_ms())
+                kernel_ms.append(eng.last_kernel_ms())
     clocks = clk.summary()
 
     # ---- end to end through the public API with host buffers ----

@@ -83,13 +83,24 @@ struct Tally<false> {
 
 /* Geometry records (rt_kernels.h: RtBlobLayout), in shared memory when resident. */
 struct Geo {
-    const float4* sph;
-    const float4* pln;
-    const float4* lit;
+    const float4* lgeo;  /* [Lpad] light {o, r*r}; the sphere records follow directly: sph == lgeo + Lpad */
+    const float4* sph;   /* [Spad] sphere {c, r*r} */
+    const float4* laux;  /* [L] {premultiplied rgb, radius} */
+    const float4* pln;   /* [4P] */
     const uint32_t* flag;
     const float* lut255; /* i / 255.0f for i in 0..255 (IEEE division, filled once per CTA) */
-    uint32_t S, P, L;
+    uint32_t S, P, L, Spad, Lpad;
 };
+__device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFrameParams& fp, const float* lut) {
+    g.S = fp.S; g.P = fp.P; g.L = fp.L;
+    g.Spad = fp.lay.Spad; g.Lpad = fp.lay.Lpad;
+    g.lgeo = base + fp.lay.geo_off;
+    g.sph = g.lgeo + fp.lay.Lpad;
+    g.laux = base + fp.lay.laux_off;
+    g.pln = base + fp.lay.pln_off;
+    g.flag = reinterpret_cast<const uint32_t*>(base + fp.lay.flag_off);
+    g.lut255 = lut;
+}
 
 /* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */
 __device__ __forceinline__ uint32_t xorshift_step(uint32_t x) {

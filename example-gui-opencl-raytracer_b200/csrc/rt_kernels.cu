@@ -33,8 +33,6 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
     Geo g;
-    g.S = fp.S; g.P = fp.P; g.L = fp.L;
-    g.lut255 = lut255;
     if (RESIDENT) {
         const uint32_t bytes = fp.lay.total * 16u;
         if (threadIdx.x == 0) mbar_init(&bar, 1);
@@ -51,16 +49,9 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
     for (uint32_t i = threadIdx.x; i < 256u; i += kBlock) lut255[i] = (float)i / 255.0f; /* overlaps the copy */
     if (RESIDENT) {
         mbar_wait(&bar, 0);
-        const float4* base = reinterpret_cast<const float4*>(rt_smem);
-        g.sph = base + fp.lay.sph_off;
-        g.pln = base + fp.lay.pln_off;
-        g.lit = base + fp.lay.lit_off;
-        g.flag = reinterpret_cast<const uint32_t*>(base + fp.lay.flag_off);
+        geo_bind(g, reinterpret_cast<const float4*>(rt_smem), fp, lut255);
     } else {
-        g.sph = fp.blob + fp.lay.sph_off;
-        g.pln = fp.blob + fp.lay.pln_off;
-        g.lit = fp.blob + fp.lay.lit_off;
-        g.flag = reinterpret_cast<const uint32_t*>(fp.blob + fp.lay.flag_off);
+        geo_bind(g, fp.blob, fp, lut255);
     }
     __syncthreads();
 
@@ -135,18 +126,22 @@ __global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ R
     }
 }
 
-/* ---- scene_prep: wire arrays -> compact blob (one thread per object) ---- */
+/* ---- scene_prep: wire arrays -> compact blob (one thread per record slot) ---- */
 __global__ void scene_prep(const unsigned char* __restrict__ spheres, uint32_t S, const unsigned char* __restrict__ planes,
                            uint32_t P, const unsigned char* __restrict__ lights, uint32_t L, float4* __restrict__ blob,
                            RtBlobLayout lay) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const float4 never = make_float4(0.0f, 0.0f, 0.0f, -CUDART_INF_F); /* D = b*b - 4a*(|v|^2 + inf) < 0 for every finite ray */
+    float4* sph = blob + lay.geo_off + lay.Lpad;
     if (i < S) {
         const float4* q = reinterpret_cast<const float4*>(spheres + (size_t)i * RT_SPHERE_BYTES);
         float4 c = q[0];
         float r = q[1].x;
-        blob[lay.sph_off + i] = make_float4(c.x, c.y, c.z, r * r);
+        sph[i] = make_float4(c.x, c.y, c.z, r * r);
         uint32_t transp = __float_as_uint(q[4].x); /* material @32: rgb, {amb,dif,spe,shin}, {transperent,...} */
         reinterpret_cast<uint32_t*>(blob + lay.flag_off)[i] = transp ? 1u : 0u;
+    } else if (i < lay.Spad) {
+        sph[i] = never;
     }
     if (i < P) {
         const float4* q = reinterpret_cast<const float4*>(planes + (size_t)i * RT_PLANE_BYTES);
@@ -173,14 +168,16 @@ __global__ void scene_prep(const unsigned char* __restrict__ spheres, uint32_t S
         float4 o = q[0], ri = q[1], c = q[2];
         float radius = ri.x, intensity = ri.y;
         V3 pre = (xyz(c) * intensity) * kInvPi; /* rgb*intensity*M_1_PI_F, left to right */
-        float4* out = blob + lay.lit_off + 2 * i;
-        out[0] = make_float4(o.x, o.y, o.z, radius * radius);
-        out[1] = make_float4(pre.x, pre.y, pre.z, radius);
+        blob[lay.geo_off + i] = make_float4(o.x, o.y, o.z, radius * radius);
+        blob[lay.laux_off + i] = make_float4(pre.x, pre.y, pre.z, radius);
+    } else if (i < lay.Lpad) {
+        blob[lay.geo_off + i] = never;
     }
     if (i == 0 && S + P + L == 0) blob[0] = make_float4(0, 0, 0, 0);
 }
 
-/* ---- tile_cost: skeleton trace of five rays per tile (scheduling hint only; cannot change any pixel) ---- */
+/* ---- tile_cost: skeleton trace (no shading, no refraction children) of five rays per 2x2 group of tiles.
+ * A scheduling hint only: it cannot change any pixel. ---- */
 constexpr uint32_t kCostBuckets = 64;
 
 __device__ uint32_t skeleton_cost(const RtFrameParams& fp, const Geo& g, uint32_t id) {
@@ -188,40 +185,27 @@ __device__ uint32_t skeleton_cost(const RtFrameParams& fp, const Geo& g, uint32_
     primary_ray(fp, id, o, d);
     Tally<false> tl;
     uint32_t cost = 0;
-    float n_cur = kAirN;
     for (int depth = 0; depth < kMaxDepth && cost < kCostBuckets; depth++) {
         RayF r;
         ray_setup_fast(r, o, d);
-        float t = CUDART_INF_F;
-        int who = -1, whop = -1;
-        for_sphere_hits(r, g.sph, 1, g.S, tl, [&](uint32_t i, float t1) {
-            if (!(t1 >= t)) { t = t1; who = (int)i; }
-            return false;
-        });
-        for (uint32_t j = 0; j < g.P; j++) {
-            float t1;
-            if (!hit_plane_fast(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) || t1 >= t) continue;
-            t = t1;
-            whop = (int)j;
-        }
-        if (who < 0 && whop < 0) break;
-        V3 ip = o + d * t, nrm;
+        Closest c;
+        closest_pass(r, g, tl, c);
+        if ((c.k >= 0 && !c.occluded) || (c.who < 0 && c.whop < 0)) break;
+        V3 ip = o + d * c.t, nrm;
         Material m;
-        if (whop >= 0) {
-            nrm = xyz(g.pln[4 * whop]);
-            m = load_material(fp.raw_planes + (size_t)whop * RT_PLANE_BYTES);
+        if (c.whop >= 0) {
+            nrm = xyz(g.pln[4 * c.whop]);
+            m = load_material(fp.raw_planes + (size_t)c.whop * RT_PLANE_BYTES);
         } else {
             float ql;
-            nrm = normalize_len(ip - xyz(g.sph[who]), ql);
-            m = load_material(fp.raw_spheres + (size_t)who * RT_SPHERE_BYTES);
+            nrm = normalize_len(ip - xyz(g.sph[c.who]), ql);
+            m = load_material(fp.raw_spheres + (size_t)c.who * RT_SPHERE_BYTES);
         }
         const bool shaded = (m.diffuse != 0.0f) || (m.specular != 0.0f);
         cost += shaded ? 4u : 1u;
         if (m.transperent) cost += 12u; /* a refraction subtree hangs off this hit */
         ip = ip + nrm * kEps;
         float cosI = -dot3(nrm, d);
-        float n2 = (n_cur == kAirN) ? m.n : kAirN;
-        (void)n2;
         d = d + nrm * (2.0f * cosI);
         o = ip;
     }
@@ -235,21 +219,16 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
     __syncthreads();
     Geo g;
-    g.S = fp.S; g.P = fp.P; g.L = fp.L;
-    g.lut255 = lut255;
-    g.sph = fp.blob + fp.lay.sph_off;
-    g.pln = fp.blob + fp.lay.pln_off;
-    g.lit = fp.blob + fp.lay.lit_off;
-    g.flag = reinterpret_cast<const uint32_t*>(fp.blob + fp.lay.flag_off);
-    const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
-    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tile < ntiles) {
-        const uint32_t tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
-        const uint32_t px[5] = {0, kTileW - 1, 0, kTileW - 1, kTileW / 2};
-        const uint32_t py[5] = {0, 0, kTileH - 1, kTileH - 1, kTileH / 2};
+    geo_bind(g, fp.blob, fp, lut255);
+    const uint32_t gx = (fp.tiles_x + 1) / 2, gy = (fp.tiles_y + 1) / 2;
+    const uint32_t grp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (grp < gx * gy) {
+        const uint32_t bx = grp % gx, by = grp / gx;
+        const uint32_t px[5] = {0, 2 * kTileW - 1, 0, 2 * kTileW - 1, kTileW};
+        const uint32_t py[5] = {0, 0, 2 * kTileH - 1, 2 * kTileH - 1, kTileH};
         uint32_t cost = 0;
         for (int s = 0; s < 5; s++) {
-            uint32_t x = tx * kTileW + px[s], lr = ty * kTileH + py[s];
+            uint32_t x = bx * 2 * kTileW + px[s], lr = by * 2 * kTileH + py[s];
             if (x >= fp.W) x = fp.W - 1;
             if (lr >= fp.local_rows) lr = fp.local_rows - 1;
             const uint32_t y = ((lr / fp.band_rows) * fp.parts + fp.part) * fp.band_rows + lr % fp.band_rows;
@@ -257,28 +236,41 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
             uint32_t c = skeleton_cost(fp, g, y * fp.W + x);
             cost = c > cost ? c : cost;
         }
-        cost_out[tile] = cost;
-        atomicAdd(&shist[cost], 1u);
+        uint32_t n = 0;
+        for (uint32_t dy = 0; dy < 2; dy++)
+            for (uint32_t dx = 0; dx < 2; dx++) {
+                const uint32_t tx = bx * 2 + dx, ty = by * 2 + dy;
+                if (tx < fp.tiles_x && ty < fp.tiles_y) { cost_out[ty * fp.tiles_x + tx] = cost; n++; }
+            }
+        atomicAdd(&shist[cost], n);
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
         if (shist[i]) atomicAdd(&hist[i], shist[i]);
 }
 
-/* counting sort, heaviest bucket first; order within a bucket is arbitrary (it cannot affect any pixel) */
+/* counting sort, heaviest bucket first; order within a bucket is arbitrary (it cannot affect any pixel).
+ * One global atomic per (block, bucket): ranks inside a block come from shared-memory atomics. */
 __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __restrict__ hist,
                            uint32_t* __restrict__ cursor, uint32_t* __restrict__ order, uint32_t ntiles) {
-    __shared__ uint32_t base[kCostBuckets];
+    __shared__ uint32_t base[kCostBuckets], local[kCostBuckets], gbase[kCostBuckets];
+    for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) local[i] = 0;
     if (threadIdx.x == 0) {
         uint32_t acc = 0;
         for (int b = (int)kCostBuckets - 1; b >= 0; b--) { base[b] = acc; acc += hist[b]; }
     }
     __syncthreads();
     const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t c = 0, rank = 0;
     if (tile < ntiles) {
-        const uint32_t c = cost[tile];
-        order[base[c] + atomicAdd(&cursor[c], 1u)] = tile;
+        c = cost[tile];
+        rank = atomicAdd(&local[c], 1u);
     }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
+        gbase[i] = local[i] ? atomicAdd(&cursor[i], local[i]) : 0u;
+    __syncthreads();
+    if (tile < ntiles) order[base[c] + gbase[c] + rank] = tile;
 }
 
 /* FP32 pipe calibration: 8 independent FMA chains per thread. */
@@ -382,8 +374,8 @@ using namespace rt;
 cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, const unsigned char* d_planes, uint32_t P,
                                  const unsigned char* d_lights, uint32_t L, float4* d_blob, RtBlobLayout lay,
                                  cudaStream_t st) {
-    uint32_t n = S > P ? S : P;
-    n = n > L ? n : L;
+    uint32_t n = lay.Spad > P ? lay.Spad : P;
+    n = n > lay.Lpad ? n : lay.Lpad;
     if (n == 0) n = 1;
     scene_prep<<<(n + 127) / 128, 128, 0, st>>>(d_spheres, S, d_planes, P, d_lights, L, d_blob, lay);
     return cudaGetLastError();
@@ -394,11 +386,11 @@ cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
     cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, 2 * kCostBuckets * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
-    const uint32_t blocks = (ntiles + 127) / 128;
-    tile_cost<<<blocks, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
+    const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
+    tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    tile_order<<<blocks, 128, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles);
+    tile_order<<<(ntiles + 255) / 256, 256, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles);
     return cudaGetLastError();
 }
 

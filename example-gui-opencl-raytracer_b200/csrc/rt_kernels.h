@@ -11,21 +11,26 @@
 #define RT_MATERIAL_OFFSET 32 /* rmaterial sits at byte 32 of rsphere and rplane */
 
 /* Compact geometry ("scene blob"), produced on the device by scene_prep and staged into shared memory
- * by one TMA bulk copy per CTA.  Units are float4 records:
- *   [sph_off  .. +S )   {cx, cy, cz, r*r}
- *   [pln_off  .. +4P)   {n.xyz, -}, {p.xyz, -}, {basis0.xyz, texture_scale}, {basis1.xyz, texture_id bits}
- *   [lit_off  .. +2L)   {o.xyz, r*r}, {rgb*intensity*M_1_PI_F, radius}
+ * by TMA bulk copies.  Units are float4 records:
+ *   [geo_off  .. +Lpad)      light  {o.xyz, r*r}          \ one contiguous run of "sphere-like" records;
+ *   [         .. +Spad)      sphere {c.xyz, r*r}          /  each count padded to a multiple of 4 with
+ *                                                            never-hit records {0,0,0,-inf}
+ *   [laux_off .. +L)         light  {rgb*intensity*M_1_PI_F, radius}
+ *   [pln_off  .. +4P)        {n.xyz, -}, {p.xyz, -}, {basis0.xyz, texture_scale}, {basis1.xyz, texture_id bits}
  *   [flag_off .. +ceil(S/4)) one uint32 per sphere: material.transperent != 0
  */
 struct RtBlobLayout {
-    uint32_t sph_off, pln_off, lit_off, flag_off, total; /* in float4 records */
+    uint32_t geo_off, laux_off, pln_off, flag_off, total; /* in float4 records */
+    uint32_t Lpad, Spad;
 };
 static inline RtBlobLayout rt_blob_layout(uint32_t S, uint32_t P, uint32_t L) {
     RtBlobLayout b;
-    b.sph_off = 0;
-    b.pln_off = S;
-    b.lit_off = b.pln_off + 4 * P;
-    b.flag_off = b.lit_off + 2 * L;
+    b.Lpad = (L + 3u) & ~3u;
+    b.Spad = (S + 3u) & ~3u;
+    b.geo_off = 0;
+    b.laux_off = b.Lpad + b.Spad;
+    b.pln_off = b.laux_off + L;
+    b.flag_off = b.pln_off + 4 * P;
     b.total = b.flag_off + (S + 3) / 4;
     if (b.total == 0) b.total = 1;
     return b;

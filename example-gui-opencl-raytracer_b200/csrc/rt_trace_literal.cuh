@@ -109,7 +109,7 @@ __device__ __forceinline__ uint32_t trace_pixel_literal(const RtFrameParams& fp,
             int k = -1;
             for (uint32_t i = 0; i < g.L; i++) {
                 float t1;
-                if (!hit_sphere(r, g.lit[2 * i], t1, tl) || t1 >= tL) continue;
+                if (!hit_sphere(r, g.lgeo[i], t1, tl) || t1 >= tL) continue;
                 tL = t1;
                 k = (int)i;
             }
@@ -127,7 +127,7 @@ __device__ __forceinline__ uint32_t trace_pixel_literal(const RtFrameParams& fp,
                     V3 ip = o + d * tL;
                     V3 od = o - ip;
                     float dd = sqrtf(dot3(od, od));
-                    V3 col = xyz(g.lit[2 * k + 1]) * (1.0f / dd * dd); /* (1/d)*d, primitives.cl:288 */
+                    V3 col = xyz(g.laux[k]) * (1.0f / dd * dd); /* (1/d)*d, primitives.cl:288 */
                     rgb = rgb + col * f;
                     if (AOV && first) hit_id = RTB_HIT_LIGHT | (uint32_t)k;
                     depth = kMaxDepth; /* `break` of raytracing.cl:53 */
@@ -198,7 +198,7 @@ __device__ __forceinline__ uint32_t trace_pixel_literal(const RtFrameParams& fp,
             float shin = (float)m.shininess;
             float fs = f * m.specular, fd = f * m.diffuse;
             for (uint32_t i = 0; i < g.L; i++) {
-                float4 l0 = g.lit[2 * i], l1 = g.lit[2 * i + 1];
+                float4 l0 = g.lgeo[i], l1 = g.laux[i];
                 V3 lo = xyz(l0);
                 float radius = l1.w;
                 V3 ld = lo - ip;
