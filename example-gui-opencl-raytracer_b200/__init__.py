@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librtb200.so")
+LIB_PATH = os.environ.get("RTB_LIB") or os.path.join(HERE, "librtb200.so")  # RTB_LIB: A/B builds only
 
 HIT_LIGHT = 0x80000000
 COUNTER_NAMES = ("segments", "shadow_rays", "sphere_tests", "sphere_dpos", "plane_tests", "texels", "shadow_skipped")

@@ -185,7 +185,9 @@ __device__ __forceinline__ void primary_ray(const RtFrameParams& fp, uint32_t id
 __device__ __forceinline__ float reflect_amount(const Material& m, float n1, float n2, float cosI) {
     float refl = m.reflectivity;
     if (m.dielectric) {
-        float r0 = (n1 - n2) / (n1 + n2);
+        const float rn = n1 - n2, rd = n1 + n2;
+        /* 0 / (positive finite) is 0: spares the division's slow path for index-matched media (mirror, n = 1) */
+        float r0 = (rn == 0.0f && rd > 1e-30f && rd < 1e30f) ? rn : rn / rd;
         r0 *= r0;
         float cosX = cosI;
         float fr;

@@ -24,11 +24,14 @@
 
 namespace rt {
 
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 5
+#endif
 extern __shared__ __align__(128) unsigned char rt_smem[];
 
 /* MODE: 0 = fast, 1 = literal + counters (reference accounting), 2 = fast + counters (executed work) */
 template <bool RESIDENT, int MODE, bool AOV>
-__global__ void __launch_bounds__(kBlock) render_frame(const __grid_constant__ RtFrameParams fp) {
+__global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __grid_constant__ RtFrameParams fp) {
     constexpr bool COUNT = MODE != 0;
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
