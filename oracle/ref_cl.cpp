@@ -148,3 +148,53 @@ int ref_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t y0, 
 int ref_hw_threads(void) { int n = (int)std::thread::hardware_concurrency(); return n > 0 ? n : 1; }
 
 }  // extern "C"
+
+/* ---- per-function known-answer entry points: thin marshalling onto the reference's own functions
+ * (narrow instantiation).  Mirrors the rto_* set of rt_oracle.h. ---- */
+namespace rn = ref_narrow;
+static inline void st3(float* p, const float3& v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
+static inline rn::rray mkray(const float* o, const float* d) {
+    rn::rray r; r.origin = f3(o); r.dir = f3(d); r.rgb = float3(0.0f); r.depth = 0; return r;
+}
+extern "C" {
+float ref_xorshift32(uint32_t* state) { rn::xorshift32_state s; s.x = *state; float v = rn::xorshift32(&s); *state = s.x; return v; }
+void ref_map_to_cube(const float* dir, uint32_t face, int* uv) { float3 d = f3(dir); clshim::int2 r = rn::map_to_cube(&d, face); uv[0] = r.x; uv[1] = r.y; }
+void ref_reflect(const float* I, const float* N, float* out) { float3 i = f3(I), n = f3(N); st3(out, rn::reflect(&i, &n)); }
+void ref_refract(float n1, float n2, const float* I, const float* N, float* out) { float3 i = f3(I), n = f3(N); st3(out, rn::refract(n1, n2, &i, &n)); }
+float ref_schlick(float n1, float n2, const float* I, const float* N) { float3 i = f3(I), n = f3(N); return rn::compute_schlick(n1, n2, &i, &n); }
+int ref_emod(int a, int b) { return rn::euclidean_modulo(a, b); }
+int ref_isect_sphere(const float* o, const float* d, const float* c, float r, float* t) {
+    rn::rray ray = mkray(o, d); float3 cc = f3(c); return rn::intersect_sphere(&ray, &cc, r, t) ? 1 : 0;
+}
+int ref_isect_plane(const float* o, const float* d, const float* n, const float* p, float* t) {
+    rn::rray ray = mkray(o, d); float3 nn = f3(n), pp = f3(p); return rn::intersect_plane(&ray, &nn, &pp, t) ? 1 : 0;
+}
+void ref_plane_texel(const void* plane, const float* P, const uint8_t* tex, int tw, int th, int tl, float* rgb) {
+    rn::rplane pl = *(const rn::rplane*)plane; float3 ip = f3(P); image2d_array_t im{tex, tw, th, tl};
+    st3(rgb, rn::plane_texture_pixel(&pl, &ip, im));
+}
+void ref_raygen(const float* cam, uint32_t W, uint32_t H, uint32_t id, float* o, float* d) {
+    alignas(16) unsigned char buf[64]; rn::rray* one = (rn::rray*)buf;
+    clshim::g_global_id = id;
+    rn::raygen(f3(cam), f3(cam + 3), f3(cam + 6), f3(cam + 9), cam[12], cam[13], W, H, one - id);
+    st3(o, one->origin); st3(d, one->dir);
+}
+int ref_find_light(const float* o, const float* d, const void* spheres, uint32_t S, const void* planes, uint32_t P,
+                   const void* lights, uint32_t L, float* color) {
+    rn::rray ray = mkray(o, d); float3 c;
+    bool r = rn::findLightIntersection(&ray, (rn::rlight*)lights, (rn::rsphere*)spheres, (rn::rplane*)planes, L, S, P, &c);
+    if (r) st3(color, c);
+    return r ? 1 : 0;
+}
+int ref_find_solid(const float* o, const float* d, const void* spheres, uint32_t S, const void* planes, uint32_t P,
+                   const uint8_t* tex, int tw, int th, int tl, float* ip, float* nrm, void* material64) {
+    rn::rray ray = mkray(o, d); float3 a, b; rn::rmaterial m; image2d_array_t im{tex, tw, th, tl};
+    bool r = rn::findSolidIntersection(&ray, (rn::rsphere*)spheres, (rn::rplane*)planes, (rn::uchar)S, (rn::uchar)P, &a, &b, &m, im);
+    if (r) { st3(ip, a); st3(nrm, b); memcpy(material64, &m, 64); }
+    return r ? 1 : 0;
+}
+float ref_shadow(const float* to, const float* from, const void* spheres, uint32_t S, const void* planes, uint32_t P) {
+    float3 t = f3(to), f = f3(from);
+    return rn::testShadowPath(&t, &f, (rn::rsphere*)spheres, (rn::rplane*)planes, S, P);
+}
+}  // extern "C"

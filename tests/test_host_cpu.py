@@ -1,0 +1,147 @@
+"""CPU-side checks (no GPU): the C ABI exports what include/*.h declares, the host-side mirror agrees with
+the oracle's helpers, the PNG codec decodes the shipped assets exactly, and the N>1 row-band gather
+rebuilds the single-part frame (gloo, world_size 2)."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return set(re.findall(r"\b((?:rtb|cl_wrap|cuda_wrap)_\w+)\s*\(", text))
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    L = pkg.lib()   # raises if librtb200.so is missing
+    names = declared("rtb200.h") | declared("cuda_wrap.h")
+    assert len(names) >= 35
+    for n in sorted(names):
+        assert hasattr(L, n), "librtb200.so does not export " + n
+    assert names == set(pkg.ENGINE_SYMBOLS) | set(pkg.WRAP_SYMBOLS)
+
+
+def test_no_compute_without_a_gpu(pkg):
+    """The product path must fail loudly, never fall back to a CPU implementation."""
+    if pkg.lib().rtb_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(pkg.RtbError):
+        pkg.Engine(0)
+
+
+def test_cl_wrap_struct_layout(pkg):
+    w = pkg.ClWrap
+    assert w.buffers.offset == 4 * 8 + 8 + 16 * 8           # 4 handles, kernels_num (+pad), kernels[16]
+    assert C.sizeof(w) == w.buffers.offset + 16 * 32 * 8 + 16 * 32 * 4 + 16 * 4
+    src = subprocess.run(["gcc", "-Iinclude", "-Iinclude/shim", "-x", "c", "-", "-o", "/tmp/rtb_layout"], cwd=ROOT,
+                         input=b'#include <stdio.h>\n#include <stddef.h>\n#include "cuda_wrap.h"\n'
+                               b'int main(){printf("%zu %zu %zu", sizeof(cl_wrap), offsetof(cl_wrap, buffers), sizeof(cl_float3));return 0;}')
+    assert src.returncode == 0
+    out = subprocess.run(["/tmp/rtb_layout"], capture_output=True).stdout.decode().split()
+    assert [int(v) for v in out] == [C.sizeof(w), w.buffers.offset, 16]
+
+
+def test_camera_and_map_helpers_match_oracle_helpers(pkg, ref):
+    from example_gui_opencl_raytracer_b200 import host
+    for (W, H) in ((800, 600), (3840, 2160), (101, 67)):
+        a = host.camera(W=W, H=H, **host.RAYPNG_CAMERA)
+        b = ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    s, p, l = host.load_map(os.path.join(ROOT, "scenes", "render.map"))
+    assert (len(s), len(p), len(l)) == (4 * 96, 2 * 96, 3 * 48)
+    assert [s, p, l] == ref.load_map(os.path.join(ROOT, "scenes", "render.map"))
+    # the packers reproduce the file (scene_dump.c:8-69 values)
+    sp = (host.sphere((4.5, .5, -1), .5, dict(host.PLASTIC, rgb=(1, 0, 0))) + host.sphere((-1, 1, 4.5), .8, dict(host.PLASTIC, rgb=(0, 0, 1))) +
+          host.sphere((.8, .8, 1.5), .8, dict(host.GLASS)) + host.sphere((-.6, .8, -1), .8, dict(host.GLASS, rgb=(0, 1, 0), ambient=.05)))
+    assert sp == s
+    assert host.render_map_lights() == l
+    tmp = "/tmp/rtb_roundtrip.map"
+    host.dump_map(tmp, s, p, l)
+    assert open(tmp, "rb").read() == open(os.path.join(ROOT, "scenes", "render.map"), "rb").read()
+    with pytest.raises(ValueError):
+        host.dump_map(tmp, s * 64, p, l)      # 256 spheres do not fit the one-byte count
+
+
+def test_png_codec_decodes_assets_exactly(pkg, ref):
+    from example_gui_opencl_raytracer_b200 import host
+    tex, sky = host.default_images(ROOT)
+    rt, rs = ref.default_textures(ROOT)   # PIL
+    assert tex.shape == (4, 256, 256, 4) and sky.shape == (1, 3072, 4096, 4)
+    assert np.array_equal(tex, rt) and np.array_equal(sky, rs)
+    # writer -> reader round trip, odd size
+    L = pkg.lib()
+    L.rtpng_write_rgb8.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
+    rgb = np.random.default_rng(1).integers(0, 256, size=(37, 53, 3), dtype=np.uint8)
+    assert L.rtpng_write_rgb8(b"/tmp/rtb_rt.png", rgb.ctypes.data_as(C.c_void_p), 53, 37) == 0
+    back = host.load_png_layers(["/tmp/rtb_rt.png"])
+    assert np.array_equal(back[0, :, :, :3], rgb) and (back[..., 3] == 255).all()
+    from PIL import Image
+    assert np.array_equal(np.asarray(Image.open("/tmp/rtb_rt.png")), rgb)
+    # the reference's format gate (opencl_wrap.c:299-307): 8-bit RGB only
+    Image.fromarray(rgb[..., 0]).save("/tmp/rtb_gray.png")
+    with pytest.raises(ValueError):
+        host.load_png_layers(["/tmp/rtb_gray.png"])
+
+
+def test_synthetic_scene_is_deterministic(pkg):
+    from example_gui_opencl_raytracer_b200 import host
+    a = host.sphere_grid_scene(32)
+    b = host.sphere_grid_scene(32)
+    assert a[0] == b[0] and len(a[0]) == 1024 * 96 and len(a[1]) == 96 and len(a[2]) == 3 * 48
+
+
+def test_partition_rows_matches_python_twin(pkg):
+    from example_gui_opencl_raytracer_b200 import bands
+    for H in (1, 7, 250, 2160):
+        for band in (1, 4, 8, 100):
+            for world in (1, 2, 3, 8):
+                tot = 0
+                for r in range(world):
+                    n = int(pkg.lib().rtb_partition_rows(H, C.byref(pkg.Partition(band, world, r))))
+                    assert n == len(bands.band_rows_of(r, world, H, band))
+                    tot += n
+                assert tot == H
+
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np, torch, torch.distributed as dist
+import __graft_entry__ as g
+pkg = g.load_package(); ref = g.load_oracle()
+from example_gui_opencl_raytracer_b200 import bands
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+scene = ref.render_map_scene(sys.argv[1])
+ok = True
+for (W, H, band) in ((64, 48, 8), (40, 30, 4), (33, 21, 8)):
+    cam = ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA)
+    fg = bands.FrameGather(W, H, band, world, rank, torch.device("cpu"))
+    rows = bands.band_rows_of(rank, world, H, band)
+    full, _ = ref.port().render(scene, cam, W, H, threads=2, want_hit=False)   # CPU stand-in for this rank's render
+    mine = full.reshape(H, W)[rows].astype(np.int64).astype(np.uint32).view(np.int32).reshape(-1)
+    fg.local[: mine.size] = torch.from_numpy(mine.copy())
+    frame = fg.gather()
+    if rank == 0:
+        ok = ok and np.array_equal(frame.numpy().view(np.uint32), full)
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if ok else 3)
+'''
+
+
+def test_two_rank_band_gather_rebuilds_the_frame():
+    """world_size 2 over gloo: the gather + interleave must reproduce the one-part frame bit for bit."""
+    path = "/tmp/rtb_gloo_worker.py"
+    open(path, "w").write(WORKER)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29617", path, ROOT],
+                       capture_output=True, timeout=300)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
