@@ -145,8 +145,9 @@ static void put_chunk(FILE* fp, const char* type, const unsigned char* data, uin
     fwrite(c, 1, 4, fp);
 }
 
-int rtpng_write_rgb8(const char* path, const uint8_t* rgb, uint32_t w, uint32_t h) {
+int rtpng_write_rgb8_fp(FILE* fp, const uint8_t* rgb, uint32_t w, uint32_t h) {
     const size_t stride = (size_t)w * 3, raw_len = (stride + 1) * h;
+    if (!fp) return RTPNG_EOPEN;
     if (raw_len > 0x7ff00000u) return RTPNG_EFORMAT;
     unsigned char* raw = (unsigned char*)malloc(raw_len ? raw_len : 1);
     if (!raw) return RTPNG_ENOMEM;
@@ -159,8 +160,6 @@ int rtpng_write_rgb8(const char* path, const uint8_t* rgb, uint32_t w, uint32_t 
     if (!z) { free(raw); return RTPNG_ENOMEM; }
     if (compress2(z, &zcap, raw, (uLong)raw_len, 6) != Z_OK) { free(raw); free(z); return RTPNG_ECORRUPT; }
     free(raw);
-    FILE* fp = fopen(path, "wb");
-    if (!fp) { free(z); return RTPNG_EOPEN; }
     fwrite(kSig, 1, 8, fp);
     unsigned char ih[13] = {(unsigned char)(w >> 24), (unsigned char)(w >> 16), (unsigned char)(w >> 8), (unsigned char)w,
                             (unsigned char)(h >> 24), (unsigned char)(h >> 16), (unsigned char)(h >> 8), (unsigned char)h,
@@ -169,5 +168,13 @@ int rtpng_write_rgb8(const char* path, const uint8_t* rgb, uint32_t w, uint32_t 
     put_chunk(fp, "IDAT", z, (uint32_t)zcap);
     put_chunk(fp, "IEND", NULL, 0);
     free(z);
-    return fclose(fp) == 0 ? RTPNG_OK : RTPNG_EOPEN;
+    return ferror(fp) ? RTPNG_EOPEN : RTPNG_OK;
+}
+
+int rtpng_write_rgb8(const char* path, const uint8_t* rgb, uint32_t w, uint32_t h) {
+    FILE* fp = fopen(path, "wb");
+    if (!fp) return RTPNG_EOPEN;
+    int rc = rtpng_write_rgb8_fp(fp, rgb, w, h);
+    if (fclose(fp) != 0 && rc == RTPNG_OK) rc = RTPNG_EOPEN;
+    return rc;
 }

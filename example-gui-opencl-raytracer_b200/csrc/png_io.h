@@ -6,6 +6,7 @@
 #ifndef RT_PNG_IO_H
 #define RT_PNG_IO_H
 #include <stdint.h>
+#include <stdio.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -16,6 +17,8 @@ int rtpng_info(const char* path, uint32_t* w, uint32_t* h, int* bit_depth, int* 
 int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t h);
 /* Write w*h RGB8 pixels (row 0 = top) as a non-interlaced 8-bit RGB PNG. */
 int rtpng_write_rgb8(const char* path, const uint8_t* rgb, uint32_t w, uint32_t h);
+/* Same, onto an open stream (left open). */
+int rtpng_write_rgb8_fp(FILE* fp, const uint8_t* rgb, uint32_t w, uint32_t h);
 #ifdef __cplusplus
 }
 #endif
