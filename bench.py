@@ -322,7 +322,7 @@ def run_gpu_arm(args):
 
     # ---- end to end through the public API with host buffers ----
     if world == 1:
-        e2e_ms, h2d, d2h = e2e_cl_wrap(pkg, wl, args, host_frame)
+        e2e_ms, h2d, d2h, rb_stats = e2e_cl_wrap(pkg, wl, args, host_frame)
     else:
         def step_e2e():
             eng.set_camera(wl["cam"])
@@ -330,7 +330,7 @@ def run_gpu_arm(args):
             if rank == 0:
                 host_frame.copy_(frame, non_blocking=True)
         t, _ = timed(step_e2e, args.steps, args.warmup, do_flush=False)
-        e2e_ms, h2d, d2h = t / args.steps, 14 * 4, H * W * 4
+        e2e_ms, h2d, d2h, rb_stats = t / args.steps, 14 * 4, H * W * 4, None
 
     t_ms = torch.tensor([total_ms, e2e_ms, float(np.mean(kernel_ms))], dtype=torch.float64, device=dev)
     if world > 1:
@@ -360,6 +360,7 @@ def run_gpu_arm(args):
             "clocks": clocks,
             "e2e": {"value": frame_rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
                     "frames_per_s": 1e3 / e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "readback": rb_stats,
                     "api": "cl_wrap_load_single_data x6 + cl_wrap_output(raygen) + cl_wrap_output(raytracer, read-back)"
                     if world == 1 else "rtb_set_camera + rtb_render(band) + NCCL gather + D2H on rank 0"},
             "gpu_launches": args.steps * world,
@@ -385,64 +386,23 @@ def run_gpu_arm(args):
 def e2e_cl_wrap(pkg, wl, args, host_frame):
     """The per-frame call sequence of raypng.c:50-57,86-89 / rayinteractive.c:98-103,186-189 with HOST
     buffers; set-up (scene, images, output slot) happens once, as in the reference drivers."""
-    import ctypes as C
-    L = pkg.wrap_lib()
+    from example_gui_opencl_raytracer_b200.wrap_session import WrapSession
     W, H = wl["W"], wl["H"]
-    w = pkg.ClWrap()
-    cs = C.c_char_p
-    L.cl_wrap_init(C.byref(w), C.c_uint64(pkg.CL_DEVICE_TYPE_GPU), cs(b"src/cl/raygen.cl"), cs(b"raygen"),
-                   cs(b"src/cl/raytracing.cl"), cs(b"raytracer"), cs(None))
-    cam = np.ascontiguousarray(wl["cam"], np.float32)
-    vec = [np.zeros(4, np.float32) for _ in range(4)]
-    for i in range(4):
-        vec[i][:3] = cam[3 * i: 3 * i + 3]
-    wf, hf = C.c_float(cam[12]), C.c_float(cam[13])
-    pw, ph, pixels = C.c_uint32(W), C.c_uint32(H), C.c_uint32(W * H)
-
-    def camera_args():
-        for i in range(4):
-            L.cl_wrap_load_single_data(C.byref(w), 0, i, vec[i].ctypes.data_as(C.c_void_p), 16)
-        L.cl_wrap_load_single_data(C.byref(w), 0, 4, C.byref(wf), 4)
-        L.cl_wrap_load_single_data(C.byref(w), 0, 5, C.byref(hf), 4)
-    camera_args()
-    L.cl_wrap_load_single_data(C.byref(w), 0, 6, C.byref(pw), 4)
-    L.cl_wrap_load_single_data(C.byref(w), 0, 7, C.byref(ph), 4)
-    L.cl_wrap_load_global_data(C.byref(w), 0, 8, None, 64 * W * H, pkg.CL_MEM_READ_WRITE)
-    L.cl_wrap_load_single_data(C.byref(w), 1, 0, C.byref(w.buffers[0], 8 * C.sizeof(C.c_void_p)), 8)
-    s, p, l = wl["spheres"], wl["planes"], wl["lights"]
-    L.cl_wrap_load_global_data(C.byref(w), 1, 1, s, len(s), pkg.CL_MEM_READ_ONLY)
-    L.cl_wrap_load_global_data(C.byref(w), 1, 2, p, len(p), pkg.CL_MEM_READ_ONLY)
-    L.cl_wrap_load_global_data(C.byref(w), 1, 3, l, len(l), pkg.CL_MEM_READ_ONLY)
-    ns, np_, nl = len(s) // 96, len(p) // 96, len(l) // 48
-    if max(ns, np_, nl) <= 255:
-        cnts = [C.c_uint8(ns), C.c_uint8(np_), C.c_uint8(nl)]
-        csz = 1
-    else:
-        cnts = [C.c_uint32(ns), C.c_uint32(np_), C.c_uint32(nl)]
-        csz = 4
-    for i in range(3):
-        L.cl_wrap_load_single_data(C.byref(w), 1, 4 + i, C.byref(cnts[i]), csz)
-    L.cl_wrap_load_single_data(C.byref(w), 1, 7, C.byref(pixels), 4)
-    from example_gui_opencl_raytracer_b200 import host
-    tex = [cs(os.path.join(ROOT, f).encode()) for f in host.TEXTURE_FILES]
-    L.cl_wrap_load_images(C.byref(w), C.c_uint32(1), C.c_uint32(8), C.c_uint64(pkg.CL_MEM_COPY_HOST_PTR), C.c_uint32(4), *tex)
-    L.cl_wrap_load_images(C.byref(w), C.c_uint32(1), C.c_uint32(9), C.c_uint64(pkg.CL_MEM_COPY_HOST_PTR), C.c_uint32(1),
-                          cs(os.path.join(ROOT, host.SKYBOX_FILE).encode()))
-    L.cl_wrap_load_global_data(C.byref(w), 1, 10, None, 4 * W * H, pkg.CL_MEM_WRITE_ONLY)
-    hp = C.c_void_p(host_frame.data_ptr())
+    ses = WrapSession(W, H, wl["spheres"], wl["planes"], wl["lights"], wl["cam"], root=ROOT)
+    hp = host_frame.data_ptr()
 
     def frame():
-        camera_args()
-        L.cl_wrap_output(C.byref(w), W * H, 0, 0, 0, 0, None)
-        L.cl_wrap_output(C.byref(w), W * H, 4 * W * H, 1, 1, 10, hp)
+        ses.set_camera(wl["cam"])
+        ses.frame(hp)
     for _ in range(max(3, args.warmup)):
         frame()
     t0 = time.perf_counter()  # the API is synchronous (clFinish + blocking read): host clock == device done
     for _ in range(args.steps):
         frame()
     ms = (time.perf_counter() - t0) * 1e3 / args.steps
-    L.cl_wrap_release(C.byref(w))
-    return ms, 4 * 16 + 2 * 4, 4 * W * H
+    stats = ses.readback_stats()
+    ses.release()
+    return ms, 4 * 16 + 2 * 4, 4 * W * H, stats
 
 
 def main():

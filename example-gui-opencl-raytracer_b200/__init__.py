@@ -27,11 +27,11 @@ ENGINE_SYMBOLS = (
     "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
-    "rtb_host_register", "rtb_host_unregister", "rtb_last_launch", "rtb_fp32_peak_tflops",
+    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_last_launch", "rtb_fp32_peak_tflops",
 )
 WRAP_SYMBOLS = (
     "cl_wrap_init", "cl_wrap_load_global_data", "cl_wrap_load_single_data", "cl_wrap_load_images", "cl_wrap_output",
-    "cl_wrap_release", "cuda_wrap_engine", "cuda_wrap_last_kernel_ms",
+    "cl_wrap_release", "cuda_wrap_engine", "cuda_wrap_last_kernel_ms", "cuda_wrap_readback_stats",
 )
 
 
@@ -90,6 +90,8 @@ def lib():
             "rtb_dev_read": (i, [vp, vp, vp, sz]),
             "rtb_host_register": (i, [vp, sz]),
             "rtb_host_unregister": (i, [vp]),
+            "rtb_host_map": (i, [vp, sz, C.POINTER(vp), C.POINTER(i)]),
+            "rtb_set_mirror": (i, [vp, vp]),
             "rtb_last_launch": (i, [vp, C.POINTER(LaunchInfo)]),
             "rtb_fp32_peak_tflops": (C.c_double, [vp, i]),
         }
@@ -315,6 +317,8 @@ def wrap_lib():
         L.cl_wrap_load_images.restype = None
         L.cuda_wrap_engine.argtypes = [wp]
         L.cuda_wrap_engine.restype = C.c_void_p
+        L.cuda_wrap_readback_stats.argtypes = [wp, C.POINTER(C.c_ulong), C.POINTER(C.c_ulong)]
+        L.cuda_wrap_readback_stats.restype = None
         L.cuda_wrap_last_kernel_ms.argtypes = [wp]
         L.cuda_wrap_last_kernel_ms.restype = C.c_float
         L._wrap_ready = True

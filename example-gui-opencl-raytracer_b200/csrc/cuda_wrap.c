@@ -8,6 +8,7 @@
 #include "../../include/cuda_wrap.h"
 
 #include <stdarg.h>
+#include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -46,7 +47,20 @@ typedef struct {
     uint32_t bound_ns, bound_np, bound_nl;
     int scene_dirty;
     const void *bound_tex, *bound_sky;
+    /* host read-back buffers seen by cl_wrap_output (N1: frame mirrored into the caller's buffer by the kernel) */
+    struct {
+        void* host;      /* caller's pointer */
+        size_t size;
+        void* dev_view;  /* device-visible alias once mapped, else NULL */
+        int registered;  /* page-locked by this wrapper (to undo in cl_wrap_release) */
+        int uses, failed;
+    } hostbuf[4];
+    int mirror_mode;     /* 0 auto (map on the 2nd use of a buffer), 1 never, 2 from the first use */
+    unsigned long mirrored_frames, copied_frames;
 } wrap_state;
+
+#define CANARY(k) (0xA5C30000u | (uint32_t)(k)) /* top byte != 0: never a 0x00RRGGBB pixel word (raytracing.cl:194) */
+enum { N_CANARY = 8 };
 
 static void die(const char* msg) {
     printf("ERROR:\t%s\n", msg);
@@ -90,6 +104,10 @@ void cl_wrap_init(cl_wrap* wrap, cl_device_type type, ...) {
     wrap->device = (cl_device_id)(size_t)(device + 1);
     wrap->queue = (cl_command_queue)rtb_stream(e);
     wrap_state* s = (wrap_state*)calloc(1, sizeof(wrap_state));
+    if (s) {
+        const char* ro = getenv("RTB_HOST_OUTPUT"); /* copy | mirror | auto (default) */
+        s->mirror_mode = ro && !strcmp(ro, "copy") ? 1 : (ro && !strcmp(ro, "mirror") ? 2 : 0);
+    }
     if (!s) die("Out of host memory");
     wrap->program = (cl_program)s;
 
@@ -207,6 +225,44 @@ void cl_wrap_load_images(cl_wrap* wrap, cl_uint kernel_id, cl_uint arg_id, cl_me
     wrap->buffers_ids[kernel_id][wrap->buffers_num[kernel_id]++] = arg_id;
 }
 
+/* N1: a device-visible alias of the caller's read-back buffer, or NULL to use the plain D2H copy.
+ * Page-locking costs ~0.25 ms/MB once, so in auto mode a buffer is mapped on its second use (a one-frame
+ * raypng run never pays it; the interactive loop pays it once). */
+static void* mirror_view(cl_wrap* wrap, void* host, size_t size) {
+    wrap_state* s = st(wrap);
+    if (s->mirror_mode == 1 || ((uintptr_t)host & 15)) return NULL;
+    int free_i = -1;
+    for (int i = 0; i < 4; i++) {
+        if (s->hostbuf[i].host == host && s->hostbuf[i].size == size) {
+            if (s->hostbuf[i].failed) return NULL;
+            if (s->hostbuf[i].dev_view) return s->hostbuf[i].dev_view;
+            free_i = i;
+            break;
+        }
+        if (!s->hostbuf[i].host && free_i < 0) free_i = i;
+    }
+    if (free_i < 0) return NULL; /* table full: keep copying */
+    s->hostbuf[free_i].host = host;
+    s->hostbuf[free_i].size = size;
+    if (++s->hostbuf[free_i].uses < 2 && s->mirror_mode != 2) return NULL;
+    void* view = NULL;
+    int reg = 0;
+    if (rtb_host_map(host, size, &view, &reg) != 0 || !view) { s->hostbuf[free_i].failed = 1; return NULL; }
+    s->hostbuf[free_i].dev_view = view;
+    s->hostbuf[free_i].registered = reg;
+    return view;
+}
+static void mirror_drop(cl_wrap* wrap, void* host) {
+    wrap_state* s = st(wrap);
+    for (int i = 0; i < 4; i++)
+        if (s->hostbuf[i].host == host) {
+            if (s->hostbuf[i].registered) rtb_host_unregister(host);
+            s->hostbuf[i].dev_view = NULL;
+            s->hostbuf[i].registered = 0;
+            s->hostbuf[i].failed = 1;
+        }
+}
+
 static uint32_t scalar_count(const scalar_cell* c) { /* cl_uchar in the reference (raytracing.cl:17); cl_uint accepted */
     if (c->size == 1) return c->bytes[0];
     if (c->size == 2) { uint16_t v; memcpy(&v, c->bytes, 2); return v; }
@@ -235,7 +291,7 @@ static void run_raygen(cl_wrap* wrap, size_t array_size) {
     s->rays_valid = 1;
 }
 
-static void run_raytracer(cl_wrap* wrap, cl_uint k, size_t array_size) {
+static uint64_t run_raytracer(cl_wrap* wrap, cl_uint k, size_t array_size, void* host_output, size_t output_size, int* mirrored) {
     wrap_state* s = st(wrap);
     rtb_engine* e = eng(wrap);
     const scalar_cell* c = s->scalars[k];
@@ -267,8 +323,19 @@ static void run_raytracer(cl_wrap* wrap, cl_uint k, size_t array_size) {
     if (n > array_size) n = array_size;
     if (n > total) n = total;
     if ((size_t)n * 4 > sl[RT_OUT].size) die("The device kernel failed"); /* would write past the output buffer */
+    *mirrored = 0;
+    if (host_output && output_size == (size_t)n * 4 && n >= 64) {
+        uint32_t* view = (uint32_t*)mirror_view(wrap, host_output, output_size);
+        if (view) {
+            volatile uint32_t* h = (volatile uint32_t*)host_output;
+            for (int c = 0; c < N_CANARY; c++) h[(size_t)c * (n - 1) / (N_CANARY - 1)] = CANARY(c);
+            if (rtb_set_mirror(e, view) != 0) die_engine("Couldn't run the kernel");
+            *mirrored = 1;
+        }
+    }
     if (rtb_render(e, s->W, s->H, (uint32_t)n, NULL, (uint32_t*)wrap->buffers[k][RT_OUT], NULL, 0) != 0)
         die_engine("Couldn't run the kernel");
+    return n;
 }
 
 /* image arrays are bound lazily (their slots can be filled in any order before the first launch) */
@@ -277,17 +344,32 @@ static void bind_images(cl_wrap* wrap, cl_uint k);
 void cl_wrap_output(cl_wrap* wrap, size_t array_size, size_t output_size, cl_uint kernel_run_id, cl_uint kernel_id,
                     cl_int arg_id, void* host_output) {
     check_kernel(wrap, kernel_run_id);
+    int mirrored = 0;
+    uint64_t n = 0;
     switch (kind_of(wrap, kernel_run_id)) {
         case K_RAYGEN: run_raygen(wrap, array_size); break;
-        case K_RAYTRACER:
+        case K_RAYTRACER: {
             bind_images(wrap, kernel_run_id);
-            run_raytracer(wrap, kernel_run_id, array_size);
+            /* the frame can be mirrored into host_output only when the read-back names this launch's output slot */
+            int same = host_output && kernel_id == kernel_run_id && arg_id == RT_OUT && wrap->buffers[kernel_id][RT_OUT];
+            n = run_raytracer(wrap, kernel_run_id, array_size, same ? host_output : NULL, output_size, &mirrored);
             break;
+        }
         default: die("Couldn't run the kernel");
     }
     if (rtb_sync(eng(wrap)) != 0) die_engine("The device kernel failed"); /* clFinish, opencl_wrap.c:380-385 */
 
     if (!host_output) return;
+    if (mirrored) {
+        /* every canary must have been overwritten by a pixel word; if one survives, the mapping no longer
+         * aliases the caller's pages (buffer freed and re-allocated at the same address): drop it and copy */
+        const volatile uint32_t* h = (const volatile uint32_t*)host_output;
+        int ok = 1;
+        for (int c = 0; c < N_CANARY; c++) if ((h[(size_t)c * (n - 1) / (N_CANARY - 1)] >> 24) != 0) ok = 0;
+        if (ok) { st(wrap)->mirrored_frames++; return; }
+        mirror_drop(wrap, host_output);
+    }
+    st(wrap)->copied_frames++;
     check_kernel(wrap, kernel_id);
     if (arg_id < 0 || arg_id >= __MAX_BUFFERS || !wrap->buffers[kernel_id][arg_id]) die("Failed to transfer device memory to host");
     const slot_info* si = &st(wrap)->slots[kernel_id][arg_id];
@@ -314,6 +396,8 @@ static void bind_images(cl_wrap* wrap, cl_uint k) {
 void cl_wrap_release(cl_wrap* wrap) {
     if (!wrap->context) return;
     rtb_sync(eng(wrap));
+    for (int i = 0; i < 4; i++)
+        if (st(wrap)->hostbuf[i].registered) rtb_host_unregister(st(wrap)->hostbuf[i].host);
     for (cl_uint k = 0; k < wrap->kernels_num; k++) {
         for (cl_uint i = 0; i < wrap->buffers_num[k]; i++) {
             cl_uint a = wrap->buffers_ids[k][i];
@@ -331,4 +415,8 @@ void cl_wrap_release(cl_wrap* wrap) {
 }
 
 struct rtb_engine* cuda_wrap_engine(cl_wrap* wrap) { return wrap ? eng(wrap) : NULL; }
+void cuda_wrap_readback_stats(cl_wrap* wrap, unsigned long* mirrored, unsigned long* copied) {
+    if (mirrored) *mirrored = wrap && wrap->program ? st(wrap)->mirrored_frames : 0;
+    if (copied) *copied = wrap && wrap->program ? st(wrap)->copied_frames : 0;
+}
 float cuda_wrap_last_kernel_ms(cl_wrap* wrap) { return wrap && wrap->context ? rtb_last_render_ms(eng(wrap)) : -1.0f; }

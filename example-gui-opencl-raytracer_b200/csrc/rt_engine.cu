@@ -71,6 +71,7 @@ struct rtb_engine {
     DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
     DevBuf tile_cost, tile_order, tile_hist;
     int opt_trace = 0, opt_tile_order = 1;
+    uint32_t* mirror = nullptr; /* one-shot, see rtb_set_mirror */
     rtb_launch_info last{};
 };
 
@@ -256,6 +257,9 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     if (((uintptr_t)d_out & 15) || ((uintptr_t)d_hit & 15)) return fail(-1, "rtb_render: output buffers must be 16-byte aligned");
     fp.out = d_out;
     fp.hit = d_hit;
+    fp.mirror = e->mirror;
+    e->mirror = nullptr;
+    if ((uintptr_t)fp.mirror & 15) return fail(-1, "rtb_render: mirror buffer must be 16-byte aligned");
     fp.tile_counter = (unsigned int*)e->sched.p;
     fp.counters = (unsigned long long*)((char*)e->sched.p + 64);
     fp.tiles_x = (W + 7) / 8;
@@ -384,12 +388,33 @@ int rtb_dev_read(rtb_engine* e, void* host, const void* dptr, size_t nbytes) {
     CU(cudaStreamSynchronize(e->stream), "D2H sync");
     return 0;
 }
+int rtb_set_mirror(rtb_engine* e, uint32_t* mirror) {
+    if (!e) return fail(-1, "null engine");
+    e->mirror = mirror;
+    return 0;
+}
+int rtb_host_map(void* host, size_t nbytes, void** dev_view, int* registered_here) {
+    if (!host || !dev_view) return fail(-1, "rtb_host_map: null argument");
+    if (registered_here) *registered_here = 0;
+    void* d = nullptr;
+    if (cudaHostGetDevicePointer(&d, host, 0) != cudaSuccess) { /* not page-locked yet */
+        (void)cudaGetLastError();
+        cudaError_t ce = cudaHostRegister(host, nbytes, cudaHostRegisterMapped | cudaHostRegisterPortable);
+        if (ce != cudaSuccess) { (void)cudaGetLastError(); return fail(-2, "cudaHostRegister", ce); }
+        if (registered_here) *registered_here = 1;
+        ce = cudaHostGetDevicePointer(&d, host, 0);
+        if (ce != cudaSuccess) { (void)cudaGetLastError(); cudaHostUnregister(host); if (registered_here) *registered_here = 0; return fail(-2, "cudaHostGetDevicePointer", ce); }
+    }
+    *dev_view = d;
+    return 0;
+}
 int rtb_host_register(void* host, size_t nbytes) {
     CU(cudaHostRegister(host, nbytes, cudaHostRegisterDefault), "cudaHostRegister");
     return 0;
 }
 int rtb_host_unregister(void* host) {
-    CU(cudaHostUnregister(host), "cudaHostUnregister");
+    cudaError_t ce = cudaHostUnregister(host);
+    if (ce != cudaSuccess) { (void)cudaGetLastError(); return fail(-2, "cudaHostUnregister", ce); }
     return 0;
 }
 

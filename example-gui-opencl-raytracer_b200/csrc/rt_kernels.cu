@@ -93,11 +93,18 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
             uint32_t w3 = __shfl_down_sync(0xffffffffu, word, 3);
             uint32_t live3 = __shfl_down_sync(0xffffffffu, (uint32_t)live, 3);
             if ((lane & 3u) == 0u && live) {
-                if (live3) *reinterpret_cast<uint4*>(fp.out + at) = make_uint4(word, w1, w2, w3);
-                else { /* id >= total inside this quad: scalar tail */
+                if (live3) {
+                    *reinterpret_cast<uint4*>(fp.out + at) = make_uint4(word, w1, w2, w3);
+                    if (fp.mirror) __stcs(reinterpret_cast<uint4*>(fp.mirror + at), make_uint4(word, w1, w2, w3));
+                } else { /* id >= total inside this quad: scalar tail */
                     fp.out[at] = word;
                     if (id + 1 < fp.total) fp.out[at + 1] = w1;
                     if (id + 2 < fp.total) fp.out[at + 2] = w2;
+                    if (fp.mirror) {
+                        fp.mirror[at] = word;
+                        if (id + 1 < fp.total) fp.mirror[at + 1] = w1;
+                        if (id + 2 < fp.total) fp.mirror[at + 2] = w2;
+                    }
                 }
             }
             if (AOV && fp.hit) {
@@ -115,6 +122,7 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
             }
         } else if (live) {
             fp.out[at] = word;
+            if (fp.mirror) fp.mirror[at] = word;
             if (AOV && fp.hit) fp.hit[at] = hid;
         }
     }

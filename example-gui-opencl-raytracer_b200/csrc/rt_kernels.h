@@ -54,6 +54,8 @@ struct RtFrameParams {
     /* outputs (compact: local_rows x W) */
     uint32_t* out;
     uint32_t* hit; /* may be NULL */
+    uint32_t* mirror; /* may be NULL: second copy of `out` (mapped host memory: the frame lands in the caller's buffer
+                         while the kernel runs, 16 bytes per store, no D2H copy afterwards) */
     /* scheduling */
     unsigned int* tile_counter; /* zeroed before launch */
     const uint32_t* order;      /* queue slot -> tile (heaviest first), or NULL for row-major order */

@@ -12,6 +12,9 @@
  *   - raygen is fused into the raytracer launch: running kernel "raygen" latches its scalar arguments
  *     (camera basis, width, height), running "raytracer" renders; the ray buffer requested for raygen
  *     arg 8 is given a handle (drivers alias it into raytracer arg 0) but never materialised;
+ *   - read-back: when cl_wrap_output's host_output names the launch's own output slot, the
+ *     kernel also stores the frame straight into that host buffer (page-locked and mapped on its second use;
+ *     RTB_HOST_OUTPUT=copy|mirror|auto) so no D2H copy follows the render; the device slot still gets the frame;
  *   - cl_mem is a CUDA device pointer; cl_wrap.context holds the rtb_engine (include/rtb200.h),
  *     cl_wrap.program the wrapper's private slot table.
  */
@@ -61,6 +64,8 @@ void cl_wrap_release(cl_wrap* wrap);
 /* ---- extensions (not in the reference) ---- */
 /* The engine behind a wrapper, for the hit-id AOV, counters and timing (include/rtb200.h). */
 struct rtb_engine* cuda_wrap_engine(cl_wrap* wrap);
+/* How many read-backs were mirrored into the caller's buffer by the kernel / done as a D2H copy. */
+void cuda_wrap_readback_stats(cl_wrap* wrap, unsigned long* mirrored, unsigned long* copied);
 /* Device milliseconds of the last raytracer launch. */
 float cuda_wrap_last_kernel_ms(cl_wrap* wrap);
 

@@ -123,6 +123,13 @@ int rtb_dev_free(rtb_engine* e, void* dptr);
 int rtb_dev_write(rtb_engine* e, void* dptr, const void* host, size_t nbytes); /* blocking H2D */
 int rtb_dev_read(rtb_engine* e, void* host, const void* dptr, size_t nbytes);  /* blocking D2H */
 int rtb_host_register(void* host, size_t nbytes);   /* page-lock a caller buffer (optional fast path) */
+/* Device-visible view of a HOST buffer: page-locks and maps it unless it already is (cudaHostAlloc'ed or
+ * registered memory); *registered_here = 1 when this call did the registration (undo with rtb_host_unregister). */
+int rtb_host_map(void* host, size_t nbytes, void** dev_view, int* registered_here);
+/* One-shot: the NEXT rtb_render also writes every frame word to `mirror` (same compact layout as d_out; any
+ * device-visible pointer, typically an rtb_host_map view, so the frame is in the caller's host buffer when the
+ * kernel ends -- PCIe writes overlap the render, no D2H copy).  Cleared by that render.  16-byte aligned. */
+int rtb_set_mirror(rtb_engine* e, uint32_t* mirror);
 int rtb_host_unregister(void* host);
 
 /* Launch geometry the renderer chose for the last frame (for bench.py's accounting). */

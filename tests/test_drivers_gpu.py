@@ -81,3 +81,35 @@ print("not reached")
     print(r.stdout, r.stderr)
     assert r.returncode == 1
     assert "ERROR:\t" in r.stdout and "not reached" not in r.stdout
+
+
+@pytest.mark.parametrize("mode", ["auto", "copy", "mirror"])
+def test_readback_mirror_equals_copy(pkg, ref, scene, mode, monkeypatch):
+    """SURVEY.md 8(f) N1: from the second use of a host buffer the kernel stores the frame straight into it;
+    the words must be those of the plain D2H copy, and a new host buffer must start with a copy again."""
+    from example_gui_opencl_raytracer_b200.wrap_session import WrapSession
+    monkeypatch.setenv("RTB_HOST_OUTPUT", mode)
+    W, H = 640, 360
+    cam = ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA)
+    want, _ = (ref.ref() if ref.have_ref() else ref.port()).render(scene, cam, W, H, want_hit=False)
+    ses = WrapSession(W, H, scene.spheres, scene.planes, scene.lights, cam)
+    bufs = [np.zeros(W * H + 8, np.uint32) for _ in range(2)]
+    for b in bufs:
+        view = b[(-(b.ctypes.data // 4)) % 4:][:W * H]   # 16-byte aligned window
+        assert view.ctypes.data % 16 == 0
+        for _ in range(3):
+            view[:] = 0xFFFFFFFF
+            ses.frame(view.ctypes.data)
+            assert np.array_equal(view, want.astype(np.uint32))
+    stats = ses.readback_stats()
+    print(mode, stats)
+    assert stats == {"auto": {"mirrored": 4, "copied": 2}, "copy": {"mirrored": 0, "copied": 6},
+                     "mirror": {"mirrored": 6, "copied": 0}}[mode]
+    # an unaligned host pointer always takes the copy path
+    odd = np.zeros(W * H + 8, np.uint32)
+    v = odd[(-(odd.ctypes.data // 4)) % 4 + 1:][:W * H]
+    ses.frame(v.ctypes.data)
+    ses.frame(v.ctypes.data)
+    assert np.array_equal(v, want.astype(np.uint32))
+    assert ses.readback_stats()["copied"] == stats["copied"] + 2
+    ses.release()
