@@ -13,7 +13,7 @@ OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png
 
 all: $(PKG)/librtb200.so
 
-$(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
+$(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_coop.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels.ptxas.log || (cat $(CSRC)/rt_kernels.ptxas.log; false)
 	@grep -E "registers|spill" $(CSRC)/rt_kernels.ptxas.log | sort | uniq -c | sort -rn | head -20
 
@@ -29,9 +29,14 @@ $(CSRC)/png_io.o: $(CSRC)/png_io.c $(CSRC)/png_io.h
 $(PKG)/librtb200.so: $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lz
 
+# diagnostic build: per-tile wall time in the hit-id AOV (tools/exp/tile_times.py, RTB_LIB=...)
+timing: all
+	$(NVCC) $(NVFLAGS) $(KFLAGS) -DRT_TILE_TIMING -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_timing.o 2> /dev/null
+	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o -lz
+
 oracle:
 	$(MAKE) -C oracle
 
 clean:
 	rm -f $(OBJS) $(PKG)/librtb200.so $(CSRC)/*.ptxas.log
-.PHONY: all oracle clean
+.PHONY: all oracle clean timing

@@ -220,12 +220,30 @@ def run_gpu_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     pkg = entry.load_package()
+    eng = pkg.Engine(local)
+    try:
+        gpu_body(args, pkg, eng, world, rank, local)
+    finally:
+        # every tensor that touched the engine's stream or NCCL's is gone (gpu_body's locals) before either is torn down
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        eng.close()
+    return 0
+
+
+def gpu_body(args, pkg, eng, world, rank, local):
+    import torch
+    import torch.distributed as dist
     from example_gui_opencl_raytracer_b200 import host
     wl = make_workload(args.workload, host)
     W, H = wl["W"], wl["H"]
     tex, sky = host.default_images(ROOT)
 
-    eng = pkg.Engine(local)
     eng.upload_scene(wl["spheres"], wl["planes"], wl["lights"])
     eng.upload_images(0, tex)
     eng.upload_images(1, sky)
@@ -375,12 +393,7 @@ def run_gpu_arm(args):
         if world == 1 and not args.no_cpu:
             mrays, ms, cores, kind, sample, _ = cpu_time_frames(wl, 1, 0, budget_total_s=20.0)
             line["cpu_baseline"] = {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample}
-        print(json.dumps(line))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    eng.close()
-    return 0
+        print(json.dumps(line), flush=True)
 
 
 def e2e_cl_wrap(pkg, wl, args, host_frame):

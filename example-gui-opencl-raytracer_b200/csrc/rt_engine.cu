@@ -298,7 +298,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
 int rtb_render(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
                uint32_t* d_hit, int want_hit) {
     if (!e) return fail(-1, "null engine");
-    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, e->opt_trace ? 1 : 0, nullptr);
+    return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, e->opt_trace == 1 ? 1 : (e->opt_trace == 2 ? 3 : 0), nullptr);
 }
 int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part, uint32_t* d_out,
                        uint32_t* d_hit, int want_hit, int executed, uint64_t* counters) {
@@ -308,7 +308,7 @@ int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
 
 int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!e || !name) return fail(-1, "rtb_set_option: null argument");
-    if (!strcmp(name, "trace")) { e->opt_trace = value ? 1 : 0; return 0; }
+    if (!strcmp(name, "trace")) { e->opt_trace = (value == 1 || value == 2) ? value : 0; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     return fail(-1, "rtb_set_option: unknown option");
 }

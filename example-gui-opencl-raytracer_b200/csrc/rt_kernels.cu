@@ -20,6 +20,7 @@
 
 #include "rt_device.cuh"
 #include "rt_trace_fast.cuh"
+#include "rt_trace_coop.cuh"
 #include "rt_trace_literal.cuh"
 
 namespace rt {
@@ -29,10 +30,12 @@ namespace rt {
 #endif
 extern __shared__ __align__(128) unsigned char rt_smem[];
 
-/* MODE: 0 = fast, 1 = literal + counters (reference accounting), 2 = fast + counters (executed work) */
+/* MODE: 0 = cooperative trace (production), 1 = literal + counters (reference accounting), 2 = cooperative +
+ * counters (executed work), 3 = per-lane fast trace (the previous production path, kept for A/B) */
 template <bool RESIDENT, int MODE, bool AOV>
 __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __grid_constant__ RtFrameParams fp) {
-    constexpr bool COUNT = MODE != 0;
+    constexpr bool COUNT = MODE == 1 || MODE == 2;
+    constexpr bool COOP = MODE == 0 || MODE == 2;
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
     Geo g;
@@ -59,6 +62,13 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31u;
+    CoopSmem cs;
+    {
+        unsigned char* base = rt_smem + (RESIDENT ? fp.lay.total * 16u : 0u) + (threadIdx.x >> 5) * kCoopBytesPerWarp;
+        cs.owner = reinterpret_cast<float4*>(base);
+        cs.task = cs.owner + 32;
+        cs.light = cs.task + kCoopTasks;
+    }
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
     const bool vec_store = (fp.W % 4u) == 0u; /* rows are 16-byte aligned */
     Tally<COUNT> tl;
@@ -80,11 +90,24 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
         const bool live = x < fp.W && lr < fp.local_rows && y < fp.H && id < fp.total;
 
         uint32_t word = 0, hid = 0;
-        if (live) {
+#ifdef RT_TILE_TIMING /* diagnostic build: the hit-id AOV carries each tile's wall time in ns (tools/exp/tile_times.py) */
+        unsigned long long t_begin;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
+#endif
+        if (COOP) {
+            word = trace_tile_coop<COUNT, AOV>(fp, g, cs, id, live, lane, hid, tl);
+        } else if (live) {
             if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);
             else word = trace_pixel_fast<COUNT, AOV>(fp, g, id, hid, tl);
         }
         __syncwarp();
+#ifdef RT_TILE_TIMING
+        {
+            unsigned long long t_end;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+            hid = (uint32_t)(t_end - t_begin);
+        }
+#endif
 
         const size_t at = (size_t)lr * fp.W + x;
         if (vec_store) { /* lanes 0 and 4 of each tile row store 4 pixels = 16 bytes */
@@ -409,11 +432,12 @@ cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cu
     const uint32_t blob_bytes = fp.lay.total * 16u;
     /* keep the geometry resident while it leaves room for >= 2 CTAs per SM */
     const bool resident = blob_bytes <= 96u * 1024u;
-    const uint32_t smem = resident ? blob_bytes : 0u;
+    const bool coop = mode == 0 || mode == 2;
+    const uint32_t smem = (resident ? blob_bytes : 0u) + (coop ? (kBlock / 32) * kCoopBytesPerWarp : 0u);
     const bool aov = fp.hit != nullptr;
 #define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape)
 #define RT_GO_A(R, M) do { if (aov) RT_GO(R, M, true); else RT_GO(R, M, false); } while (0)
-#define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else RT_GO_A(R, 2); } while (0)
+#define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else RT_GO_A(R, 3); } while (0)
     if (resident) RT_GO_M(true);
     else RT_GO_M(false);
 #undef RT_GO

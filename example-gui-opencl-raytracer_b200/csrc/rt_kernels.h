@@ -71,8 +71,8 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
 struct RtLaunchShape {
     uint32_t grid, block, smem_bytes, resident;
 };
-/* Launches the fused raygen+raytracer kernel.  mode: 0 = fast trace, 1 = literal trace + reference work
- * counters, 2 = fast trace + executed-work counters.  Geometry is staged in shared memory when it fits. */
+/* Launches the fused raygen+raytracer kernel.  mode: 0 = cooperative trace, 1 = literal trace + reference work
+ * counters, 2 = cooperative trace + executed-work counters, 3 = per-lane fast trace.  Geometry is staged in shared memory when it fits. */
 cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
 
 /* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[128] (zeroed here), d_order[ntiles]. */

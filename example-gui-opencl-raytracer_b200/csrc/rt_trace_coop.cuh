@@ -1,0 +1,246 @@
+/* rt_trace_coop.cuh -- the production trace: warp-cooperative shadow rays.
+ *
+ * Same pixel words as rt_trace_fast.cuh / rt_trace_literal.cuh (and the oracle); what changes is WHO runs the
+ * shadow rays.  Measured on render.map at 4K (tools/exp/tile_times.py): with one pixel per lane from start to
+ * finish, the slowest 8x4 tile (a glass-sphere pixel with >1000 segments) runs for 2.15 ms of a 2.66 ms
+ * kernel, and lanes whose segment ended on the sky or a light idle while their neighbours trace 2L shadow
+ * rays.  Shadow rays are 3/4 of all tests and independent of one another, so here the warp
+ * walks its tile in lock step, one segment per live lane per round:
+ *   A  (per lane)  closest hit, classification, material, ambient term; per light of a chunk of <= 4 lights:
+ *                  shading geometry, the four RNG draws (raytracing.cl:99-100), and -- unless the light's
+ *                  terms are exact zeros (R5) -- two shadow TASKS {theta, phi, light, owner lane} appended to
+ *                  the warp's task list in shared memory (positions from ballots);
+ *   B  (warp)      tasks are dealt round-robin to ALL 32 lanes, finished pixels included: sample point on
+ *                  the light (bounded sincos), testShadowPath, opacity written back into the task slot;
+ *   C  (per lane)  the owner folds its opacities into rgb in the reference's order (light by light, specular
+ *                  then diffuse), then Fresnel / reflection / refraction child as before.
+ * A task's value does not depend on which lane computes it (same routine, same operands), so the words are
+ * identical; the per-pixel RNG stream is drawn by the owner in the reference's order.
+ * Shared memory per warp: 32 owner records (hit point) + 256 task slots + 4x32 light records, 16 bytes each = 6.5 KiB.
+ */
+#pragma once
+#include "rt_trace_fast.cuh"
+
+namespace rt {
+
+constexpr int kCoopLights = 4;                                   /* lights per chunk */
+constexpr int kCoopTasks = 32 * kCoopLights * kShadowSamples;    /* 256 */
+constexpr uint32_t kCoopBytesPerWarp = 32 * 16 + kCoopTasks * 16 + 32 * kCoopLights * 16; /* 6656 */
+
+struct CoopSmem {
+    float4* owner; /* [32] {ip.xyz, -} */
+    float4* task;  /* [kCoopTasks] {theta, phi, light (bits), owner lane (bits)}; .x becomes the opacity */
+    float4* light; /* [kCoopLights][32] per owner and light of the chunk: {dist, max(0,n.h), max(0,n.l), flags | slot << 8} */
+};
+
+/* Phase B for one task. */
+template <bool COUNT>
+__device__ __forceinline__ float coop_run_task(const Geo& g, const CoopSmem& cs, float4 tk, Tally<COUNT>& tl) {
+    const uint32_t li = __float_as_uint(tk.z), ow = __float_as_uint(tk.w);
+    const float4 l0 = g.lgeo[li];
+    const float radius = g.laux[li].w;
+    const float4 ipo = cs.owner[ow];
+    float sp, cp, sth, cth;
+    sincos_bounded(tk.y, sp, cp);
+    sincos_bounded(tk.x, sth, cth);
+    const float rs = radius * sp;
+    const V3 sample = xyz(l0) + mk(rs * cth, rs * sth, radius * cp); /* raytracing.cl:101-106 */
+    return shadow_path_fast(sample, xyz(ipo), g, tl);
+}
+
+/* One 8x4 tile, all 32 lanes in lock step.  `live` = this lane owns a pixel of the frame.  Returns the pixel word. */
+template <bool COUNT, bool AOV>
+__device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, const Geo& g, const CoopSmem& cs, uint32_t id,
+                                                    bool live, uint32_t lane, uint32_t& hit_id, Tally<COUNT>& tl) {
+    constexpr uint32_t kFull = 0xffffffffu;
+    Saved st[kMaxDepth - 1];
+    uint32_t rng = id; /* raytracing.cl:32-33 */
+    uint32_t sz = 1;
+    V3 o = mk(0.0f, 0.0f, 0.0f), d = mk(0.0f, 0.0f, 1.0f), rgb = mk(0.0f, 0.0f, 0.0f);
+    if (live) primary_ray(fp, id, o, d);
+    int depth = 0;
+    float n_cur = kAirN, f = 1.0f;
+    bool first = true, done = !live;
+    if (AOV) hit_id = 0;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t L = g.L;
+
+    for (;;) {
+        if (!done) {
+            while (depth >= kMaxDepth) { /* entry finished: fold it into its parent (raytracing.cl:183-190) */
+                if (sz == 1) { done = true; break; }
+                const Saved& p = st[sz - 2];
+                rgb = p.rgb + rgb;
+                o = p.o; d = p.d; depth = p.depth; n_cur = p.n; f = p.f;
+                sz--;
+            }
+        }
+        if (__all_sync(kFull, done)) break;
+
+        /* ---- phase A: this lane's segment up to the direct-light loop ---- */
+        bool shade = false;
+        V3 ip = mk(0.0f, 0.0f, 0.0f), nrm = ip, vv = ip;
+        Material m;
+        m.shininess = 0; m.transperent = 0; m.dielectric = 0;
+        m.n = 1.0f; m.reflectivity = 0.0f; m.specular = 0.0f; m.diffuse = 0.0f;
+        if (!done) {
+            tl.add(RTB_SEGMENTS);
+            RayF r;
+            ray_setup_fast(r, o, d);
+            Closest c;
+            closest_pass(r, g, tl, c);
+            if (c.k >= 0 && !c.occluded) { /* a visible light ends the chain, raytracing.cl:48-54 */
+                V3 lp = o + d * c.tL;
+                V3 od = o - lp;
+                float dd = sqrtf(dot3(od, od));
+                V3 col = xyz(g.laux[c.k]) * (1.0f / dd * dd); /* (1/d)*d, primitives.cl:288 */
+                rgb = rgb + col * f;
+                if (AOV && first) hit_id = RTB_HIT_LIGHT | (uint32_t)c.k;
+                depth = kMaxDepth;
+            } else if (c.who < 0 && c.whop < 0) { /* skybox, raytracing.cl:61-81 */
+                int u, v;
+                cube_uv(d, (uint32_t)(fp.sw / 4), u, v);
+                tl.add(RTB_TEXELS);
+                V3 px = texel_rgb(fp.sky, fp.sw, fp.sh, 1, u, fp.sh - v, 0, g.lut255);
+                rgb = rgb + px * f;
+                depth = kMaxDepth;
+            } else {
+                shade = true;
+                ip = o + d * c.t;
+                if (c.whop >= 0) {
+                    nrm = xyz(g.pln[4 * c.whop]);
+                    m = load_material(fp.raw_planes + (size_t)c.whop * RT_PLANE_BYTES);
+                    if (m.texture_id >= 0) { /* primitives.cl:217-259; sampled once, for the plane that won */
+                        float4 b0 = g.pln[4 * c.whop + 2], b1 = g.pln[4 * c.whop + 3];
+                        float ui = dot3(xyz(b0), ip) * m.texture_scale;
+                        float vi = dot3(xyz(b1), ip) * m.texture_scale;
+                        tl.add(RTB_TEXELS);
+                        m.rgb = texel_rgb(fp.tex, fp.tw, fp.th, fp.tl, emod(f2i_x86(ui), fp.tw), emod(f2i_x86(vi), fp.th),
+                                          m.texture_id, g.lut255);
+                    }
+                    if (AOV && first) hit_id = 1u + g.S + (uint32_t)c.whop;
+                } else {
+                    float qlen;
+                    nrm = normalize_len(ip - xyz(g.sph[c.who]), qlen);
+                    m = load_material(fp.raw_spheres + (size_t)c.who * RT_SPHERE_BYTES);
+                    if (AOV && first) hit_id = 1u + (uint32_t)c.who;
+                }
+                ip = ip + nrm * kEps;
+                rgb = rgb + (m.rgb * f) * m.ambient; /* raytracing.cl:83-84 */
+                float vlen;
+                vv = normalize_len(o - ip, vlen);
+            }
+            first = false;
+        }
+
+        /* ---- direct light, raytracing.cl:87-136, in chunks of kCoopLights lights (L is warp-uniform) ---- */
+        if (__any_sync(kFull, shade)) {
+            const float shin = (float)m.shininess;
+            const float fs = f * m.specular, fd = f * m.diffuse;
+            if (shade) cs.owner[lane] = make_float4(ip.x, ip.y, ip.z, 0.0f);
+            for (uint32_t c0 = 0; c0 < L; c0 += kCoopLights) {
+                const uint32_t nk = L - c0 < (uint32_t)kCoopLights ? L - c0 : (uint32_t)kCoopLights; /* warp-uniform */
+                uint32_t ntask = 0;
+#pragma unroll 1
+                for (uint32_t k = 0; k < nk; k++) {
+                    const uint32_t i = c0 + k;
+                    bool post = false;
+                    float th0 = 0.0f, ph0 = 0.0f, th1 = 0.0f, ph1 = 0.0f;
+                    float dist = 1.0f, sx = 0.0f, dif = 0.0f;
+                    uint32_t bits = 0; /* bit 0: tasks posted; bit 1: spec_zero; bit 2: diff_zero; bits 8..: first task slot */
+                    if (shade) {
+                        const float4 l0 = g.lgeo[i];
+                        V3 sdir = normalize_len(xyz(l0) - ip, dist);
+                        float hlen;
+                        V3 hh = normalize_len(vv + sdir, hlen);
+                        float ndh = dot3(nrm, hh);
+                        sx = 0.0f < ndh ? ndh : 0.0f;
+                        float ndl = dot3(nrm, sdir);
+                        dif = 0.0f < ndl ? ndl : 0.0f;
+                        /* R5: exact zeros */
+                        const bool spec_zero = (fs == 0.0f) || (sx == 0.0f && shin > 0.0f);
+                        const bool diff_zero = (fd == 0.0f) || (dif == 0.0f);
+                        if (spec_zero) bits |= 2u;
+                        if (diff_zero) bits |= 4u;
+                        if (spec_zero && diff_zero) {
+                            rng = xorshift_step(xorshift_step(xorshift_step(xorshift_step(rng)))); /* 2 samples x 2 draws */
+                            tl.add(RTB_SHADOW_SKIPPED, kShadowSamples);
+                        } else {
+                            th0 = (float)(kTwoPi * (double)rng_next(rng));
+                            ph0 = (float)(kPi * (double)rng_next(rng));
+                            th1 = (float)(kTwoPi * (double)rng_next(rng));
+                            ph1 = (float)(kPi * (double)rng_next(rng));
+                            post = true;
+                        }
+                    }
+                    const uint32_t mask = __ballot_sync(kFull, post);
+                    if (post) {
+                        const uint32_t a = ntask + 2u * (uint32_t)__popc(mask & lt);
+                        bits |= 1u | (a << 8);
+                        cs.task[a] = make_float4(th0, ph0, __uint_as_float(i), __uint_as_float(lane));
+                        cs.task[a + 1] = make_float4(th1, ph1, __uint_as_float(i), __uint_as_float(lane));
+                    }
+                    if (shade) cs.light[k * 32u + lane] = make_float4(dist, sx, dif, __uint_as_float(bits));
+                    ntask += 2u * (uint32_t)__popc(mask);
+                }
+                __syncwarp();
+                /* ---- phase B: every lane, finished or not, takes tasks ---- */
+#pragma unroll 1
+                for (uint32_t t = lane; t < ntask; t += 32u) {
+                    const float4 tk = cs.task[t];
+                    const float op = coop_run_task(g, cs, tk, tl);
+                    reinterpret_cast<float*>(cs.task + t)[0] = op;
+                }
+                __syncwarp();
+                /* ---- phase C: owners fold their lights in, in order ---- */
+                if (shade) {
+#pragma unroll 1
+                    for (uint32_t k = 0; k < nk; k++) {
+                        const float4 rec = cs.light[k * 32u + lane];
+                        const uint32_t bits = __float_as_uint(rec.w);
+                        if (!(bits & 1u)) continue;
+                        const uint32_t a = bits >> 8;
+                        const float r0 = reinterpret_cast<const float*>(cs.task + a)[0];
+                        const float r1 = reinterpret_cast<const float*>(cs.task + a + 1)[0];
+                        const float soft = (0.0f + r0) + r1;
+                        if (soft == 0.0f) continue; /* light_rgb *= 0: both terms are exact zeros */
+                        const float ssr = soft / (float)kShadowSamples;
+                        const float4 l1 = g.laux[c0 + k];
+                        V3 lrgb = div3_pos(xyz(l1) * 1.0f, rec.x * rec.x) * ssr;
+                        if (!(bits & 2u)) rgb = rgb + (lrgb * fs) * pow_ieee(rec.y, shin);
+                        if (!(bits & 4u)) rgb = rgb + (lrgb * fd) * rec.z;
+                    }
+                }
+                __syncwarp(); /* the next chunk / round reuses the task slots */
+            }
+        }
+
+        /* ---- Fresnel, reflection, refraction child (raytracing.cl:138-179) ---- */
+        if (shade) {
+            V3 incident = d;
+            float n1 = n_cur;
+            float n2 = (n1 == kAirN) ? m.n : kAirN;
+            float cosI = -dot3(nrm, incident);
+            float refl = reflect_amount(m, n1, n2, cosI);
+            float old_f = f;
+            f *= refl;
+            d = incident + nrm * (2.0f * cosI); /* primitives.cl:127-130 */
+            o = ip;
+            depth++;
+            if (m.transperent && sz < (uint32_t)kMaxDepth && refl < 1.0f) {
+                V3 co, cd;
+                if (refract_child(o, nrm, incident, n1, n2, co, cd)) {
+                    Saved& p = st[sz - 1];
+                    p.o = o; p.d = d; p.rgb = rgb; p.depth = depth; p.n = n_cur; p.f = f;
+                    sz++;
+                    o = co; d = cd; rgb = mk(0.0f, 0.0f, 0.0f);
+                    f = old_f * (1.0f - refl);
+                    n_cur = n2;
+                }
+            }
+        }
+    }
+    return pack_rgb(rgb);
+}
+
+}  // namespace rt
