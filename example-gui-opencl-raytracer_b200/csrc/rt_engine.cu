@@ -70,7 +70,7 @@ struct rtb_engine {
 
     DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
     DevBuf tile_cost, tile_order, tile_hist;
-    int opt_trace = 0, opt_tile_order = 1;
+    int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0;
     uint32_t* mirror = nullptr; /* one-shot, see rtb_set_mirror */
     rtb_launch_info last{};
 };
@@ -271,6 +271,8 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     CU(cudaEventRecord(e->ev0, e->stream), "event record");
     CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter");
     fp.order = nullptr;
+    fp.cost = nullptr;
+    fp.coop_min_cost = (uint32_t)e->opt_coop_min_cost;
     if (e->opt_tile_order && e->last.tiles >= 4096) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
         if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 4) || e->tile_hist.ensure(1024)) return -2;
@@ -278,6 +280,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                                 e->stream),
            "tile_order launch");
         fp.order = (const uint32_t*)e->tile_order.p;
+        fp.cost = (const uint32_t*)e->tile_cost.p;
     }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
@@ -309,6 +312,7 @@ int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
 int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!e || !name) return fail(-1, "rtb_set_option: null argument");
     if (!strcmp(name, "trace")) { e->opt_trace = (value == 1 || value == 2) ? value : 0; return 0; }
+    if (!strcmp(name, "coop_min_cost")) { e->opt_coop_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     return fail(-1, "rtb_set_option: unknown option");
 }

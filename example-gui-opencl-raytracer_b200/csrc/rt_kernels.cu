@@ -94,7 +94,10 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
         unsigned long long t_begin;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
 #endif
-        if (COOP) {
+        /* hybrid: the cooperative walk shortens the heavy tiles (glass, mirrors) that bound the kernel's tail; the
+         * per-lane walk has less lock-step overhead on the cheap majority.  Same words either way. */
+        const bool heavy = COOP && (!fp.cost || __ldg(fp.cost + tile) >= fp.coop_min_cost);
+        if (heavy) {
             word = trace_tile_coop<COUNT, AOV>(fp, g, cs, id, live, lane, hid, tl);
         } else if (live) {
             if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);

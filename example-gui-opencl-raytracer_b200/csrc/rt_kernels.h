@@ -60,6 +60,8 @@ struct RtFrameParams {
     unsigned int* tile_counter; /* zeroed before launch */
     const uint32_t* order;      /* queue slot -> tile (heaviest first), or NULL for row-major order */
     uint32_t tiles_x, tiles_y;
+    const uint32_t* cost;       /* per-tile cost estimate (tile_cost), or NULL */
+    uint32_t coop_min_cost;     /* tiles whose estimate reaches this walk in cooperative mode, the rest lane per pixel */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
 };
 

@@ -92,7 +92,9 @@ int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                        uint32_t* d_out, uint32_t* d_hit, int want_hit, int executed, uint64_t* counters);
 
 /* Engine options.  "trace": 0 = production trace (warp-cooperative shadow rays; default), 1 = literal trace
- * (reference control flow; same pixels, slower), 2 = per-lane fast trace (same pixels; the previous production path).  "tile_order": 1 = cost-ordered tile queue (default), 0 = row-major queue. */
+ * (reference control flow; same pixels, slower), 2 = per-lane fast trace (same pixels; the previous production path).  "tile_order": 1 = cost-ordered tile queue (default), 0 = row-major queue.
+ * "coop_min_cost": tiles whose cost estimate (0..63) reaches this value use the cooperative walk, cheaper tiles the
+ * per-lane walk (0 = all cooperative, 64 = none; scheduling only, pixels do not change). */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
 /* Brute-force check of the arithmetic routines against IEEE division / sqrt (trials per thread on 592x256
  * threads).  out[0] = division mismatches, out[1] = normalize mismatches, out[2] = max |sincos - libdevice|
