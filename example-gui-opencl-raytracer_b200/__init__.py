@@ -27,7 +27,7 @@ ENGINE_SYMBOLS = (
     "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
-    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_last_launch", "rtb_fp32_peak_tflops",
+    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops",
 )
 WRAP_SYMBOLS = (
     "cl_wrap_init", "cl_wrap_load_global_data", "cl_wrap_load_single_data", "cl_wrap_load_images", "cl_wrap_output",
@@ -92,6 +92,7 @@ def lib():
             "rtb_host_unregister": (i, [vp]),
             "rtb_host_map": (i, [vp, sz, C.POINTER(vp), C.POINTER(i)]),
             "rtb_set_mirror": (i, [vp, vp]),
+            "rtb_assemble_bands": (i, [vp, vp, sz, vp, u32, u32, u32, u32]),
             "rtb_last_launch": (i, [vp, C.POINTER(LaunchInfo)]),
             "rtb_fp32_peak_tflops": (C.c_double, [vp, i]),
         }
@@ -182,6 +183,11 @@ class Engine:
         c["rays"] = c["segments"] + c["shadow_rays"]
         c["flop"] = algorithmic_flop(c)
         return c
+
+    def assemble_bands(self, d_compact, stride_words, d_frame, W, H, band_rows, parts):
+        """Gathering rank: compact band buffers -> row-major frame (one kernel on the engine's stream)."""
+        _check(lib().rtb_assemble_bands(self._h, C.c_void_p(d_compact), stride_words, C.c_void_p(d_frame), W, H, band_rows,
+                                        parts), "rtb_assemble_bands")
 
     def sync(self):
         _check(lib().rtb_sync(self._h), "rtb_sync")

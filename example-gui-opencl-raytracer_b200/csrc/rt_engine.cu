@@ -309,6 +309,17 @@ int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     return render_impl(e, W, H, total, part, d_out, d_hit, want_hit, executed ? 2 : 1, counters);
 }
 
+int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W,
+                       uint32_t H, uint32_t band_rows, uint32_t parts) {
+    if (!e || !d_compact || !d_frame) return fail(-1, "rtb_assemble_bands: null argument");
+    if (!W || !H || !band_rows || !parts) return fail(-1, "rtb_assemble_bands: bad geometry");
+    rtb_partition p0 = {band_rows, parts, 0};
+    if ((size_t)rtb_partition_rows(H, &p0) * W > stride_words) return fail(-1, "rtb_assemble_bands: stride smaller than a part");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(rt_launch_assemble_bands(d_compact, stride_words, d_frame, W, H, band_rows, parts, e->stream), "assemble_bands launch");
+    return 0;
+}
+
 int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!e || !name) return fail(-1, "rtb_set_option: null argument");
     if (!strcmp(name, "trace")) { e->opt_trace = (value == 1 || value == 2) ? value : 0; return 0; }

@@ -310,6 +310,23 @@ __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __
     if (tile < ntiles) order[base[c] + gbase[c] + rank] = tile;
 }
 
+/* Row-band re-interleave on the gathering rank: `compact` holds `parts` band buffers of
+ * `stride` words each (what the gather delivers); frame row y comes from part (y / band_rows) % parts.
+ * One uint4 (4 pixels) per thread when W % 4 == 0. */
+__global__ void assemble_bands(const uint32_t* __restrict__ compact, size_t stride, uint32_t* __restrict__ frame,
+                               uint32_t W, uint32_t H, uint32_t band_rows, uint32_t parts) {
+    const uint32_t wq = (W + 3u) / 4u;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)wq * H) return;
+    const uint32_t y = (uint32_t)(i / wq), xq = (uint32_t)(i % wq);
+    const uint32_t b = y / band_rows, r = b % parts;
+    const uint32_t lr = (b / parts) * band_rows + y % band_rows;
+    const uint32_t* src = compact + (size_t)r * stride + (size_t)lr * W + 4u * xq;
+    uint32_t* dst = frame + (size_t)y * W + 4u * xq;
+    if ((W & 3u) == 0u && (stride & 3u) == 0u) *reinterpret_cast<uint4*>(dst) = __ldcs(reinterpret_cast<const uint4*>(src));
+    else for (uint32_t k = 0; k < 4u && 4u * xq + k < W; k++) dst[k] = src[k];
+}
+
 /* FP32 pipe calibration: 8 independent FMA chains per thread. */
 __global__ void fma_peak(float* sink, int iters) {
     float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.0f, a2 = a0 + 2.0f, a3 = a0 + 3.0f;
@@ -447,6 +464,13 @@ cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cu
 #undef RT_GO_A
 #undef RT_GO_M
     return cudaErrorInvalidValue;
+}
+
+cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W, uint32_t H,
+                                     uint32_t band_rows, uint32_t parts, cudaStream_t st) {
+    const size_t n = (size_t)((W + 3u) / 4u) * H;
+    assemble_bands<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_compact, stride_words, d_frame, W, H, band_rows, parts);
+    return cudaGetLastError();
 }
 
 cudaError_t rt_launch_fma_peak(float* d_sink, int iters, int blocks, int threads, cudaStream_t st) {

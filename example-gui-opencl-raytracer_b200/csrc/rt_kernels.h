@@ -84,3 +84,7 @@ cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint
 cudaError_t rt_launch_fma_peak(float* d_sink, int iters, int blocks, int threads, cudaStream_t st);
 /* d_out[3] (zeroed by the caller): division mismatches, normalize mismatches, max sincos deviation in 2^-24 units */
 cudaError_t rt_launch_arith_selftest(uint32_t seed, uint32_t per_thread, uint32_t* d_out, cudaStream_t st);
+
+/* Gathering rank: compact per-part band buffers (parts x stride_words) -> row-major frame. */
+cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W, uint32_t H,
+                                     uint32_t band_rows, uint32_t parts, cudaStream_t st);

@@ -91,6 +91,11 @@ int rtb_render(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_
 int rtb_render_counted(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part,
                        uint32_t* d_out, uint32_t* d_hit, int want_hit, int executed, uint64_t* counters);
 
+/* On the gathering rank: re-interleave `parts` compact band buffers (part r at d_compact + r*stride_words, as the
+ * gather delivers them; stride_words >= rows of part 0 x W) into the row-major H x W frame, on the engine's stream. */
+int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W,
+                       uint32_t H, uint32_t band_rows, uint32_t parts);
+
 /* Engine options.  "trace": 0 = production trace (warp-cooperative shadow rays; default), 1 = literal trace
  * (reference control flow; same pixels, slower), 2 = per-lane fast trace (same pixels; the previous production path).  "tile_order": 1 = cost-ordered tile queue (default), 0 = row-major queue.
  * "coop_min_cost": tiles whose cost estimate (0..63) reaches this value use the cooperative walk, cheaper tiles the

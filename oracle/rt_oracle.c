@@ -29,6 +29,10 @@ typedef struct { float origin[4]; float radius; uint32_t pad[3]; w_material m; }
 typedef struct { float normal[4]; float point[4]; w_material m; } w_plane;                 /* 96 B */
 typedef struct { float origin[4]; float radius, intensity; uint32_t pad[2]; float rgb[4]; } w_light; /* 48 B */
 
+/* EXTENSION X1 (SURVEY.md 8(a'), no counterpart in the reference): a triangle record, 112 B. */
+typedef struct { float v0[4], v1[4], v2[4]; w_material m; } w_triangle;
+_Static_assert(sizeof(w_triangle) == 112, "rtriangle");
+
 _Static_assert(sizeof(w_material) == 64, "rmaterial");
 _Static_assert(sizeof(w_sphere) == 96, "rsphere");
 _Static_assert(sizeof(w_plane) == 96, "rplane");
@@ -48,7 +52,12 @@ typedef struct {
     const w_light* lit; uint32_t L;
     const uint8_t* tex; int tw, th, tl;
     const uint8_t* sky; int sw, sh;
+    const w_triangle* tri; uint32_t T; /* extension X1 */
 } scene_t;
+
+/* Extension X1: triangles for the NEXT rto_render* calls (process-global so the reference-shaped signatures stay). */
+static const w_triangle* g_tri = 0;
+static uint32_t g_T = 0;
 
 /* ---------- vector helpers: each component op is one rounded binary32 operation ---------- */
 static inline v3 mk(float x, float y, float z) { v3 r = {x, y, z}; return r; }
@@ -180,6 +189,28 @@ static inline int hit_plane(v3 o, v3 d, v3 n, v3 p, float* t) {
     return 1;
 }
 
+/* EXTENSION X1 -- no reference code: Moeller-Trumbore, two-sided, every step one rounded binary32 operation in
+ * this order.  The CUDA kernels restate exactly this sequence.  Parity for scenes with triangles is therefore
+ * SELF-CONSISTENCY ONLY ("parity unpinned"). */
+static inline int hit_triangle(v3 o, v3 d, v3 v0, v3 e1, v3 e2, float* t) {
+    COUNT(RTO_TRI_TESTS);
+    v3 p = cross3(d, e2);
+    float det = dot3(e1, p);
+    if (det == 0) return 0;
+    float inv = 1.0f / det;
+    v3 s = sub(o, v0);
+    float u = dot3(s, p) * inv;
+    if (u < 0 || u > 1) return 0;
+    v3 q = cross3(s, e1);
+    float v = dot3(d, q) * inv;
+    if (v < 0 || u + v > 1) return 0;
+    float t2 = dot3(e2, q) * inv;
+    if (t2 <= 0) return 0;
+    *t = t2;
+    return 1;
+}
+#define TRI_EDGES(tr) v3 v0_ = ld3((tr)->v0), e1_ = sub(ld3((tr)->v1), v0_), e2_ = sub(ld3((tr)->v2), v0_)
+
 /* ref: primitives.cl:217-259.  Tangent basis = first unit axis e with sum(cross(e, n)) != 0 (Q16);
  * if none qualifies the reference reads an uninitialised basis -- defined here (and in cl_shim.hpp,
  * whose float3 default-constructs to zero) as the zero vectors. */
@@ -228,6 +259,11 @@ static int find_light(v3 o, v3 d, const scene_t* sc, v3* color, uint32_t* which)
         float t1;
         if (hit_plane(o, d, ld3(p->normal), ld3(p->point), &t1) && t1 <= t) return 0;
     }
+    for (uint32_t i = 0; i < sc->T; i++) { /* X1: triangles occlude like planes */
+        TRI_EDGES(&sc->tri[i]);
+        float t1;
+        if (hit_triangle(o, d, v0_, e1_, e2_, &t1) && t1 <= t) return 0;
+    }
     *color = col;
     if (which) *which = k;
     return 1;
@@ -269,6 +305,18 @@ static int find_solid(v3 o, v3 d, const scene_t* sc, v3* ip_out, v3* n_out, w_ma
         got = 1;
         who = 1 + sc->S + j;
     }
+    for (uint32_t k = 0; k < sc->T; k++) { /* X1: after the planes, same strict rejection; normal = unit(e1 x e2), not flipped */
+        TRI_EDGES(&sc->tri[k]);
+        float t1;
+        if (!hit_triangle(o, d, v0_, e1_, e2_, &t1) || t1 >= t) continue;
+        t = t1;
+        ip = add(o, scl(d, t));
+        nrm = unit(cross3(e1_, e2_));
+        ip = add(ip, scl(nrm, EPS_OFFSET));
+        m = sc->tri[k].m;
+        got = 1;
+        who = 1 + sc->S + sc->P + k;
+    }
     if (!got) return 0;
     *ip_out = ip; *n_out = nrm; *m_out = m;
     if (id) *id = who;
@@ -292,6 +340,12 @@ static float shadow_path(v3 to, v3 from, const scene_t* sc) {
         const w_plane* p = &sc->pln[j];
         float t1;
         if (!hit_plane(from, d, ld3(p->normal), ld3(p->point), &t1) || t1 >= t) continue;
+        return 0.0f;
+    }
+    for (uint32_t k = 0; k < sc->T; k++) { /* X1 */
+        TRI_EDGES(&sc->tri[k]);
+        float t1;
+        if (!hit_triangle(from, d, v0_, e1_, e2_, &t1) || t1 >= t) continue;
         return 0.0f;
     }
     return opacity;
@@ -445,7 +499,7 @@ int rto_render_counted(int wide, const float* cam, uint32_t W, uint32_t H, uint3
     if (!wide && (S > 255 || P > 255 || L > 255)) return -1;   /* uchar counts, ref: raytracing.cl:17 */
     if (y1 > H || y0 > y1 || W == 0) return -1;
     scene_t sc = {(const w_sphere*)spheres, S, (const w_plane*)planes, P, (const w_light*)lights, L,
-                  tex, tw, th, tl, sky, sw, sh};
+                  tex, tw, th, tl, sky, sw, sh, g_tri, g_T};
     if (threads < 1) threads = 1;
     if (threads > 256) threads = 256;
     volatile uint32_t next = y0;
@@ -467,6 +521,12 @@ int rto_render_counted(int wide, const float* cam, uint32_t W, uint32_t H, uint3
     return 0;
 }
 
+void rto_set_triangles(const void* tris, uint32_t T) { g_tri = (const w_triangle*)tris; g_T = tris ? T : 0; }
+int rto_isect_triangle(const float* o, const float* d, const float* v0, const float* v1, const float* v2, float* t) {
+    v3 a = ld3(v0);
+    return hit_triangle(ld3(o), ld3(d), a, sub(ld3(v1), a), sub(ld3(v2), a), t);
+}
+
 int rto_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t y0, uint32_t y1, const void* spheres,
                uint32_t S, const void* planes, uint32_t P, const void* lights, uint32_t L, const uint8_t* tex,
                int tw, int th, int tl, const uint8_t* sky, int sw, int sh, uint32_t* out, uint32_t* hit,
@@ -480,7 +540,7 @@ int rto_segment_map(const float* cam, uint32_t W, uint32_t H, const void* sphere
                     uint32_t P, const void* lights, uint32_t L, const uint8_t* tex, int tw, int th, int tl,
                     const uint8_t* sky, int sw, int sh, uint32_t* seg) {
     scene_t sc = {(const w_sphere*)spheres, S, (const w_plane*)planes, P, (const w_light*)lights, L,
-                  tex, tw, th, tl, sky, sw, sh};
+                  tex, tw, th, tl, sky, sw, sh, g_tri, g_T};
     for (uint32_t id = 0; id < W * H; id++) {
         (void)trace_pixel(cam, W, id, &sc, 0);
         seg[id] = tl_pixel_segments;

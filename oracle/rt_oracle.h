@@ -28,6 +28,7 @@ enum {
     RTO_SPHERE_DPOS = 3,  /* ... of which reached the sqrt (D >= 0) */
     RTO_PLANE_TESTS = 4,  /* intersect_plane calls */
     RTO_TEXELS = 5,       /* read_imagei calls (plane texture + skybox) */
+    RTO_TRI_TESTS = 7,    /* EXTENSION X1: triangle tests (no reference counterpart) */
     RTO_NCOUNTERS = 8
 };
 
@@ -43,6 +44,12 @@ int rto_render_counted(int wide, const float* cam, uint32_t W, uint32_t H, uint3
                        const void* spheres, uint32_t S, const void* planes, uint32_t P, const void* lights,
                        uint32_t L, const uint8_t* tex, int tw, int th, int tl, const uint8_t* sky, int sw, int sh,
                        uint32_t* out, uint32_t* hit, int threads, uint64_t* counters);
+
+/* EXTENSION X1 (no reference counterpart; parity unpinned): triangle records (112 B: v0, v1, v2 as float4, then
+ * rmaterial) used by every later rto_render* call until reset with (NULL, 0).  Slotted after the planes in the
+ * three traversal loops; opaque; normal = normalize(cross(v1-v0, v2-v0)). */
+void rto_set_triangles(const void* tris, uint32_t T);
+int rto_isect_triangle(const float* o, const float* d, const float* v0, const float* v1, const float* v2, float* t);
 
 /* Segments traced per pixel (cost map for load-balance analysis; single-threaded). */
 int rto_segment_map(const float* cam, uint32_t W, uint32_t H, const void* spheres, uint32_t S, const void* planes,

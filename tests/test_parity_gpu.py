@@ -125,3 +125,23 @@ def test_executed_counters_are_consistent(engine, ref):
     print(lit, fast)
     assert fast["segments"] == lit["segments"]
     assert fast["shadow_rays"] + fast["shadow_skipped"] == lit["shadow_rays"]
+
+
+@pytest.mark.parametrize("W,H,parts,band", [(328, 250, 4, 8), (64, 37, 3, 5), (130, 64, 2, 8)])
+def test_assemble_bands_kernel(engine, ref, pkg, W, H, parts, band):
+    """The gathering rank's re-interleave kernel: parts rendered into one landing area -> the 1-part frame."""
+    engine.set_camera(ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA))
+    whole, _ = engine.render_to_host(W, H, want_hit=False)
+    rows = [engine.partition_rows(H, pkg.Partition(band, parts, r)) for r in range(parts)]
+    stride = max(rows) * W
+    stride += (-stride) % 4
+    landing = engine.dev_alloc(parts * stride * 4)
+    frame = engine.dev_alloc(W * H * 4)
+    for r in range(parts):
+        engine.render(W, H, part=pkg.Partition(band, parts, r), d_out=landing.value + r * stride * 4)
+    engine.assemble_bands(landing.value, stride, frame.value, W, H, band, parts)
+    engine.sync()
+    got = engine.dev_read(frame, W * H * 4).view(np.uint32)
+    engine.dev_free(landing)
+    engine.dev_free(frame)
+    assert np.array_equal(got, whole)
