@@ -18,13 +18,14 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTB_LIB") or os.path.join(HERE, "librtb200.so")  # RTB_LIB: A/B builds only
 
 HIT_LIGHT = 0x80000000
-COUNTER_NAMES = ("segments", "shadow_rays", "sphere_tests", "sphere_dpos", "plane_tests", "texels", "shadow_skipped")
+COUNTER_NAMES = ("segments", "shadow_rays", "sphere_tests", "sphere_dpos", "plane_tests", "texels", "shadow_skipped",
+                 "tri_tests")
 NCOUNTERS = 8
 
 # Every symbol include/rtb200.h and include/cuda_wrap.h declare (checked by tests/test_abi.py).
 ENGINE_SYMBOLS = (
     "rtb_last_error", "rtb_device_count", "rtb_create", "rtb_destroy", "rtb_upload_scene", "rtb_bind_scene_device",
-    "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
+    "rtb_upload_triangles", "rtb_bind_triangles_device", "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
     "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops",
@@ -68,6 +69,8 @@ def lib():
             "rtb_destroy": (None, [vp]),
             "rtb_upload_scene": (i, [vp, vp, u32, vp, u32, vp, u32]),
             "rtb_bind_scene_device": (i, [vp, vp, u32, vp, u32, vp, u32]),
+            "rtb_upload_triangles": (i, [vp, vp, u32]),
+            "rtb_bind_triangles_device": (i, [vp, vp, u32]),
             "rtb_upload_images": (i, [vp, i, vp, u32, u32, u32]),
             "rtb_bind_images_device": (i, [vp, i, vp, u32, u32, u32]),
             "rtb_set_camera": (i, [vp, C.POINTER(C.c_float)]),
@@ -144,6 +147,14 @@ class Engine:
         self.S, self.P, self.L = s.size // 96, p.size // 96, l.size // 48
         _check(lib().rtb_upload_scene(self._h, _host_ptr(s), self.S, _host_ptr(p), self.P, _host_ptr(l), self.L),
                "rtb_upload_scene")
+
+    def upload_triangles(self, tris):
+        """EXTENSION X1 (no reference counterpart): rtriangle records, 112 B each; b"" removes them."""
+        t = np.ascontiguousarray(np.frombuffer(bytes(tris), np.uint8)) if len(tris) else np.zeros(0, np.uint8)
+        if t.size % 112:
+            raise ValueError("triangle array is not whole 112-byte records")
+        self.T = t.size // 112
+        _check(lib().rtb_upload_triangles(self._h, _host_ptr(t), self.T), "rtb_upload_triangles")
 
     def bind_scene_device(self, d_spheres, S, d_planes, P, d_lights, L):
         self.S, self.P, self.L = int(S), int(P), int(L)
@@ -270,8 +281,9 @@ class Engine:
 
 
 def algorithmic_flop(c):
-    """21 flop per sphere test (+5 when D >= 0), 14 per plane test; nothing else counted."""
-    return 21 * c["sphere_tests"] + 5 * c["sphere_dpos"] + 14 * c["plane_tests"]
+    """21 flop per sphere test (+5 when D >= 0), 14 per plane test, 37 per triangle test
+    (extension X1); nothing else counted."""
+    return 21 * c["sphere_tests"] + 5 * c["sphere_dpos"] + 14 * c["plane_tests"] + 37 * c.get("tri_tests", 0)
 
 
 def assemble_bands(parts_rows, W, H, band_rows):

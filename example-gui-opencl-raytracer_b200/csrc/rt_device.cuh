@@ -90,6 +90,8 @@ struct Geo {
     const uint32_t* flag;
     const float* lut255; /* i / 255.0f for i in 0..255 (IEEE division, filled once per CTA) */
     uint32_t S, P, L, Spad, Lpad;
+    const float4* tri; /* extension X1: [3T] {v0, e1, e2}, global memory */
+    uint32_t T;
 };
 __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFrameParams& fp, const float* lut) {
     g.S = fp.S; g.P = fp.P; g.L = fp.L;
@@ -100,6 +102,8 @@ __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFra
     g.pln = base + fp.lay.pln_off;
     g.flag = reinterpret_cast<const uint32_t*>(base + fp.lay.flag_off);
     g.lut255 = lut;
+    g.tri = fp.tri;
+    g.T = fp.T;
 }
 
 /* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */
@@ -160,6 +164,43 @@ __device__ __forceinline__ Material load_material(const unsigned char* rec) {
     m.transperent = __float_as_uint(c.x); m.dielectric = __float_as_uint(c.y); m.n = c.z; m.reflectivity = c.w;
     m.texture_id = __float_as_int(d.x); m.texture_scale = d.y;
     return m;
+}
+
+__device__ __forceinline__ Material load_material_at(const unsigned char* mat) {
+    const float4* q = reinterpret_cast<const float4*>(mat);
+    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    Material m;
+    m.rgb = mk(a.x, a.y, a.z);
+    m.ambient = b.x; m.diffuse = b.y; m.specular = b.z; m.shininess = __float_as_uint(b.w);
+    m.transperent = __float_as_uint(c.x); m.dielectric = __float_as_uint(c.y); m.n = c.z; m.reflectivity = c.w;
+    m.texture_id = __float_as_int(d.x); m.texture_scale = d.y;
+    return m;
+}
+
+/* EXTENSION X1 (no reference counterpart; oracle/rt_oracle.c:hit_triangle is the definition): Moeller-Trumbore,
+ * two-sided, one rounded operation per step in exactly that order. */
+template <bool COUNT>
+__device__ __forceinline__ bool hit_triangle(V3 o, V3 d, const float4* rec, float& t, Tally<COUNT>& tl) {
+    tl.add(RTB_TRI_TESTS);
+    const V3 v0 = xyz(__ldg(rec)), e1 = xyz(__ldg(rec + 1)), e2 = xyz(__ldg(rec + 2));
+    V3 p = cross3(d, e2);
+    float det = dot3(e1, p);
+    if (det == 0.0f) return false;
+    float inv = 1.0f / det;
+    V3 s = o - v0;
+    float u = dot3(s, p) * inv;
+    if (u < 0.0f || u > 1.0f) return false;
+    V3 q = cross3(s, e1);
+    float v = dot3(d, q) * inv;
+    if (v < 0.0f || u + v > 1.0f) return false;
+    float t2 = dot3(e2, q) * inv;
+    if (t2 <= 0.0f) return false;
+    t = t2;
+    return true;
+}
+__device__ __forceinline__ V3 triangle_normal(const float4* rec) {
+    V3 n = cross3(xyz(__ldg(rec + 1)), xyz(__ldg(rec + 2)));
+    return n / sqrtf(dot3(n, n));
 }
 
 /* One suspended stack entry (raytracing.cl:28-30 keeps rray + n + f in three arrays). */

@@ -58,6 +58,9 @@ struct rtb_engine {
     const unsigned char *d_spheres = nullptr, *d_planes = nullptr, *d_lights = nullptr; /* owned or bound */
     uint32_t S = 0, P = 0, L = 0;
     DevBuf blob;
+    DevBuf tris, tri_rec; /* extension X1 */
+    const unsigned char* d_tris = nullptr;
+    uint32_t T = 0;
     RtBlobLayout lay{};
     bool have_scene = false;
 
@@ -113,7 +116,7 @@ void rtb_destroy(rtb_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     cudaStreamSynchronize(e->stream);
-    e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
+    e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
     e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release();
     cudaEventDestroy(e->ev0);
@@ -166,6 +169,36 @@ int rtb_bind_scene_device(rtb_engine* e, const void* d_spheres, uint32_t S, cons
     e->d_lights = (const unsigned char*)d_lights;
     e->S = S; e->P = P; e->L = L;
     return prep_scene(e);
+}
+
+static int prep_tris(rtb_engine* e) {
+    if (e->T == 0) return 0;
+    if (e->tri_rec.ensure((size_t)e->T * 48)) return -2;
+    CU(rt_launch_tri_prep(e->d_tris, e->T, (float4*)e->tri_rec.p, e->stream), "tri_prep launch");
+    return 0;
+}
+int rtb_upload_triangles(rtb_engine* e, const void* tris, uint32_t T) {
+    if (!e) return fail(-1, "null engine");
+    if (T && !tris) return fail(-1, "rtb_upload_triangles: null array with non-zero count");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaStreamSynchronize(e->stream), "sync before triangle upload");
+    if (e->tris.ensure((size_t)T * RT_TRIANGLE_BYTES)) return -2;
+    if (T) CU(cudaMemcpyAsync(e->tris.p, tris, (size_t)T * RT_TRIANGLE_BYTES, cudaMemcpyHostToDevice, e->stream), "H2D triangles");
+    e->d_tris = (const unsigned char*)e->tris.p;
+    e->T = T;
+    int rc = prep_tris(e);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(e->stream), "triangle upload");
+    return 0;
+}
+int rtb_bind_triangles_device(rtb_engine* e, const void* d_tris, uint32_t T) {
+    if (!e) return fail(-1, "null engine");
+    if (T && !d_tris) return fail(-1, "rtb_bind_triangles_device: null array");
+    if ((uintptr_t)d_tris & 15) return fail(-1, "rtb_bind_triangles_device: array must be 16-byte aligned");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    e->d_tris = (const unsigned char*)d_tris;
+    e->T = T;
+    return prep_tris(e);
 }
 
 int rtb_upload_images(rtb_engine* e, int which, const uint8_t* rgba, uint32_t w, uint32_t h, uint32_t layers) {
@@ -240,6 +273,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.S = e->S; fp.P = e->P; fp.L = e->L; fp.lay = e->lay;
     fp.blob = (const float4*)e->blob.p;
     fp.raw_spheres = e->d_spheres; fp.raw_planes = e->d_planes;
+    fp.T = e->T; fp.tri = (const float4*)e->tri_rec.p; fp.raw_tris = e->d_tris;
     /* a scene whose planes carry texture ids needs the texture array; without one, ids clamp onto a 1x1 dummy */
     fp.tex = (const uchar4*)(e->d_tex ? e->d_tex : e->d_sky);
     fp.tw = e->d_tex ? (int)e->tw : 1; fp.th = e->d_tex ? (int)e->th : 1; fp.tl = e->d_tex ? (int)e->tl : 1;

@@ -213,6 +213,17 @@ __global__ void scene_prep(const unsigned char* __restrict__ spheres, uint32_t S
     if (i == 0 && S + P + L == 0) blob[0] = make_float4(0, 0, 0, 0);
 }
 
+/* ---- tri_prep (extension X1): rtriangle wire records -> {v0, e1 = v1 - v0, e2 = v2 - v0} ---- */
+__global__ void tri_prep(const unsigned char* __restrict__ tris, uint32_t T, float4* __restrict__ rec) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T) return;
+    const float4* q = reinterpret_cast<const float4*>(tris + (size_t)i * RT_TRIANGLE_BYTES);
+    const V3 v0 = xyz(q[0]), e1 = xyz(q[1]) - v0, e2 = xyz(q[2]) - v0;
+    rec[3 * i + 0] = make_float4(v0.x, v0.y, v0.z, 0.0f);
+    rec[3 * i + 1] = make_float4(e1.x, e1.y, e1.z, 0.0f);
+    rec[3 * i + 2] = make_float4(e2.x, e2.y, e2.z, 0.0f);
+}
+
 /* ---- tile_cost: skeleton trace (no shading, no refraction children) of five rays per 2x2 group of tiles.
  * A scheduling hint only: it cannot change any pixel. ---- */
 constexpr uint32_t kCostBuckets = 64;
@@ -227,10 +238,13 @@ __device__ uint32_t skeleton_cost(const RtFrameParams& fp, const Geo& g, uint32_
         ray_setup_fast(r, o, d);
         Closest c;
         closest_pass(r, g, tl, c);
-        if ((c.k >= 0 && !c.occluded) || (c.who < 0 && c.whop < 0)) break;
+        if ((c.k >= 0 && !c.occluded) || (c.who < 0 && c.whop < 0 && c.whot < 0)) break;
         V3 ip = o + d * c.t, nrm;
         Material m;
-        if (c.whop >= 0) {
+        if (c.whot >= 0) {
+            nrm = triangle_normal(g.tri + 3 * c.whot);
+            m = load_material_at(fp.raw_tris + (size_t)c.whot * RT_TRIANGLE_BYTES + RT_TRI_MATERIAL_OFFSET);
+        } else if (c.whop >= 0) {
             nrm = xyz(g.pln[4 * c.whop]);
             m = load_material(fp.raw_planes + (size_t)c.whop * RT_PLANE_BYTES);
         } else {
@@ -432,6 +446,12 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
     n = n > lay.Lpad ? n : lay.Lpad;
     if (n == 0) n = 1;
     scene_prep<<<(n + 127) / 128, 128, 0, st>>>(d_spheres, S, d_planes, P, d_lights, L, d_blob, lay);
+    return cudaGetLastError();
+}
+
+cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* d_rec, cudaStream_t st) {
+    if (T == 0) return cudaSuccess;
+    tri_prep<<<(T + 127) / 128, 128, 0, st>>>(d_tris, T, d_rec);
     return cudaGetLastError();
 }
 

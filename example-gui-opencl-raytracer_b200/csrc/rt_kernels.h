@@ -9,6 +9,9 @@
 #define RT_PLANE_BYTES 96
 #define RT_LIGHT_BYTES 48
 #define RT_MATERIAL_OFFSET 32 /* rmaterial sits at byte 32 of rsphere and rplane */
+/* EXTENSION X1 (no reference counterpart): rtriangle = v0, v1, v2 as float4 (48 B) + rmaterial (64 B) */
+#define RT_TRIANGLE_BYTES 112
+#define RT_TRI_MATERIAL_OFFSET 48
 
 /* Compact geometry ("scene blob"), produced on the device by scene_prep and staged into shared memory
  * by TMA bulk copies.  Units are float4 records:
@@ -48,6 +51,10 @@ struct RtFrameParams {
     const float4* blob;
     const unsigned char* raw_spheres; /* wire arrays: materials are read in place */
     const unsigned char* raw_planes;
+    /* extension X1: triangles (not staged: 48 B records {v0, e1, e2} read through L1, broadcast per warp) */
+    uint32_t T;
+    const float4* tri;
+    const unsigned char* raw_tris;
     /* image arrays */
     const uchar4* tex; int tw, th, tl;
     const uchar4* sky; int sw, sh;
@@ -88,3 +95,6 @@ cudaError_t rt_launch_arith_selftest(uint32_t seed, uint32_t per_thread, uint32_
 /* Gathering rank: compact per-part band buffers (parts x stride_words) -> row-major frame. */
 cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W, uint32_t H,
                                      uint32_t band_rows, uint32_t parts, cudaStream_t st);
+
+/* Extension X1: rtriangle wire array -> {v0, v1-v0, v2-v0} records (3 float4 each). */
+cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* d_rec, cudaStream_t st);

@@ -97,7 +97,7 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
                 rgb = rgb + col * f;
                 if (AOV && first) hit_id = RTB_HIT_LIGHT | (uint32_t)c.k;
                 depth = kMaxDepth;
-            } else if (c.who < 0 && c.whop < 0) { /* skybox, raytracing.cl:61-81 */
+            } else if (c.who < 0 && c.whop < 0 && c.whot < 0) { /* skybox, raytracing.cl:61-81 */
                 int u, v;
                 cube_uv(d, (uint32_t)(fp.sw / 4), u, v);
                 tl.add(RTB_TEXELS);
@@ -107,7 +107,11 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
             } else {
                 shade = true;
                 ip = o + d * c.t;
-                if (c.whop >= 0) {
+                if (c.whot >= 0) { /* extension X1 */
+                    nrm = triangle_normal(g.tri + 3 * c.whot);
+                    m = load_material_at(fp.raw_tris + (size_t)c.whot * RT_TRIANGLE_BYTES + RT_TRI_MATERIAL_OFFSET);
+                    if (AOV && first) hit_id = 1u + g.S + g.P + (uint32_t)c.whot;
+                } else if (c.whop >= 0) {
                     nrm = xyz(g.pln[4 * c.whop]);
                     m = load_material(fp.raw_planes + (size_t)c.whop * RT_PLANE_BYTES);
                     if (m.texture_id >= 0) { /* primitives.cl:217-259; sampled once, for the plane that won */

@@ -74,6 +74,11 @@ __device__ __forceinline__ float shadow_path_literal(V3 to, V3 from, const Geo& 
         if (!hit_plane(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) || t1 >= len) continue;
         return 0.0f;
     }
+    for (uint32_t k = 0; k < g.T; k++) { /* extension X1 */
+        float t1;
+        if (!hit_triangle(r.o, r.d, g.tri + 3 * k, t1, tl) || t1 >= len) continue;
+        return 0.0f;
+    }
     return opacity;
 }
 
@@ -123,6 +128,10 @@ __device__ __forceinline__ uint32_t trace_pixel_literal(const RtFrameParams& fp,
                     float t1;
                     if (hit_plane(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) && t1 <= tL) blocked = true;
                 }
+                for (uint32_t q = 0; q < g.T && !blocked; q++) { /* extension X1 */
+                    float t1;
+                    if (hit_triangle(r.o, r.d, g.tri + 3 * q, t1, tl) && t1 <= tL) blocked = true;
+                }
                 if (!blocked) {
                     V3 ip = o + d * tL;
                     V3 od = o - ip;
@@ -155,7 +164,15 @@ __device__ __forceinline__ uint32_t trace_pixel_literal(const RtFrameParams& fp,
             if (COUNT && __float_as_int(g.pln[4 * j + 3].w) >= 0) tl.add(RTB_TEXELS);
         }
 
-        if (who < 0 && whop < 0) { /* skybox, raytracing.cl:61-81 */
+        int whot = -1;
+        for (uint32_t q = 0; q < g.T; q++) { /* extension X1 */
+            float t1;
+            if (!hit_triangle(r.o, r.d, g.tri + 3 * q, t1, tl) || t1 >= t) continue;
+            t = t1;
+            whot = (int)q;
+        }
+
+        if (who < 0 && whop < 0 && whot < 0) { /* skybox, raytracing.cl:61-81 */
             int u, v;
             cube_uv(d, (uint32_t)(fp.sw / 4), u, v);
             tl.add(RTB_TEXELS);
@@ -168,7 +185,11 @@ __device__ __forceinline__ uint32_t trace_pixel_literal(const RtFrameParams& fp,
 
         V3 ip = o + d * t, nrm;
         Material m;
-        if (whop >= 0) {
+        if (whot >= 0) { /* extension X1 */
+            nrm = triangle_normal(g.tri + 3 * whot);
+            m = load_material_at(fp.raw_tris + (size_t)whot * RT_TRIANGLE_BYTES + RT_TRI_MATERIAL_OFFSET);
+            if (AOV && first) hit_id = 1u + g.S + g.P + (uint32_t)whot;
+        } else if (whop >= 0) {
             nrm = xyz(g.pln[4 * whop]);
             m = load_material(fp.raw_planes + (size_t)whop * RT_PLANE_BYTES);
             if (m.texture_id >= 0) { /* primitives.cl:217-259 with the per-plane basis from scene_prep */

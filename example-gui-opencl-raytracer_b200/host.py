@@ -47,6 +47,14 @@ def light(origin, radius, intensity, rgb):
     return struct.pack("<3f4xff8x3f4x", *origin, radius, intensity, *rgb)
 
 
+TRIANGLE_BYTES = 112
+
+
+def triangle(v0, v1, v2, mat):
+    """EXTENSION X1 (SURVEY.md 8(a'), no reference counterpart): rtriangle = float4 v0, v1, v2 + rmaterial."""
+    return struct.pack("<3f4x3f4x3f4x", *v0, *v1, *v2) + material(**mat)
+
+
 def load_map(path):
     """extract_robj (src/cpu_obj.c:76-101) -> (spheres, planes, lights) as bytes."""
     d = open(path, "rb").read()
@@ -185,3 +193,38 @@ def sphere_grid_scene(n_side=32, seed=0x5EED1024, spacing=1.0):
               light((0, 10, 14), .3, 200.0, (.8, .9, 1)))
     cam = dict(origin=(0.0, 9.0, -half - 6.0), look=(0.0, -0.55, 1.0), fov=90.0, focal=1.0)
     return b"".join(sp), planes, lights, cam
+
+
+def heightfield_mesh_scene(n=158, seed=0x7121A461, size=16.0, amplitude=0.9):
+    """Config 4 (extension X1): a seeded n x n heightfield = 2*n*n triangles (158 -> 49,928) over the textured
+    ground plane, 3 lights.  Returns (spheres, planes, lights, triangles, camera kwargs)."""
+    state = [seed & 0xFFFFFFFF]
+
+    def rnd():
+        state[0] = (1664525 * state[0] + 1013904223) & 0xFFFFFFFF
+        return state[0] / 4294967296.0
+    k1, k2, p1, p2 = 0.9 + rnd(), 0.7 + rnd(), 6.28 * rnd(), 6.28 * rnd()
+    step = size / n
+
+    def hgt(i, j):
+        x, z = i * step - size / 2, j * step - size / 2
+        return 0.6 + amplitude * (0.5 * np.sin(k1 * x + p1) * np.cos(k2 * z + p2) + 0.5 * np.sin(0.37 * x * z + p1))
+    tris = []
+    for j in range(n):
+        for i in range(n):
+            x0, x1 = i * step - size / 2, (i + 1) * step - size / 2
+            z0, z1 = j * step - size / 2 + 4.0, (j + 1) * step - size / 2 + 4.0
+            a, b, c, d = (x0, hgt(i, j), z0), (x1, hgt(i + 1, j), z0), (x0, hgt(i, j + 1), z1), (x1, hgt(i + 1, j + 1), z1)
+            kind = (i + j) % 8
+            if kind == 0:
+                m = dict(MIRROR, rgb=(.25, .25, .3), reflectivity=0.6)
+            else:
+                m = dict(PLASTIC, rgb=(0.3 + 0.6 * rnd(), 0.4 + 0.5 * rnd(), 0.3 + 0.6 * rnd()))
+            tris.append(triangle(a, c, b, m))   # wound so that e1 x e2 points up (+y)
+            tris.append(triangle(b, c, d, m))
+    planes = plane((0, 1, 0), (0, -0.6, 0), dict(STONE, rgb=(0, 0, 0), texture_id=2, texture_scale=100.0))
+    lights = (light((-6, 8, -4), .3, 260.0, (1, 1, 1)) + light((8, 6, 6), .3, 180.0, (1, .9, .8)) +
+              light((0, 10, 14), .3, 200.0, (.8, .9, 1)))
+    spheres = sphere((0.0, 2.6, 4.0), 0.9, dict(GLASS)) + sphere((-3.0, 2.2, 6.0), 0.7, dict(MIRROR, reflectivity=1.0))
+    cam = dict(origin=(0.0, 6.5, -9.0), look=(0.0, -0.45, 1.0), fov=90.0, focal=1.0)
+    return spheres, planes, lights, b"".join(tris), cam

@@ -25,7 +25,8 @@ extern "C" {
 
 typedef struct rtb_engine rtb_engine;
 
-/* Hit-id encoding: 0 sky, 1+i sphere i, 1+S+j plane j, RTB_HIT_LIGHT|k light k. */
+/* Hit-id encoding: 0 sky, 1+i sphere i, 1+S+j plane j, 1+S+P+k triangle k (extension),
+ * RTB_HIT_LIGHT|k light k. */
 #define RTB_HIT_LIGHT 0x80000000u
 
 /* Work counters filled by rtb_render_counted (same order as oracle/rt_oracle.h). */
@@ -36,6 +37,7 @@ enum {
     RTB_SPHERE_DPOS = 3,  /* ... of which had D >= 0 */
     RTB_PLANE_TESTS = 4,  /* intersect_plane calls, primitives.cl:197 */
     RTB_TEXELS = 5,       /* texel fetches the reference would make (primitives.cl:250, raytracing.cl:70) */
+    RTB_TRI_TESTS = 7,    /* EXTENSION X1: triangle tests */
     RTB_SHADOW_SKIPPED = 6, /* executed-work accounting only: shadow rays elided because their light term is exactly 0 */
     RTB_NCOUNTERS = 8
 };
@@ -65,6 +67,14 @@ int rtb_upload_scene(rtb_engine* e, const void* spheres, uint32_t S, const void*
 /* Same, but the wire arrays already live in this device's memory (not copied, must stay valid). */
 int rtb_bind_scene_device(rtb_engine* e, const void* d_spheres, uint32_t S, const void* d_planes, uint32_t P,
                           const void* d_lights, uint32_t L);
+
+/* EXTENSION X1 -- triangles; the reference has none, so there is no reference parity for scenes
+ * that use them (checked against oracle/rt_oracle.c's own definition only).  Wire record rtriangle = 112 bytes:
+ * float4 v0, v1, v2 (w unused) then the 64-byte rmaterial.  Triangles are visited after the planes in all three
+ * traversals, are opaque and two-sided, normal = normalize(cross(v1-v0, v2-v0)) (not flipped), never textured.
+ * T = 0 removes them.  Call after rtb_upload_scene / rtb_bind_scene_device (which do not touch them). */
+int rtb_upload_triangles(rtb_engine* e, const void* tris, uint32_t T);
+int rtb_bind_triangles_device(rtb_engine* e, const void* d_tris, uint32_t T);
 
 /* RGBA8 image arrays, layers*h*w*4 bytes, row 0 = top row.  which: 0 = plane textures (kernel arg 8),
  * 1 = skybox (kernel arg 9, layers must be 1). */

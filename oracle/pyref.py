@@ -188,6 +188,15 @@ class _Port(_Lib):
         self.counted_fn.argtypes = _RENDER_ARGS + [u64p]
         self.counted_fn.restype = C.c_int
 
+    def set_triangles(self, tris):
+        """EXTENSION X1 (no reference counterpart): rtriangle records for the following render calls; b"" resets."""
+        self._tris = np.frombuffer(bytes(tris), np.uint8).copy() if len(tris) else None   # keep alive
+        if self._tris is None:
+            self.lib.rto_set_triangles(None, 0)
+        else:
+            assert self._tris.size % 112 == 0
+            self.lib.rto_set_triangles(C.c_void_p(self._tris.ctypes.data), C.c_uint32(self._tris.size // 112))
+
     def render_counted(self, scene, cam, W, H, y0=0, y1=None, wide=False, threads=0):
         """Like render() but also returns the work counters as a dict (plus 'rays' and 'flop')."""
         y1 = H if y1 is None else y1
@@ -205,6 +214,7 @@ class _Port(_Lib):
         if rc != 0:
             raise ValueError("rto_render_counted rejected its arguments")
         c = {k: int(cnt[i]) for i, k in enumerate(self.COUNTER_NAMES)}
+        c["tri_tests"] = int(cnt[7])
         c["rays"] = c["segments"] + c["shadow_rays"]
         c["flop"] = algorithmic_flop(c)
         return out, hit, c
@@ -212,7 +222,7 @@ class _Port(_Lib):
 
 def algorithmic_flop(c):
     """21 flop per sphere test (+5 when D >= 0), 14 per plane test; nothing else counted."""
-    return 21 * c["sphere_tests"] + 5 * c["sphere_dpos"] + 14 * c["plane_tests"]
+    return 21 * c["sphere_tests"] + 5 * c["sphere_dpos"] + 14 * c["plane_tests"] + 37 * c.get("tri_tests", 0)
 
 
 def port():
