@@ -37,6 +37,22 @@ SM_LANES = 128  # FP32 lanes per SM
 _JSON_FD = 1
 
 
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one render_frame launch, from the committed `ncu --set full`
+    capture of this same command (profiles/); None for workloads that were not captured."""
+    if workload != "render_map_4k":
+        return None
+    try:
+        tot = 0.0
+        for ln in open(os.path.join(ROOT, "profiles", "r01_v4_render_frame_key_metrics.txt")):
+            k, unit, v = ln.split()[0], ln.split()[1], ln.split()[-1]
+            if k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(v) * {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}[unit]
+        return tot or None
+    except Exception:
+        return None
+
+
 def peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -61,9 +77,22 @@ def make_workload(name, host):
         s, p, l, camp = host.sphere_grid_scene(32)
         W, H = 3840, 2160
         desc = "synthetic 1,024 mixed-material spheres over a textured plane at 3840x2160 (counts widened)"
+    elif name in ("mesh50k_8k", "mesh50k_4k", "mesh5k_4k"):
+        n = 50 if name == "mesh5k_4k" else 158
+        s, p, l, tris, camp = host.heightfield_mesh_scene(n)
+        W, H = (7680, 4320) if name.endswith("8k") else (3840, 2160)
+        desc = ("EXTENSION X1 (no reference parity): %d-triangle heightfield + ground plane + 2 spheres at %dx%d, "
+                "brute-force closest hit" % (len(tris) // 112, W, H))
+    elif name == "spheres255_8k":
+        s, p, l, camp = host.sphere_grid_scene(16)
+        s = s[:255 * 96]
+        W, H = 7680, 4320
+        desc = "255 mixed-material spheres (the most the reference's uchar counts allow) over a textured plane at 7680x4320"
     else:
         raise SystemExit("unknown workload " + name)
-    return dict(name=name, spheres=s, planes=p, lights=l, W=W, H=H, cam=host.camera(W=W, H=H, **camp), camp=camp,
+    if not name.startswith("mesh"):
+        tris = b""
+    return dict(name=name, spheres=s, planes=p, lights=l, tris=tris, W=W, H=H, cam=host.camera(W=W, H=H, **camp), camp=camp,
                 desc=desc, camera_fn=host.camera)
 
 
@@ -131,20 +160,23 @@ def cpu_sample_shape(W, H, budget_s, probe):
     """Pick the divisor s so that the (W/s)x(H/s) frame fits the time budget, from a small probe run."""
     probe_px, probe_s = probe
     per_px = probe_s / probe_px
-    for s in (1, 2, 3, 4, 5, 6, 8, 10, 12, 15, 16, 20, 24, 30):
+    for s in (1, 2, 3, 4, 5, 6, 8, 10, 12, 15, 16, 20, 24, 30, 40, 48, 60, 80, 120):
         if W % s or H % s:
             continue
         if per_px * (W // s) * (H // s) <= budget_s:
             return s
-    return 30
+    return 120
 
 
 def cpu_setup(wl):
     ref = entry.load_oracle()
     tex, sky = ref.default_textures(ROOT)
     scene = ref.Scene(wl["spheres"], wl["planes"], wl["lights"], tex, sky)
-    wide = max(scene.S, scene.P, scene.L) > 255
-    if ref.have_ref():
+    wide = max(scene.S, scene.P, scene.L) > 255 or len(wl["tris"]) > 0
+    if len(wl["tris"]):   # extension X1: only the port knows triangles
+        lib_, kind = ref.port(), "port"
+        lib_.set_triangles(wl["tris"])
+    elif ref.have_ref():
         lib_, kind = ref.ref(), "reference"
     else:
         lib_, kind = ref.port(), "port"
@@ -161,7 +193,7 @@ def cpu_time_frames(wl, steps, warmup, budget_total_s):
     """Returns (mrays_per_s, ms_per_step, cores, kind, sample description)."""
     ref, scene, wide, lib_, kind, cores = cpu_setup(wl)
     W, H = wl["W"], wl["H"]
-    pw, ph = W // 16, H // 16
+    pw, ph = (W // 16, H // 16) if not len(wl["tris"]) else (W // 96, H // 90)   # brute-force meshes: tiny probe
     t0 = time.perf_counter()
     lib_.render(scene, cpu_camera_for(ref, wl, pw, ph), pw, ph, wide=wide, threads=cores, want_hit=False)
     probe = (pw * ph, max(time.perf_counter() - t0, 1e-4))
@@ -246,6 +278,7 @@ def gpu_body(args, pkg, eng, world, rank, local):
     tex, sky = host.default_images(ROOT)
 
     eng.upload_scene(wl["spheres"], wl["planes"], wl["lights"])
+    eng.upload_triangles(wl["tris"])
     eng.upload_images(0, tex)
     eng.upload_images(1, sky)
     eng.set_camera(wl["cam"])
@@ -372,7 +405,9 @@ def gpu_body(args, pkg, eng, world, rank, local):
                     if world == 1 else "rtb_set_camera + rtb_render(band) + NCCL gather + D2H on rank 0"},
             "gpu_launches": args.steps * world,
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": achieved_tf / peak_tf, "traffic": None,
+                         "frac": achieved_tf / peak_tf, "traffic": ncu_traffic(wl["name"]),
+                         "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/r01_v4_*); algorithmic bytes: 33.2 MB "
+                                         "frame + <= 4 B per texel fetch; the kernel is FP32-issue bound, not HBM bound",
                          "kernel": "render_frame", "kernel_ms": float(np.mean(kernel_ms)),
                          "peak_source": "%d SMs x 128 lanes x 2 flop x %.0f MHz (MEASURED_PEAKS.json sm_max_mhz); no tensor/HBM bound applies"
                                         % (sms, sm_max),
@@ -391,7 +426,7 @@ def e2e_cl_wrap(pkg, wl, args, host_frame):
     buffers; set-up (scene, images, output slot) happens once, as in the reference drivers."""
     from example_gui_opencl_raytracer_b200.wrap_session import WrapSession
     W, H = wl["W"], wl["H"]
-    ses = WrapSession(W, H, wl["spheres"], wl["planes"], wl["lights"], wl["cam"], root=ROOT)
+    ses = WrapSession(W, H, wl["spheres"], wl["planes"], wl["lights"], wl["cam"], root=ROOT, triangles=wl["tris"])
     hp = host_frame.data_ptr()
 
     def frame():

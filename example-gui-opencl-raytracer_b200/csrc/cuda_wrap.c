@@ -22,7 +22,8 @@ enum { K_NONE = 0, K_RAYGEN = 1, K_RAYTRACER = 2 };
 enum { RG_CORNER = 0, RG_ORIGIN = 1, RG_UP = 2, RG_RIGHT = 3, RG_WF = 4, RG_HF = 5, RG_W = 6, RG_H = 7, RG_RAYS = 8 };
 /* raytracer args (raytracing.cl:14-21) */
 enum { RT_RAYS = 0, RT_SPHERES = 1, RT_PLANES = 2, RT_LIGHTS = 3, RT_NS = 4, RT_NP = 5, RT_NL = 6, RT_TOTAL = 7,
-       RT_TEX = 8, RT_SKY = 9, RT_OUT = 10 };
+       RT_TEX = 8, RT_SKY = 9, RT_OUT = 10,
+       RT_TRIS = 11, RT_NT = 12 /* EXTENSION X1 (optional): rtriangle buffer and its cl_uint count */ };
 
 typedef struct {
     unsigned char bytes[16];
@@ -47,6 +48,7 @@ typedef struct {
     uint32_t bound_ns, bound_np, bound_nl;
     int scene_dirty;
     const void *bound_tex, *bound_sky;
+    const void* bound_t; uint32_t bound_nt;
     /* host read-back buffers seen by cl_wrap_output (N1: frame mirrored into the caller's buffer by the kernel) */
     struct {
         void* host;      /* caller's pointer */
@@ -315,6 +317,15 @@ static uint64_t run_raytracer(cl_wrap* wrap, cl_uint k, size_t array_size, void*
         s->bound_s = ds; s->bound_p = dp; s->bound_l = dl;
         s->bound_ns = ns; s->bound_np = np; s->bound_nl = nl;
         s->scene_dirty = 0;
+    }
+    { /* extension X1: optional args 11 (rtriangle buffer) and 12 (count); absent = no triangles */
+        const void* dt = wrap->buffers[k][RT_TRIS];
+        uint32_t nt = (dt && c[RT_NT].size) ? scalar_count(&c[RT_NT]) : 0;
+        if ((size_t)nt * 112 > sl[RT_TRIS].size) die("Couldn't run the kernel");
+        if (dt != s->bound_t || nt != s->bound_nt) {
+            if (rtb_bind_triangles_device(e, dt, nt) != 0) die_engine("Couldn't pass the data argument to the kernel");
+            s->bound_t = dt; s->bound_nt = nt;
+        }
     }
     if (rtb_set_camera(e, s->cam) != 0) die_engine("Couldn't pass the data argument to the kernel");
 

@@ -13,7 +13,7 @@ from . import host as _host
 
 class WrapSession:
     def __init__(self, W, H, spheres, planes, lights, cam, root=_host.ROOT, texture_files=_host.TEXTURE_FILES,
-                 skybox_file=_host.SKYBOX_FILE):
+                 skybox_file=_host.SKYBOX_FILE, triangles=b""):
         self.L = L = wrap_lib()
         self.W, self.H = W, H
         self.w = w = ClWrap()
@@ -47,6 +47,11 @@ class WrapSession:
         L.cl_wrap_load_images(C.byref(w), C.c_uint32(1), C.c_uint32(9), C.c_uint64(CL_MEM_COPY_HOST_PTR), C.c_uint32(1),
                               cs(os.path.join(root, skybox_file).encode()))               # :80-81
         L.cl_wrap_load_global_data(C.byref(w), 1, 10, None, 4 * W * H, CL_MEM_WRITE_ONLY)  # :83
+        if len(triangles):  # EXTENSION X1: optional raytracer args 11 (rtriangle buffer) and 12 (cl_uint count)
+            t = bytes(triangles)
+            nt = C.c_uint32(len(t) // 112)
+            L.cl_wrap_load_global_data(C.byref(w), 1, 11, t, len(t), CL_MEM_READ_ONLY)
+            L.cl_wrap_load_single_data(C.byref(w), 1, 12, C.byref(nt), 4)
 
     def set_camera(self, cam):
         """The six per-frame scalars (rayinteractive.c:98-103)."""
