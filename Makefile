@@ -9,13 +9,17 @@ NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 --extended-lambda -Xcompiler -fPIC -
 KFLAGS  := -fmad=false -prec-div=true -prec-sqrt=true -ftz=false
 CFLAGS  := -O2 -std=gnu11 -fPIC -Wall -Wextra -ffp-contract=off -Iinclude -Iinclude/shim
 
-OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o
+OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o
 
 all: $(PKG)/librtb200.so
 
 $(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_coop.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels.ptxas.log || (cat $(CSRC)/rt_kernels.ptxas.log; false)
 	@grep -E "registers|spill" $(CSRC)/rt_kernels.ptxas.log | sort | uniq -c | sort -rn | head -20
+
+KDEPS := $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_coop.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
+$(CSRC)/rt_kernels_tri.o: $(CSRC)/rt_kernels_tri.cu $(KDEPS)
+	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels_tri.ptxas.log || (cat $(CSRC)/rt_kernels_tri.ptxas.log; false)
 
 $(CSRC)/rt_engine.o: $(CSRC)/rt_engine.cu $(CSRC)/rt_kernels.h include/rtb200.h
 	$(NVCC) $(ARCH) -O2 -lineinfo -std=c++17 -Xcompiler -fPIC -c $< -o $@
@@ -32,7 +36,7 @@ $(PKG)/librtb200.so: $(OBJS)
 # diagnostic build: per-tile wall time in the hit-id AOV (tools/exp/tile_times.py, RTB_LIB=...)
 timing: all
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -DRT_TILE_TIMING -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_timing.o 2> /dev/null
-	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o -lz
+	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o -lz
 
 oracle:
 	$(MAKE) -C oracle

@@ -14,7 +14,16 @@
 #include "../../include/rtb200.h"
 #include "rt_kernels.h"
 
-namespace rt {
+/* rt_kernels.cu is compiled twice: as is (namespace rt, no triangle code at all -- the reference's primitive set,
+ * the hot path) and through rt_kernels_tri.cu (namespace rt_tri, RT_TRIANGLES=1: extension X1). */
+#ifndef RT_TRIANGLES
+#define RT_TRIANGLES 0
+#endif
+#ifndef RT_NS
+#define RT_NS rt
+#endif
+
+namespace RT_NS {
 
 constexpr float kEps = 0.001f;                     /* primitives.cl:5  EPSILON */
 constexpr float kInvPi = 0.318309886183790671538f; /* primitives.cl:6  M_1_PI_F */
@@ -103,7 +112,7 @@ __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFra
     g.flag = reinterpret_cast<const uint32_t*>(base + fp.lay.flag_off);
     g.lut255 = lut;
     g.tri = fp.tri;
-    g.T = fp.T;
+    g.T = RT_TRIANGLES ? fp.T : 0u; /* a literal 0 in the plain build: every triangle loop and branch folds away */
 }
 
 /* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */
@@ -294,4 +303,4 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
 }
 
-}  // namespace rt
+}  // namespace RT_NS

@@ -310,7 +310,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     if (e->opt_tile_order && e->last.tiles >= 4096) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
         if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 4) || e->tile_hist.ensure(1024)) return -2;
-        CU(rt_launch_tile_order(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
+        CU((e->T ? rt_launch_tile_order_tri : rt_launch_tile_order)(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),
            "tile_order launch");
         fp.order = (const uint32_t*)e->tile_order.p;
@@ -318,7 +318,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
-    CU(rt_launch_render(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
+    CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
     CU(cudaEventRecord(e->ev1, e->stream), "event record");
     e->timed = true;
     e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;

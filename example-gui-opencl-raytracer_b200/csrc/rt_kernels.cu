@@ -23,7 +23,7 @@
 #include "rt_trace_coop.cuh"
 #include "rt_trace_literal.cuh"
 
-namespace rt {
+namespace RT_NS {
 
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 5
@@ -68,6 +68,7 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
         cs.owner = reinterpret_cast<float4*>(base);
         cs.task = cs.owner + 32;
         cs.light = cs.task + kCoopTasks;
+        cs.pre = cs.light + 32 * kCoopLights;
     }
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
     const bool vec_store = (fp.W % 4u) == 0u; /* rows are 16-byte aligned */
@@ -435,10 +436,17 @@ cudaError_t go(const RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t 
     return launch_variant<R, M, A>(fp, grid, smem, st);
 }
 
-}  // namespace rt
+}  // namespace RT_NS
 
-using namespace rt;
+using namespace RT_NS;
 
+#if RT_TRIANGLES
+#define RT_EXPORT(name) name##_tri
+#else
+#define RT_EXPORT(name) name
+#endif
+
+#if !RT_TRIANGLES
 cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, const unsigned char* d_planes, uint32_t P,
                                  const unsigned char* d_lights, uint32_t L, float4* d_blob, RtBlobLayout lay,
                                  cudaStream_t st) {
@@ -449,13 +457,18 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
     return cudaGetLastError();
 }
 
+#endif
+
+#if RT_TRIANGLES
 cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* d_rec, cudaStream_t st) {
     if (T == 0) return cudaSuccess;
     tri_prep<<<(T + 127) / 128, 128, 0, st>>>(d_tris, T, d_rec);
     return cudaGetLastError();
 }
 
-cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
+#endif
+
+cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                  cudaStream_t st) {
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
     cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, 2 * kCostBuckets * sizeof(uint32_t), st);
@@ -468,7 +481,7 @@ cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint
     return cudaGetLastError();
 }
 
-cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape) {
+cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape) {
     const uint32_t blob_bytes = fp.lay.total * 16u;
     /* keep the geometry resident while it leaves room for >= 2 CTAs per SM */
     const bool resident = blob_bytes <= 96u * 1024u;
@@ -486,6 +499,7 @@ cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cu
     return cudaErrorInvalidValue;
 }
 
+#if !RT_TRIANGLES
 cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W, uint32_t H,
                                      uint32_t band_rows, uint32_t parts, cudaStream_t st) {
     const size_t n = (size_t)((W + 3u) / 4u) * H;
@@ -502,3 +516,4 @@ cudaError_t rt_launch_arith_selftest(uint32_t seed, uint32_t per_thread, uint32_
     arith_selftest<<<148 * 4, 256, 0, st>>>(seed, per_thread, d_out);
     return cudaGetLastError();
 }
+#endif

@@ -96,5 +96,9 @@ cudaError_t rt_launch_arith_selftest(uint32_t seed, uint32_t per_thread, uint32_
 cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W, uint32_t H,
                                      uint32_t band_rows, uint32_t parts, cudaStream_t st);
 
+/* Extension X1 builds of the two launchers above (rt_kernels_tri.cu), used when the scene has triangles. */
+cudaError_t rt_launch_render_tri(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
+cudaError_t rt_launch_tile_order_tri(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
+                                     cudaStream_t st);
 /* Extension X1: rtriangle wire array -> {v0, v1-v0, v2-v0} records (3 float4 each). */
 cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* d_rec, cudaStream_t st);

@@ -16,20 +16,29 @@
  *                  then diffuse), then Fresnel / reflection / refraction child as before.
  * A task's value does not depend on which lane computes it (same routine, same operands), so the words are
  * identical; the per-pixel RNG stream is drawn by the owner in the reference's order.
- * Shared memory per warp: 32 owner records (hit point) + 256 task slots + 4x32 light records, 16 bytes each = 6.5 KiB.
+ * Shared memory per warp: 32 owner records (hit point) + 192 task slots + 3x32 light records + 32x9 R8 records,
+ * 16 bytes each = 9.5 KiB.
  */
 #pragma once
 #include "rt_trace_fast.cuh"
 
-namespace rt {
+namespace RT_NS {
 
-constexpr int kCoopLights = 4;                                   /* lights per chunk */
-constexpr int kCoopTasks = 32 * kCoopLights * kShadowSamples;    /* 256 */
-constexpr uint32_t kCoopBytesPerWarp = 32 * 16 + kCoopTasks * 16 + 32 * kCoopLights * 16; /* 6656 */
+#ifndef RT_COOP_LIGHTS
+#define RT_COOP_LIGHTS 4
+#endif
+#ifndef RT_PRE_S
+#define RT_PRE_S 0 /* R8 measured slower on B200 (2.84 vs 2.63 ms: bank conflicts on per-owner records, smaller L1 for the ray stacks): off */
+#endif
+constexpr int kCoopLights = RT_COOP_LIGHTS;                      /* lights per chunk */
+constexpr int kPreS = RT_PRE_S, kPreRec = kPreS ? kPreS + 1 : 0;                    /* R8: per-owner records: <= 8 padded spheres + 1 of <= 4 plane numerators */
+constexpr int kCoopTasks = 32 * kCoopLights * kShadowSamples;    /* 192 */
+constexpr uint32_t kCoopBytesPerWarp = 32 * 16 + kCoopTasks * 16 + 32 * kCoopLights * 16 + 32 * kPreRec * 16; /* 9728 */
 
 struct CoopSmem {
     float4* owner; /* [32] {ip.xyz, -} */
     float4* task;  /* [kCoopTasks] {theta, phi, light (bits), owner lane (bits)}; .x becomes the opacity */
+    float4* pre;   /* [32][kPreRec] R8 records of each owner's current hit point (used when Spad <= 8 and P <= 4) */
     float4* light; /* [kCoopLights][32] per owner and light of the chunk: {dist, max(0,n.h), max(0,n.l), flags | slot << 8} */
 };
 
@@ -45,6 +54,7 @@ __device__ __forceinline__ float coop_run_task(const Geo& g, const CoopSmem& cs,
     sincos_bounded(tk.x, sth, cth);
     const float rs = radius * sp;
     const V3 sample = xyz(l0) + mk(rs * cth, rs * sth, radius * cp); /* raytracing.cl:101-106 */
+    if (kPreS && g.Spad <= (uint32_t)kPreS && g.P <= 4u) return shadow_path_pre(sample, xyz(ipo), cs.pre + ow * kPreRec, kPreS, g, tl);
     return shadow_path_fast(sample, xyz(ipo), g, tl);
 }
 
@@ -141,7 +151,18 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
         if (__any_sync(kFull, shade)) {
             const float shin = (float)m.shininess;
             const float fs = f * m.specular, fd = f * m.diffuse;
-            if (shade) cs.owner[lane] = make_float4(ip.x, ip.y, ip.z, 0.0f);
+            if (shade) {
+                cs.owner[lane] = make_float4(ip.x, ip.y, ip.z, 0.0f);
+                if (kPreS && g.Spad <= (uint32_t)kPreS && g.P <= 4u) { /* R8: origin-dependent halves of this segment's shadow tests */
+                    float4* mine = cs.pre + lane * kPreRec;
+                    for (uint32_t i = 0; i < g.Spad; i++) mine[i] = sphere_pre(ip, g.sph[i]);
+                    float nums[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                    for (uint32_t j = 0; j < 4u; j++)
+                        if (j < g.P) nums[j] = dot3(xyz(g.pln[4 * j + 1]) - ip, xyz(g.pln[4 * j]));
+                    mine[kPreS] = make_float4(nums[0], nums[1], nums[2], nums[3]);
+                }
+            }
             for (uint32_t c0 = 0; c0 < L; c0 += kCoopLights) {
                 const uint32_t nk = L - c0 < (uint32_t)kCoopLights ? L - c0 : (uint32_t)kCoopLights; /* warp-uniform */
                 uint32_t ntask = 0;
@@ -247,4 +268,4 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
     return pack_rgb(rgb);
 }
 
-}  // namespace rt
+}  // namespace RT_NS

@@ -8,7 +8,7 @@
 #pragma once
 #include "rt_device.cuh"
 
-namespace rt {
+namespace RT_NS {
 
 /* The ray being traced plus hoisted sphere-test invariants (bit-identical rewrites, see rt_kernels.cu). */
 struct Ray {
@@ -278,4 +278,4 @@ __device__ __forceinline__ uint32_t trace_pixel_literal(const RtFrameParams& fp,
     return pack_rgb(rgb);
 }
 
-}  // namespace rt
+}  // namespace RT_NS
