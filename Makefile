@@ -9,7 +9,7 @@ NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 --extended-lambda -Xcompiler -fPIC -
 KFLAGS  := -fmad=false -prec-div=true -prec-sqrt=true -ftz=false
 CFLAGS  := -O2 -std=gnu11 -fPIC -Wall -Wextra -ffp-contract=off -Iinclude -Iinclude/shim
 
-OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o
+OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o
 
 all: $(PKG)/librtb200.so
 
@@ -30,13 +30,16 @@ $(CSRC)/cuda_wrap.o: $(CSRC)/cuda_wrap.c include/cuda_wrap.h include/rtb200.h $(
 $(CSRC)/png_io.o: $(CSRC)/png_io.c $(CSRC)/png_io.h
 	gcc $(CFLAGS) -c $< -o $@
 
+$(CSRC)/map_io.o: $(CSRC)/map_io.c include/rtb200.h
+	gcc $(CFLAGS) -D_POSIX_C_SOURCE=200809L -c $< -o $@
+
 $(PKG)/librtb200.so: $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lz
 
 # diagnostic build: per-tile wall time in the hit-id AOV (tools/exp/tile_times.py, RTB_LIB=...)
 timing: all
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -DRT_TILE_TIMING -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_timing.o 2> /dev/null
-	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o -lz
+	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
 
 oracle:
 	$(MAKE) -C oracle

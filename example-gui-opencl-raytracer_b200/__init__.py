@@ -28,7 +28,7 @@ ENGINE_SYMBOLS = (
     "rtb_upload_triangles", "rtb_bind_triangles_device", "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
-    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops",
+    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
 )
 WRAP_SYMBOLS = (
     "cl_wrap_init", "cl_wrap_load_global_data", "cl_wrap_load_single_data", "cl_wrap_load_images", "cl_wrap_output",
@@ -43,6 +43,12 @@ class RtbError(RuntimeError):
 class Partition(C.Structure):
     """rtb_partition: cyclic row bands (include/rtb200.h)."""
     _fields_ = [("band_rows", C.c_uint32), ("parts", C.c_uint32), ("part", C.c_uint32)]
+
+
+class MapArchive(C.Structure):
+    """rtb_map (include/rtb200.h)."""
+    _fields_ = [("spheres", C.c_void_p), ("planes", C.c_void_p), ("lights", C.c_void_p), ("triangles", C.c_void_p),
+                ("S", C.c_uint32), ("P", C.c_uint32), ("L", C.c_uint32), ("T", C.c_uint32), ("version", C.c_int)]
 
 
 class LaunchInfo(C.Structure):
@@ -98,6 +104,9 @@ def lib():
             "rtb_assemble_bands": (i, [vp, vp, sz, vp, u32, u32, u32, u32]),
             "rtb_last_launch": (i, [vp, C.POINTER(LaunchInfo)]),
             "rtb_fp32_peak_tflops": (C.c_double, [vp, i]),
+            "rtb_map_load": (i, [C.c_char_p, C.POINTER(MapArchive)]),
+            "rtb_map_save": (i, [C.c_char_p, C.POINTER(MapArchive), i]),
+            "rtb_map_free": (None, [C.POINTER(MapArchive)]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)

@@ -14,7 +14,7 @@ import struct
 
 import numpy as np
 
-from . import lib
+from . import MapArchive, lib
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -228,3 +228,28 @@ def heightfield_mesh_scene(n=158, seed=0x7121A461, size=16.0, amplitude=0.9):
     spheres = sphere((0.0, 2.6, 4.0), 0.9, dict(GLASS)) + sphere((-3.0, 2.2, 6.0), 0.7, dict(MIRROR, reflectivity=1.0))
     cam = dict(origin=(0.0, 6.5, -9.0), look=(0.0, -0.45, 1.0), fov=90.0, focal=1.0)
     return spheres, planes, lights, b"".join(tris), cam
+
+
+# ---- scene archives through the library's own reader/writer (csrc/map_io.c) ----
+def load_map_any(path):
+    """v1 (the reference's .map) or v2 ("RTM2", 32-bit counts + triangles) -> (spheres, planes, lights, triangles, version)."""
+    m = MapArchive()
+    rc = lib().rtb_map_load(path.encode(), C.byref(m))
+    if rc != 0:
+        raise IOError("%s: rtb_map_load failed (%d)" % (path, rc))
+    try:
+        out = [C.string_at(p, n * sz) if n else b"" for p, n, sz in
+               ((m.spheres, m.S, 96), (m.planes, m.P, 96), (m.lights, m.L, 48), (m.triangles, m.T, 112))]
+        return out[0], out[1], out[2], out[3], m.version
+    finally:
+        lib().rtb_map_free(C.byref(m))
+
+
+def save_map(path, spheres, planes, lights, triangles=b"", version=2):
+    bufs = [C.create_string_buffer(bytes(b), len(b)) if len(b) else None for b in (spheres, planes, lights, triangles)]
+    m = MapArchive()
+    m.spheres, m.planes, m.lights, m.triangles = [C.cast(b, C.c_void_p) if b is not None else None for b in bufs]
+    m.S, m.P, m.L, m.T = len(spheres) // 96, len(planes) // 96, len(lights) // 48, len(triangles) // 112
+    rc = lib().rtb_map_save(path.encode(), C.byref(m), version)
+    if rc != 0:
+        raise IOError("%s: rtb_map_save failed (%d)" % (path, rc))

@@ -149,6 +149,19 @@ int rtb_host_map(void* host, size_t nbytes, void** dev_view, int* registered_her
 int rtb_set_mirror(rtb_engine* e, uint32_t* mirror);
 int rtb_host_unregister(void* host);
 
+/* Scene archives.  v1 = the reference's .map (src/cpu_obj.c:51-101: 1-byte counts, <= 255 per
+ * type); v2 = "RTM2" + four uint32 counts (spheres, planes, lights, triangles) + the raw arrays.  rtb_map_load reads
+ * either (arrays malloc'ed, 16-byte aligned; release with rtb_map_free); rtb_map_save writes the version asked for
+ * (-3 if the scene does not fit v1).  Returns 0, -2 on I/O errors, -3 on a malformed file. */
+typedef struct {
+    void *spheres, *planes, *lights, *triangles;
+    uint32_t S, P, L, T;
+    int version;
+} rtb_map;
+int rtb_map_load(const char* path, rtb_map* out);
+int rtb_map_save(const char* path, const rtb_map* m, int version);
+void rtb_map_free(rtb_map* m);
+
 /* Launch geometry the renderer chose for the last frame (for bench.py's accounting). */
 typedef struct {
     uint32_t grid, block, smem_bytes, tiles, resident_scene; /* resident_scene: 1 = geometry staged in shared memory */

@@ -1,0 +1,109 @@
+"""CPU-side checks of the extensions: scene archives v1/v2 (csrc/map_io.c) and the oracle port's triangle test
+(EXTENSION X1 -- defined by oracle/rt_oracle.c itself; here it is compared with an independent float32 restatement)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def host(pkg):
+    from example_gui_opencl_raytracer_b200 import host as h
+    return h
+
+
+def test_map_v1_is_read_like_the_reference_loader(host):
+    s, p, l = host.load_map(os.path.join(ROOT, "scenes", "render.map"))      # python mirror of cpu_obj.c:76-101
+    s2, p2, l2, t2, ver = host.load_map_any(os.path.join(ROOT, "scenes", "render.map"))
+    assert ver == 1 and t2 == b"" and (s2, p2, l2) == (s, p, l)
+
+
+def test_map_v2_round_trip_and_limits(host, tmp_path):
+    s, p, l, camp = host.sphere_grid_scene(17)                   # 289 spheres: not expressible in v1
+    _, _, _, tris, _ = host.heightfield_mesh_scene(n=4)
+    f2 = str(tmp_path / "big.map")
+    host.save_map(f2, s, p, l, tris, version=2)
+    assert host.load_map_any(f2) == (s, p, l, tris, 2)
+    with pytest.raises(IOError):
+        host.save_map(str(tmp_path / "x.map"), s, p, l, b"", version=1)
+    with pytest.raises(IOError):
+        host.save_map(str(tmp_path / "y.map"), s[:96 * 3], p, l, tris, version=1)   # triangles do not fit v1 either
+    f1 = str(tmp_path / "small.map")
+    host.save_map(f1, s[:96 * 200], p, l, b"", version=1)
+    assert host.load_map(f1) == (s[:96 * 200], p, l)            # what the reference's extract_robj would read
+    assert host.load_map_any(f1)[4] == 1
+    bad = str(tmp_path / "bad.map")
+    open(bad, "wb").write(open(f2, "rb").read()[:-5])
+    with pytest.raises(IOError):
+        host.load_map_any(bad)
+    # empty scene, both versions
+    for v in (1, 2):
+        fe = str(tmp_path / ("e%d.map" % v))
+        host.save_map(fe, b"", b"", b"", b"", version=v)
+        assert host.load_map_any(fe)[:4] == (b"", b"", b"", b"")
+
+
+def mt_float32(o, d, v0, v1, v2):
+    f = np.float32
+    def dot(a, b): return f(f(f(a[0] * b[0]) + f(a[1] * b[1])) + f(a[2] * b[2]))
+    def cross(a, b): return [f(f(a[1] * b[2]) - f(a[2] * b[1])), f(f(a[2] * b[0]) - f(a[0] * b[2])), f(f(a[0] * b[1]) - f(a[1] * b[0]))]
+    def sub(a, b): return [f(a[i] - b[i]) for i in range(3)]
+    e1, e2 = sub(v1, v0), sub(v2, v0)
+    p = cross(d, e2)
+    det = dot(e1, p)
+    if det == 0: return None
+    inv = f(f(1.0) / det)
+    s = sub(o, v0)
+    u = f(dot(s, p) * inv)
+    if u < 0 or u > 1: return None
+    q = cross(s, e1)
+    v = f(dot(d, q) * inv)
+    if v < 0 or f(u + v) > 1: return None
+    t = f(dot(e2, q) * inv)
+    return None if t <= 0 else t
+
+
+def test_oracle_triangle_kat(ref):
+    lib = ref.port().lib
+    lib.rto_isect_triangle.restype = C.c_int
+    rng = np.random.default_rng(7)
+    fp = C.POINTER(C.c_float)
+    hits = 0
+    with np.errstate(all="ignore"):
+        for k in range(4000):
+            a = rng.normal(size=15).astype(np.float32) * np.float32(3.0)
+            o, d, v0, v1, v2 = a[0:3].copy(), a[3:6].copy(), a[6:9].copy(), a[9:12].copy(), a[12:15].copy()
+            if k % 7 == 0: d = (v0 + v1 + v2) / np.float32(3) - o          # aim at the centroid: certain hits
+            if k % 11 == 0: v2 = v1.copy()                                  # degenerate: det == 0
+            t = C.c_float(-1)
+            got = lib.rto_isect_triangle(o.ctypes.data_as(fp), d.ctypes.data_as(fp), v0.ctypes.data_as(fp),
+                                         v1.ctypes.data_as(fp), v2.ctypes.data_as(fp), C.byref(t))
+            want = mt_float32([np.float32(x) for x in o], [np.float32(x) for x in d], [np.float32(x) for x in v0],
+                              [np.float32(x) for x in v1], [np.float32(x) for x in v2])
+            assert bool(got) == (want is not None)
+            if got:
+                hits += 1
+                assert np.float32(t.value).tobytes() == np.float32(want).tobytes()
+    assert hits > 400
+
+
+def test_oracle_triangle_scene_is_deterministic_and_visible(ref, scene, host):
+    tris = host.triangle((-2, 0, 3), (2, 0, 3), (0, 3, 3), dict(host.PLASTIC, rgb=(.1, .8, .3)))
+    W, H = 64, 48
+    cam = host.camera(origin=(0, 1, -3), look=(0, 0, 1), fov=90.0, focal=1.0, W=W, H=H)
+    sc = ref.Scene(b"", b"", bytes(scene.lights), scene.tex, scene.sky)
+    port = ref.port()
+    base_rgb, base_hit = port.render(sc, cam, W, H)
+    port.set_triangles(tris)
+    try:
+        rgb1, hit1 = port.render(sc, cam, W, H, threads=1)
+        rgb2, hit2 = port.render(sc, cam, W, H, threads=4)
+    finally:
+        port.set_triangles(b"")
+    assert np.array_equal(rgb1, rgb2) and np.array_equal(hit1, hit2)
+    assert (hit1 == 1).sum() > 100 and (base_hit == 1).sum() == 0          # id 1+S+P+0 with S = P = 0
+    rgb3, _ = port.render(sc, cam, W, H)
+    assert np.array_equal(rgb3, base_rgb)                                   # reset really removes them
