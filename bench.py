@@ -309,13 +309,60 @@ def gpu_body(args, pkg, eng, world, rank, local):
     frame_rays, frame_flop = int(totals[0]), int(totals[1])
     my_flop = cnt["flop"]
 
+    # ---- band exchange ----
+    # "p2p":  every rank's render kernel also stores its bands straight into rank 0's frame over NVLink (CUDA IPC
+    #         mapping of a cudaMalloc'ed frame, rtb_set_mirror_frame); the only collective left is a 4-byte all-reduce
+    #         that tells rank 0 the peers' kernels have drained.
+    # "nccl": compact band buffers gathered to rank 0 with one NCCL gather, then one assemble_bands kernel.
+    exchange = args.exchange if world > 1 else "none"
+    raw_frame = peer_frame = None
+    if exchange == "p2p":
+        class _Raw:
+            def __init__(self, ptr, n):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 3}
+        if rank == 0:
+            raw_frame = eng.dev_alloc(H * W * 4)
+            handle = torch.tensor(list(eng.ipc_export(raw_frame)), dtype=torch.uint8, device=dev)
+            frame = torch.as_tensor(_Raw(raw_frame.value, H * W), device=dev)
+            target = raw_frame.value
+        else:
+            handle = torch.empty(64, dtype=torch.uint8, device=dev)
+        dist.broadcast(handle, 0)
+        if rank != 0:
+            peer_frame = eng.ipc_open(bytes(handle.cpu().tolist()))
+            target = peer_frame.value
+        done_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+
     def step_device():
         """One frame, everything on the engine's stream; frame stays in HBM (rank 0)."""
+        if exchange == "p2p":
+            eng.set_mirror_frame(target)
+            eng.render(W, H, part=part, d_out=band_buf.data_ptr())
+            if dbg is not None:
+                e1 = torch.cuda.Event(enable_timing=True); e1.record(stream)
+            dist.all_reduce(done_flag)               # completion only: the pixels already travelled with the stores
+            if dbg is not None:
+                e2 = torch.cuda.Event(enable_timing=True); e2.record(stream)
+                dbg.append((eng, e1, e2))
+            return
         eng.render(W, H, part=part, d_out=band_buf.data_ptr())
         if world > 1:
             dist.gather(band_buf, gathered, dst=0)   # the one collective: bands -> rank 0 over NCCL/NVLink
             if rank == 0:
                 eng.assemble_bands(landing.data_ptr(), max_rows * W, frame.data_ptr(), W, H, band, world)
+
+    dbg = [] if os.environ.get("BENCH_DEBUG") else None
+    verified = None
+    if world > 1:   # untimed: the N-GPU frame must be bit-identical to this rank-0 GPU's own full frame
+        with torch.cuda.stream(stream):
+            step_device()
+            barrier_ok = dist.barrier()
+            if rank == 0:
+                full = torch.empty(H * W, dtype=torch.int32, device=dev)
+                eng.render(W, H, d_out=full.data_ptr())
+                eng.sync()
+                verified = bool(torch.equal(full, frame))
+                del full
 
     def barrier():
         if world > 1:
@@ -359,6 +406,11 @@ def gpu_body(args, pkg, eng, world, rank, local):
                 eng.render(W, H, part=part, d_out=band_buf.data_ptr())
                 kernel_ms.append(eng.last_kernel_ms())
     clocks = clk.summary()
+    if dbg:
+        torch.cuda.synchronize()
+        ar = [a.elapsed_time(b) for _, a, b in dbg[-10:]]
+        print("rank %d: all_reduce span ms (kernel end -> collective end): %s; last_render_ms %.3f" %
+              (rank, ["%.3f" % x for x in ar], eng.last_render_ms()), file=sys.stderr)
 
     # ---- end to end through the public API with host buffers ----
     if world == 1:
@@ -393,8 +445,11 @@ def gpu_body(args, pkg, eng, world, rank, local):
             "config": {"workload": wl["name"], "desc": wl["desc"], "width": W, "height": H,
                        "rays_per_frame": frame_rays, "algorithmic_flop_per_frame": frame_flop,
                        "segments": int(totals[2]), "shadow_rays": int(totals[3]),
-                       "parallelism": "row bands of %d rows dealt cyclically over %d GPUs, NCCL gather to rank 0" % (band, world)
+                       "parallelism": ("row bands of %d rows dealt cyclically over %d GPUs, " % (band, world)) +
+                                      ("bands stored into rank 0's frame over NVLink by the render kernel (CUDA IPC), 4-byte NCCL "
+                                       "all-reduce as completion" if exchange == "p2p" else "NCCL gather to rank 0 + assemble kernel")
                        if world > 1 else "1 GPU",
+                       "frame_equals_1gpu": verified,
                        "l2": "flushed between timed steps (256 MiB fill outside the event pair)",
                        "launch": eng.last_launch()},
             "clocks": clocks,
@@ -402,7 +457,7 @@ def gpu_body(args, pkg, eng, world, rank, local):
                     "frames_per_s": 1e3 / e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "readback": rb_stats,
                     "api": "cl_wrap_load_single_data x6 + cl_wrap_output(raygen) + cl_wrap_output(raytracer, read-back)"
-                    if world == 1 else "rtb_set_camera + rtb_render(band) + NCCL gather + D2H on rank 0"},
+                    if world == 1 else "rtb_set_camera + rtb_render(band, %s exchange) + D2H of the frame on rank 0" % exchange},
             "gpu_launches": args.steps * world,
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": ncu_traffic(wl["name"]),
@@ -419,6 +474,15 @@ def gpu_body(args, pkg, eng, world, rank, local):
             line["cpu_baseline"] = {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample}
         sys.stdout.flush()
         os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+    if exchange == "p2p":   # unmap the peers' views before rank 0 frees the frame
+        torch.cuda.synchronize()
+        dist.barrier()
+        if peer_frame is not None:
+            eng.ipc_close(peer_frame)
+        dist.barrier()
+        frame = None
+        if raw_frame is not None:
+            eng.dev_free(raw_frame)
 
 
 def e2e_cl_wrap(pkg, wl, args, host_frame):
@@ -451,6 +515,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="render_map_4k")
     ap.add_argument("--band-rows", type=int, default=8)
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: how bands reach rank 0")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

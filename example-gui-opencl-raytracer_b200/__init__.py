@@ -28,7 +28,7 @@ ENGINE_SYMBOLS = (
     "rtb_upload_triangles", "rtb_bind_triangles_device", "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
-    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
+    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_set_mirror_frame", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
 )
 WRAP_SYMBOLS = (
     "cl_wrap_init", "cl_wrap_load_global_data", "cl_wrap_load_single_data", "cl_wrap_load_images", "cl_wrap_output",
@@ -101,6 +101,10 @@ def lib():
             "rtb_host_unregister": (i, [vp]),
             "rtb_host_map": (i, [vp, sz, C.POINTER(vp), C.POINTER(i)]),
             "rtb_set_mirror": (i, [vp, vp]),
+            "rtb_set_mirror_frame": (i, [vp, vp]),
+            "rtb_ipc_export": (i, [vp, vp, C.c_char_p]),
+            "rtb_ipc_open": (i, [vp, C.c_char_p, C.POINTER(vp)]),
+            "rtb_ipc_close": (i, [vp, vp]),
             "rtb_assemble_bands": (i, [vp, vp, sz, vp, u32, u32, u32, u32]),
             "rtb_last_launch": (i, [vp, C.POINTER(LaunchInfo)]),
             "rtb_fp32_peak_tflops": (C.c_double, [vp, i]),
@@ -203,6 +207,23 @@ class Engine:
         c["rays"] = c["segments"] + c["shadow_rays"]
         c["flop"] = algorithmic_flop(c)
         return c
+
+    def set_mirror_frame(self, d_frame):
+        """The next render also stores every word at d_frame[y*W + x] (a full frame, typically a peer GPU's)."""
+        _check(lib().rtb_set_mirror_frame(self._h, C.c_void_p(d_frame)), "rtb_set_mirror_frame")
+
+    def ipc_export(self, dptr):
+        h = C.create_string_buffer(64)
+        _check(lib().rtb_ipc_export(self._h, dptr, h), "rtb_ipc_export")
+        return h.raw
+
+    def ipc_open(self, handle):
+        p = C.c_void_p()
+        _check(lib().rtb_ipc_open(self._h, C.create_string_buffer(bytes(handle), 64), C.byref(p)), "rtb_ipc_open")
+        return p
+
+    def ipc_close(self, p):
+        _check(lib().rtb_ipc_close(self._h, p), "rtb_ipc_close")
 
     def assemble_bands(self, d_compact, stride_words, d_frame, W, H, band_rows, parts):
         """Gathering rank: compact band buffers -> row-major frame (one kernel on the engine's stream)."""

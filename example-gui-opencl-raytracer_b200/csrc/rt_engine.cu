@@ -73,8 +73,14 @@ struct rtb_engine {
 
     DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
     DevBuf tile_cost, tile_order, tile_hist;
-    int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0;
+    DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
+    int time_cur = 0;
+    bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
+    uint32_t tk_W = 0, tk_H = 0, tk_total = 0, tk_band = 0, tk_parts = 0, tk_part = 0;
+    unsigned long long scene_gen = 0, tk_scene_gen = 0;
+    int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0, opt_split_min_cost = 0 /* 0 = automatic */, opt_history = 1;
     uint32_t* mirror = nullptr; /* one-shot, see rtb_set_mirror */
+    bool mirror_global = false;
     rtb_launch_info last{};
 };
 
@@ -118,7 +124,7 @@ void rtb_destroy(rtb_engine* e) {
     cudaStreamSynchronize(e->stream);
     e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
-    e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release();
+    e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
     cudaEventDestroy(e->ev0);
     cudaEventDestroy(e->ev1);
     cudaEventDestroy(e->evk);
@@ -133,6 +139,7 @@ static int prep_scene(rtb_engine* e) {
                             e->stream),
        "scene_prep launch");
     e->have_scene = true;
+    e->scene_gen++;
     return 0;
 }
 
@@ -292,7 +299,9 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.out = d_out;
     fp.hit = d_hit;
     fp.mirror = e->mirror;
+    fp.mirror_global = e->mirror_global ? 1u : 0u;
     e->mirror = nullptr;
+    e->mirror_global = false;
     if ((uintptr_t)fp.mirror & 15) return fail(-1, "rtb_render: mirror buffer must be 16-byte aligned");
     fp.tile_counter = (unsigned int*)e->sched.p;
     fp.counters = (unsigned long long*)((char*)e->sched.p + 64);
@@ -307,14 +316,38 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.order = nullptr;
     fp.cost = nullptr;
     fp.coop_min_cost = (uint32_t)e->opt_coop_min_cost;
+    fp.split_min_cost = 64u;
     if (e->opt_tile_order && e->last.tiles >= 4096) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
-        if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 4) || e->tile_hist.ensure(1024)) return -2;
+        if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 16) || e->tile_hist.ensure(1024)) return -2;
+        /* scheduling hint: the previous frame's measured tile times when it had this geometry and scene (the camera may
+         * have moved: frames of an interactive sweep are coherent), else the skeleton trace.  Pixels never depend on it. */
+        const bool same = e->time_valid && e->tk_W == W && e->tk_H == H && e->tk_total == total && e->tk_band == pp.band_rows &&
+                          e->tk_parts == pp.parts && e->tk_part == pp.part && e->tk_scene_gen == e->scene_gen + e->T;
+        if (e->opt_history && counters == nullptr) {
+            if (e->tile_time[0].ensure(nt * 4) || e->tile_time[1].ensure(nt * 4)) return -2;
+            fp.tile_time = (uint32_t*)e->tile_time[e->time_cur].p;
+            CU(cudaMemsetAsync(fp.tile_time, 0, nt * 4, e->stream), "reset tile times");
+            if (same) {
+                fp.tile_time_prev = (const uint32_t*)e->tile_time[1 - e->time_cur].p;
+                /* measured costs: heavy tiles go to four warps.  Automatic threshold from the sweep in tools/exp/sweep_split.py:
+                 * ~500 us (cost 40) when the frame is a partition or small enough for one tile to bound the kernel,
+                 * ~2 ms (48) for a whole 4K frame, where splitting only costs lane occupancy. */
+                if (mode == 0) fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : (nt >= 200000 ? 48u : 40u);
+            }
+            e->time_cur = 1 - e->time_cur;
+            e->time_valid = true;
+            e->tk_W = W; e->tk_H = H; e->tk_total = total; e->tk_band = pp.band_rows; e->tk_parts = pp.parts; e->tk_part = pp.part;
+            e->tk_scene_gen = e->scene_gen + e->T;
+        } else {
+            e->time_valid = false;
+        }
         CU((e->T ? rt_launch_tile_order_tri : rt_launch_tile_order)(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),
            "tile_order launch");
         fp.order = (const uint32_t*)e->tile_order.p;
         fp.cost = (const uint32_t*)e->tile_cost.p;
+        fp.queue_len = (const uint32_t*)e->tile_hist.p + 128;
     }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
@@ -357,6 +390,8 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
 int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!e || !name) return fail(-1, "rtb_set_option: null argument");
     if (!strcmp(name, "trace")) { e->opt_trace = (value == 1 || value == 2) ? value : 0; return 0; }
+    if (!strcmp(name, "history")) { e->opt_history = value ? 1 : 0; e->time_valid = false; return 0; }
+    if (!strcmp(name, "split_min_cost")) { e->opt_split_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "coop_min_cost")) { e->opt_coop_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     return fail(-1, "rtb_set_option: unknown option");
@@ -440,6 +475,36 @@ int rtb_dev_read(rtb_engine* e, void* host, const void* dptr, size_t nbytes) {
 int rtb_set_mirror(rtb_engine* e, uint32_t* mirror) {
     if (!e) return fail(-1, "null engine");
     e->mirror = mirror;
+    e->mirror_global = false;
+    return 0;
+}
+int rtb_set_mirror_frame(rtb_engine* e, uint32_t* frame) {
+    if (!e) return fail(-1, "null engine");
+    e->mirror = frame;
+    e->mirror_global = true;
+    return 0;
+}
+int rtb_ipc_export(rtb_engine* e, const void* dptr, unsigned char handle[64]) {
+    if (!e || !dptr || !handle) return fail(-1, "rtb_ipc_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, const_cast<void*>(dptr)), "cudaIpcGetMemHandle");
+    memcpy(handle, &h, 64);
+    return 0;
+}
+int rtb_ipc_open(rtb_engine* e, const unsigned char handle[64], void** dptr) {
+    if (!e || !dptr || !handle) return fail(-1, "rtb_ipc_open: null argument");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    CU(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle");
+    return 0;
+}
+int rtb_ipc_close(rtb_engine* e, void* dptr) {
+    if (!e || !dptr) return fail(-1, "rtb_ipc_close: null argument");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaIpcCloseMemHandle(dptr), "cudaIpcCloseMemHandle");
     return 0;
 }
 int rtb_host_map(void* host, size_t nbytes, void** dev_view, int* registered_here) {

@@ -70,7 +70,8 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
         cs.light = cs.task + kCoopTasks;
         cs.pre = cs.light + 32 * kCoopLights;
     }
-    const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
+    /* queue length: every tile once, plus 3 extra entries per split tile (tile_order writes the total) */
+    const uint32_t ntiles = fp.order ? __ldg(fp.queue_len) : fp.tiles_x * fp.tiles_y;
     const bool vec_store = (fp.W % 4u) == 0u; /* rows are 16-byte aligned */
     Tally<COUNT> tl;
     tl.clear();
@@ -81,15 +82,18 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
         const uint32_t slot = __shfl_sync(0xffffffffu, next, 0);
         if (slot >= ntiles) break;
         if (lane == 0) next = atomicAdd(fp.tile_counter, 1u); /* prefetch: latency hides behind this tile */
-        const uint32_t tile = fp.order ? __ldg(fp.order + slot) : slot;
+        const uint32_t entry = fp.order ? __ldg(fp.order + slot) : slot;
+        const uint32_t tile = entry & 0x00ffffffu;
+        const uint32_t sub = entry >> 24; /* 0: whole 8x4 tile; 1..4: only tile row sub-1 (a split heavy tile) */
 
         const uint32_t tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
         const uint32_t x = tx * kTileW + (lane & 7u);
         const uint32_t lr = ty * kTileH + (lane >> 3);
         const uint32_t y = ((lr / fp.band_rows) * fp.parts + fp.part) * fp.band_rows + lr % fp.band_rows;
         const uint32_t id = y * fp.W + x;
-        const bool live = x < fp.W && lr < fp.local_rows && y < fp.H && id < fp.total;
+        const bool live = x < fp.W && lr < fp.local_rows && y < fp.H && id < fp.total && (sub == 0u || (lane >> 3) + 1u == sub);
 
+        const long long tile_clk0 = clock64();
         uint32_t word = 0, hid = 0;
 #ifdef RT_TILE_TIMING /* diagnostic build: the hit-id AOV carries each tile's wall time in ns (tools/exp/tile_times.py) */
         unsigned long long t_begin;
@@ -105,15 +109,20 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
             else word = trace_pixel_fast<COUNT, AOV>(fp, g, id, hid, tl);
         }
         __syncwarp();
+        /* measured cost of this tile (sub-tiles add up): the next frame's scheduling hint */
+        if (fp.tile_time && lane == 0) atomicAdd(fp.tile_time + tile, (uint32_t)((clock64() - tile_clk0) >> 10) + 1u);
 #ifdef RT_TILE_TIMING
         {
             unsigned long long t_end;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
-            hid = (uint32_t)(t_end - t_begin);
+            /* start time and duration in units of 1.024 us: [31:16] start (mod 67 ms), [15:0] duration */
+            unsigned long long dur = (t_end - t_begin) >> 10;
+            hid = (uint32_t)(((t_begin >> 10) & 0xffffull) << 16) | (uint32_t)(dur > 0xffffull ? 0xffffull : dur);
         }
 #endif
 
         const size_t at = (size_t)lr * fp.W + x;
+        const size_t mat = fp.mirror_global ? (size_t)id : at; /* mirror in full-frame (row-major) or compact layout */
         if (vec_store) { /* lanes 0 and 4 of each tile row store 4 pixels = 16 bytes */
             uint32_t w1 = __shfl_down_sync(0xffffffffu, word, 1);
             uint32_t w2 = __shfl_down_sync(0xffffffffu, word, 2);
@@ -122,15 +131,15 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
             if ((lane & 3u) == 0u && live) {
                 if (live3) {
                     *reinterpret_cast<uint4*>(fp.out + at) = make_uint4(word, w1, w2, w3);
-                    if (fp.mirror) __stcs(reinterpret_cast<uint4*>(fp.mirror + at), make_uint4(word, w1, w2, w3));
+                    if (fp.mirror) __stcs(reinterpret_cast<uint4*>(fp.mirror + mat), make_uint4(word, w1, w2, w3));
                 } else { /* id >= total inside this quad: scalar tail */
                     fp.out[at] = word;
                     if (id + 1 < fp.total) fp.out[at + 1] = w1;
                     if (id + 2 < fp.total) fp.out[at + 2] = w2;
                     if (fp.mirror) {
-                        fp.mirror[at] = word;
-                        if (id + 1 < fp.total) fp.mirror[at + 1] = w1;
-                        if (id + 2 < fp.total) fp.mirror[at + 2] = w2;
+                        fp.mirror[mat] = word;
+                        if (id + 1 < fp.total) fp.mirror[mat + 1] = w1;
+                        if (id + 2 < fp.total) fp.mirror[mat + 2] = w2;
                     }
                 }
             }
@@ -149,7 +158,7 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
             }
         } else if (live) {
             fp.out[at] = word;
-            if (fp.mirror) fp.mirror[at] = word;
+            if (fp.mirror) fp.mirror[mat] = word;
             if (AOV && fp.hit) fp.hit[at] = hid;
         }
     }
@@ -294,7 +303,26 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
                 const uint32_t tx = bx * 2 + dx, ty = by * 2 + dy;
                 if (tx < fp.tiles_x && ty < fp.tiles_y) { cost_out[ty * fp.tiles_x + tx] = cost; n++; }
             }
-        atomicAdd(&shist[cost], n);
+        atomicAdd(&shist[cost], cost >= fp.split_min_cost ? 4u * n : n); /* split tiles occupy four queue entries */
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
+        if (shist[i]) atomicAdd(&hist[i], shist[i]);
+}
+
+/* ---- tile_cost_history: the previous frame's measured tile times as cost (4*log2 scale: 16 us ~ 20, 150 us ~ 33,
+ * 800 us ~ 42).  Replaces the skeleton trace whenever a frame of the same geometry has just been rendered. ---- */
+__global__ void tile_cost_history(const uint32_t* __restrict__ prev, uint32_t* __restrict__ cost_out,
+                                  uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost) {
+    __shared__ uint32_t shist[kCostBuckets];
+    for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
+    __syncthreads();
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile < ntiles) {
+        uint32_t c = (uint32_t)(4.0f * __log2f((float)prev[tile] + 1.0f));
+        c = c < kCostBuckets ? c : kCostBuckets - 1u;
+        cost_out[tile] = c;
+        atomicAdd(&shist[c], c >= split_min_cost ? 4u : 1u);
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
@@ -304,25 +332,32 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
 /* counting sort, heaviest bucket first; order within a bucket is arbitrary (it cannot affect any pixel).
  * One global atomic per (block, bucket): ranks inside a block come from shared-memory atomics. */
 __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __restrict__ hist,
-                           uint32_t* __restrict__ cursor, uint32_t* __restrict__ order, uint32_t ntiles) {
+                           uint32_t* __restrict__ cursor, uint32_t* __restrict__ order, uint32_t ntiles,
+                           uint32_t split_min_cost, uint32_t* __restrict__ queue_len) {
     __shared__ uint32_t base[kCostBuckets], local[kCostBuckets], gbase[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) local[i] = 0;
     if (threadIdx.x == 0) {
         uint32_t acc = 0;
         for (int b = (int)kCostBuckets - 1; b >= 0; b--) { base[b] = acc; acc += hist[b]; }
+        if (blockIdx.x == 0) *queue_len = acc;
     }
     __syncthreads();
     const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t c = 0, rank = 0;
     if (tile < ntiles) {
         c = cost[tile];
-        rank = atomicAdd(&local[c], 1u);
+        rank = atomicAdd(&local[c], c >= split_min_cost ? 4u : 1u);
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
         gbase[i] = local[i] ? atomicAdd(&cursor[i], local[i]) : 0u;
     __syncthreads();
-    if (tile < ntiles) order[base[c] + gbase[c] + rank] = tile;
+    if (tile < ntiles) {
+        uint32_t* o = order + base[c] + gbase[c] + rank;
+        if (c >= split_min_cost) { /* a heavy tile is dealt to four warps, one tile row (8 pixels + 24 helper lanes) each */
+            o[0] = tile | (1u << 24); o[1] = tile | (2u << 24); o[2] = tile | (3u << 24); o[3] = tile | (4u << 24);
+        } else o[0] = tile;
+    }
 }
 
 /* Row-band re-interleave on the gathering rank: `compact` holds `parts` band buffers of
@@ -471,13 +506,15 @@ cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* 
 cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                  cudaStream_t st) {
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
-    cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, 2 * kCostBuckets * sizeof(uint32_t), st);
+    cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, (2 * kCostBuckets + 1) * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
     const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
-    tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
+    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost);
+    else tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    tile_order<<<(ntiles + 255) / 256, 256, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles);
+    tile_order<<<(ntiles + 255) / 256, 256, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles,
+                                                    fp.split_min_cost, d_hist_cursor + 2 * kCostBuckets);
     return cudaGetLastError();
 }
 

@@ -63,11 +63,16 @@ struct RtFrameParams {
     uint32_t* hit; /* may be NULL */
     uint32_t* mirror; /* may be NULL: second copy of `out` (mapped host memory: the frame lands in the caller's buffer
                          while the kernel runs, 16 bytes per store, no D2H copy afterwards) */
+    uint32_t mirror_global; /* 1: mirror is a full H x W frame indexed by global pixel id (a peer GPU's frame buffer) */
     /* scheduling */
     unsigned int* tile_counter; /* zeroed before launch */
     const uint32_t* order;      /* queue slot -> tile (heaviest first), or NULL for row-major order */
     uint32_t tiles_x, tiles_y;
     const uint32_t* cost;       /* per-tile cost estimate (tile_cost), or NULL */
+    uint32_t* tile_time;        /* per-tile wall time of THIS frame in units of 1024 SM clocks (zeroed before launch), or NULL */
+    const uint32_t* tile_time_prev; /* the previous frame's, used as next cost estimate instead of the skeleton trace, or NULL */
+    const uint32_t* queue_len;  /* number of queue entries when `order` is set (tiles + 3 per split tile) */
+    uint32_t split_min_cost;    /* tiles whose estimate reaches this are split into four 8x1 sub-tiles (64 = never) */
     uint32_t coop_min_cost;     /* tiles whose estimate reaches this walk in cooperative mode, the rest lane per pixel */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
 };
@@ -84,7 +89,8 @@ struct RtLaunchShape {
  * counters, 2 = cooperative trace + executed-work counters, 3 = per-lane fast trace.  Geometry is staged in shared memory when it fits. */
 cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
 
-/* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[128] (zeroed here), d_order[ntiles]. */
+/* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[129] (zeroed here; word 128 receives the queue length),
+ * d_order[4*ntiles]. */
 cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                  cudaStream_t st);
 

@@ -108,6 +108,10 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
 
 /* Engine options.  "trace": 0 = production trace (warp-cooperative shadow rays; default), 1 = literal trace
  * (reference control flow; same pixels, slower), 2 = per-lane fast trace (same pixels; the previous production path).  "tile_order": 1 = cost-ordered tile queue (default), 0 = row-major queue.
+ * "history": 1 (default) = a frame of the same size/partition/scene as the previous one is scheduled from that frame's
+ * MEASURED per-tile times (4*log2 cost scale) instead of the skeleton trace; 0 = always the skeleton trace.
+ * "split_min_cost" (history frames only): tiles whose cost estimate reaches this value are dealt to four warps (one 8-pixel tile row each,
+ * the other 24 lanes only run shadow tasks) so that no single warp owns a whole glass/mirror tile (64 = never, 0 = automatic: 40 for partitions, 48 for whole 4K+ frames).
  * "coop_min_cost": tiles whose cost estimate (0..63) reaches this value use the cooperative walk, cheaper tiles the
  * per-lane walk (0 = all cooperative, 64 = none; scheduling only, pixels do not change). */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
@@ -147,6 +151,15 @@ int rtb_host_map(void* host, size_t nbytes, void** dev_view, int* registered_her
  * device-visible pointer, typically an rtb_host_map view, so the frame is in the caller's host buffer when the
  * kernel ends -- PCIe writes overlap the render, no D2H copy).  Cleared by that render.  16-byte aligned. */
 int rtb_set_mirror(rtb_engine* e, uint32_t* mirror);
+/* Same, but `frame` is a full H x W row-major frame and every word goes to frame[y*W + x] (global pixel id) whatever
+ * the partition: with a PEER GPU's frame buffer (rtb_ipc_open) each rank's bands land in the gathering rank's frame
+ * over NVLink while the kernel runs -- the band exchange fused into the render. */
+int rtb_set_mirror_frame(rtb_engine* e, uint32_t* frame);
+/* CUDA IPC plumbing for that (one process per GPU): export a cudaMalloc'ed buffer of this engine's device as a 64-byte
+ * handle / map a peer's handle into this process (peer access enabled lazily) / unmap. */
+int rtb_ipc_export(rtb_engine* e, const void* dptr, unsigned char handle[64]);
+int rtb_ipc_open(rtb_engine* e, const unsigned char handle[64], void** dptr);
+int rtb_ipc_close(rtb_engine* e, void* dptr);
 int rtb_host_unregister(void* host);
 
 /* Scene archives.  v1 = the reference's .map (src/cpu_obj.c:51-101: 1-byte counts, <= 255 per

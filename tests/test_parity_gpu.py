@@ -145,3 +145,25 @@ def test_assemble_bands_kernel(engine, ref, pkg, W, H, parts, band):
     engine.dev_free(landing)
     engine.dev_free(frame)
     assert np.array_equal(got, whole)
+
+
+def test_history_scheduling_does_not_change_pixels(engine, ref):
+    """Frames after the first are scheduled from the previous frame's measured tile times (and heavy tiles are
+    split over four warps): a hint only -- every frame must carry the same words, with the camera moved too."""
+    W, H = 1024, 512
+    cams = [ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA),
+            ref.camera(origin=(1.2, 2.2, -7.5), look=(0.15, -0.05, 1.0), fov=90.0, focal=1.0, W=W, H=H)]
+    engine.set_option("history", 0)
+    want = []
+    for c in cams:
+        engine.set_camera(c)
+        want.append(engine.render_to_host(W, H, want_hit=True))
+    engine.set_option("history", 1)
+    for thr in (33, 20, 1):
+        engine.set_option("split_min_cost", thr)
+        for rep in range(3):
+            for c, (rgb0, hit0) in zip(cams, want):
+                engine.set_camera(c)
+                rgb, hit = engine.render_to_host(W, H, want_hit=True)
+                assert np.array_equal(rgb, rgb0) and np.array_equal(hit, hit0), (thr, rep)
+    engine.set_option("split_min_cost", 0)
