@@ -78,7 +78,7 @@ struct rtb_engine {
     bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
     uint32_t tk_W = 0, tk_H = 0, tk_total = 0, tk_band = 0, tk_parts = 0, tk_part = 0;
     unsigned long long scene_gen = 0, tk_scene_gen = 0;
-    int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0, opt_split_min_cost = 0 /* 0 = automatic */, opt_history = 1;
+    int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0, opt_split_min_cost = 0 /* 0 = automatic */, opt_split32_min_cost = 0 /* 0 = automatic */, opt_history = 1;
     uint32_t* mirror = nullptr; /* one-shot, see rtb_set_mirror */
     bool mirror_global = false;
     rtb_launch_info last{};
@@ -317,14 +317,15 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.cost = nullptr;
     fp.coop_min_cost = (uint32_t)e->opt_coop_min_cost;
     fp.split_min_cost = 64u;
+    fp.split32_min_cost = 64u;
     if (e->opt_tile_order && e->last.tiles >= 4096) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
-        if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 16) || e->tile_hist.ensure(1024)) return -2;
+        if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 128) || e->tile_hist.ensure(1024)) return -2;
         /* scheduling hint: the previous frame's measured tile times when it had this geometry and scene (the camera may
          * have moved: frames of an interactive sweep are coherent), else the skeleton trace.  Pixels never depend on it. */
         const bool same = e->time_valid && e->tk_W == W && e->tk_H == H && e->tk_total == total && e->tk_band == pp.band_rows &&
                           e->tk_parts == pp.parts && e->tk_part == pp.part && e->tk_scene_gen == e->scene_gen + e->T;
-        if (e->opt_history && counters == nullptr) {
+        if (e->opt_history && mode == 0) {
             if (e->tile_time[0].ensure(nt * 4) || e->tile_time[1].ensure(nt * 4)) return -2;
             fp.tile_time = (uint32_t*)e->tile_time[e->time_cur].p;
             CU(cudaMemsetAsync(fp.tile_time, 0, nt * 4, e->stream), "reset tile times");
@@ -334,6 +335,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                  * ~500 us (cost 40) when the frame is a partition or small enough for one tile to bound the kernel,
                  * ~2 ms (48) for a whole 4K frame, where splitting only costs lane occupancy. */
                 if (mode == 0) fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : (nt >= 200000 ? 48u : 40u);
+                if (mode == 0) fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : (nt >= 200000 ? 64u : 48u);
             }
             e->time_cur = 1 - e->time_cur;
             e->time_valid = true;
@@ -391,6 +393,7 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!e || !name) return fail(-1, "rtb_set_option: null argument");
     if (!strcmp(name, "trace")) { e->opt_trace = (value == 1 || value == 2) ? value : 0; return 0; }
     if (!strcmp(name, "history")) { e->opt_history = value ? 1 : 0; e->time_valid = false; return 0; }
+    if (!strcmp(name, "split32_min_cost")) { e->opt_split32_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "split_min_cost")) { e->opt_split_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "coop_min_cost")) { e->opt_coop_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }

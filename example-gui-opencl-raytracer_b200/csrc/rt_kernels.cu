@@ -84,17 +84,17 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
         if (lane == 0) next = atomicAdd(fp.tile_counter, 1u); /* prefetch: latency hides behind this tile */
         const uint32_t entry = fp.order ? __ldg(fp.order + slot) : slot;
         const uint32_t tile = entry & 0x00ffffffu;
-        const uint32_t sub = entry >> 24; /* 0: whole 8x4 tile; 1..4: only tile row sub-1 (a split heavy tile) */
+        const uint32_t sub = entry >> 24; /* 0: whole 8x4 tile; 1..4: only tile row sub-1; 5..36: only pixel sub-5 (split heavy tiles) */
 
         const uint32_t tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
         const uint32_t x = tx * kTileW + (lane & 7u);
         const uint32_t lr = ty * kTileH + (lane >> 3);
         const uint32_t y = ((lr / fp.band_rows) * fp.parts + fp.part) * fp.band_rows + lr % fp.band_rows;
         const uint32_t id = y * fp.W + x;
-        const bool live = x < fp.W && lr < fp.local_rows && y < fp.H && id < fp.total && (sub == 0u || (lane >> 3) + 1u == sub);
+        const bool live = x < fp.W && lr < fp.local_rows && y < fp.H && id < fp.total && (sub == 0u || (sub <= 4u ? (lane >> 3) + 1u == sub : lane + 5u == sub));
 
         const long long tile_clk0 = clock64();
-        uint32_t word = 0, hid = 0;
+        uint32_t word = 0, hid = 0, nseg = 0;
 #ifdef RT_TILE_TIMING /* diagnostic build: the hit-id AOV carries each tile's wall time in ns (tools/exp/tile_times.py) */
         unsigned long long t_begin;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
@@ -103,13 +103,14 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
          * per-lane walk has less lock-step overhead on the cheap majority.  Same words either way. */
         const bool heavy = COOP && (!fp.cost || __ldg(fp.cost + tile) >= fp.coop_min_cost);
         if (heavy) {
-            word = trace_tile_coop<COUNT, AOV>(fp, g, cs, id, live, lane, hid, tl);
+            word = trace_tile_coop<COUNT, AOV>(fp, g, cs, id, live, lane, hid, nseg, tl);
         } else if (live) {
             if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);
             else word = trace_pixel_fast<COUNT, AOV>(fp, g, id, hid, tl);
         }
         __syncwarp();
-        /* measured cost of this tile (sub-tiles add up): the next frame's scheduling hint */
+        /* measured cost of this tile in units of 1024 SM clocks (sub-tiles add up): the next frame's scheduling hint.
+         * (Segments traced -- nseg -- were tried as a split-invariant metric: worse order, tools/exp/sweep_split.py.) */
         if (fp.tile_time && lane == 0) atomicAdd(fp.tile_time + tile, (uint32_t)((clock64() - tile_clk0) >> 10) + 1u);
 #ifdef RT_TILE_TIMING
         {
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
 
         const size_t at = (size_t)lr * fp.W + x;
         const size_t mat = fp.mirror_global ? (size_t)id : at; /* mirror in full-frame (row-major) or compact layout */
-        if (vec_store) { /* lanes 0 and 4 of each tile row store 4 pixels = 16 bytes */
+        if (vec_store && sub <= 4u) { /* lanes 0 and 4 of each tile row store 4 pixels = 16 bytes (single-pixel entries: scalar) */
             uint32_t w1 = __shfl_down_sync(0xffffffffu, word, 1);
             uint32_t w2 = __shfl_down_sync(0xffffffffu, word, 2);
             uint32_t w3 = __shfl_down_sync(0xffffffffu, word, 3);
@@ -237,6 +238,10 @@ __global__ void tri_prep(const unsigned char* __restrict__ tris, uint32_t T, flo
 /* ---- tile_cost: skeleton trace (no shading, no refraction children) of five rays per 2x2 group of tiles.
  * A scheduling hint only: it cannot change any pixel. ---- */
 constexpr uint32_t kCostBuckets = 64;
+/* queue entries per tile: whole tile, four 8-pixel rows, or 32 single pixels (the other lanes only run shadow tasks) */
+__device__ __forceinline__ uint32_t split_ways(uint32_t cost, uint32_t split4, uint32_t split32) {
+    return cost >= split32 ? 32u : (cost >= split4 ? 4u : 1u);
+}
 
 __device__ uint32_t skeleton_cost(const RtFrameParams& fp, const Geo& g, uint32_t id) {
     V3 o, d;
@@ -303,7 +308,7 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
                 const uint32_t tx = bx * 2 + dx, ty = by * 2 + dy;
                 if (tx < fp.tiles_x && ty < fp.tiles_y) { cost_out[ty * fp.tiles_x + tx] = cost; n++; }
             }
-        atomicAdd(&shist[cost], cost >= fp.split_min_cost ? 4u * n : n); /* split tiles occupy four queue entries */
+        atomicAdd(&shist[cost], split_ways(cost, fp.split_min_cost, fp.split32_min_cost) * n);
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
@@ -313,7 +318,7 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
 /* ---- tile_cost_history: the previous frame's measured tile times as cost (4*log2 scale: 16 us ~ 20, 150 us ~ 33,
  * 800 us ~ 42).  Replaces the skeleton trace whenever a frame of the same geometry has just been rendered. ---- */
 __global__ void tile_cost_history(const uint32_t* __restrict__ prev, uint32_t* __restrict__ cost_out,
-                                  uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost) {
+                                  uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost, uint32_t split32_min_cost) {
     __shared__ uint32_t shist[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
     __syncthreads();
@@ -322,7 +327,7 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, uint32_t* _
         uint32_t c = (uint32_t)(4.0f * __log2f((float)prev[tile] + 1.0f));
         c = c < kCostBuckets ? c : kCostBuckets - 1u;
         cost_out[tile] = c;
-        atomicAdd(&shist[c], c >= split_min_cost ? 4u : 1u);
+        atomicAdd(&shist[c], split_ways(c, split_min_cost, split32_min_cost));
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
@@ -333,7 +338,7 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, uint32_t* _
  * One global atomic per (block, bucket): ranks inside a block come from shared-memory atomics. */
 __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __restrict__ hist,
                            uint32_t* __restrict__ cursor, uint32_t* __restrict__ order, uint32_t ntiles,
-                           uint32_t split_min_cost, uint32_t* __restrict__ queue_len) {
+                           uint32_t split_min_cost, uint32_t split32_min_cost, uint32_t* __restrict__ queue_len) {
     __shared__ uint32_t base[kCostBuckets], local[kCostBuckets], gbase[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) local[i] = 0;
     if (threadIdx.x == 0) {
@@ -346,7 +351,7 @@ __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __
     uint32_t c = 0, rank = 0;
     if (tile < ntiles) {
         c = cost[tile];
-        rank = atomicAdd(&local[c], c >= split_min_cost ? 4u : 1u);
+        rank = atomicAdd(&local[c], split_ways(c, split_min_cost, split32_min_cost));
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x)
@@ -354,7 +359,10 @@ __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __
     __syncthreads();
     if (tile < ntiles) {
         uint32_t* o = order + base[c] + gbase[c] + rank;
-        if (c >= split_min_cost) { /* a heavy tile is dealt to four warps, one tile row (8 pixels + 24 helper lanes) each */
+        const uint32_t ways = split_ways(c, split_min_cost, split32_min_cost);
+        if (ways == 32u) { /* the heaviest tiles: one pixel per warp, 31 helper lanes */
+            for (uint32_t k = 0; k < 32u; k++) o[k] = tile | ((5u + k) << 24);
+        } else if (ways == 4u) { /* a heavy tile is dealt to four warps, one tile row (8 pixels + 24 helper lanes) each */
             o[0] = tile | (1u << 24); o[1] = tile | (2u << 24); o[2] = tile | (3u << 24); o[3] = tile | (4u << 24);
         } else o[0] = tile;
     }
@@ -509,12 +517,12 @@ cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d
     cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, (2 * kCostBuckets + 1) * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
     const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
-    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost);
+    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost);
     else tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     tile_order<<<(ntiles + 255) / 256, 256, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles,
-                                                    fp.split_min_cost, d_hist_cursor + 2 * kCostBuckets);
+                                                    fp.split_min_cost, fp.split32_min_cost, d_hist_cursor + 2 * kCostBuckets);
     return cudaGetLastError();
 }
 

@@ -72,6 +72,7 @@ struct RtFrameParams {
     uint32_t* tile_time;        /* per-tile wall time of THIS frame in units of 1024 SM clocks (zeroed before launch), or NULL */
     const uint32_t* tile_time_prev; /* the previous frame's, used as next cost estimate instead of the skeleton trace, or NULL */
     const uint32_t* queue_len;  /* number of queue entries when `order` is set (tiles + 3 per split tile) */
+    uint32_t split32_min_cost;  /* ... into 32 single-pixel entries (64 = never) */
     uint32_t split_min_cost;    /* tiles whose estimate reaches this are split into four 8x1 sub-tiles (64 = never) */
     uint32_t coop_min_cost;     /* tiles whose estimate reaches this walk in cooperative mode, the rest lane per pixel */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
@@ -90,7 +91,7 @@ struct RtLaunchShape {
 cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
 
 /* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[129] (zeroed here; word 128 receives the queue length),
- * d_order[4*ntiles]. */
+ * d_order[32*ntiles]. */
 cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                  cudaStream_t st);
 

@@ -61,7 +61,7 @@ __device__ __forceinline__ float coop_run_task(const Geo& g, const CoopSmem& cs,
 /* One 8x4 tile, all 32 lanes in lock step.  `live` = this lane owns a pixel of the frame.  Returns the pixel word. */
 template <bool COUNT, bool AOV>
 __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, const Geo& g, const CoopSmem& cs, uint32_t id,
-                                                    bool live, uint32_t lane, uint32_t& hit_id, Tally<COUNT>& tl) {
+                                                    bool live, uint32_t lane, uint32_t& hit_id, uint32_t& nseg, Tally<COUNT>& tl) {
     constexpr uint32_t kFull = 0xffffffffu;
     Saved st[kMaxDepth - 1];
     uint32_t rng = id; /* raytracing.cl:32-33 */
@@ -95,6 +95,7 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
         m.n = 1.0f; m.reflectivity = 0.0f; m.specular = 0.0f; m.diffuse = 0.0f;
         if (!done) {
             tl.add(RTB_SEGMENTS);
+            nseg++;
             RayF r;
             ray_setup_fast(r, o, d);
             Closest c;

@@ -159,11 +159,13 @@ def test_history_scheduling_does_not_change_pixels(engine, ref):
         engine.set_camera(c)
         want.append(engine.render_to_host(W, H, want_hit=True))
     engine.set_option("history", 1)
-    for thr in (33, 20, 1):
+    for thr, thr32 in ((33, 64), (20, 30), (1, 1), (1, 64)):
         engine.set_option("split_min_cost", thr)
+        engine.set_option("split32_min_cost", thr32)
         for rep in range(3):
             for c, (rgb0, hit0) in zip(cams, want):
                 engine.set_camera(c)
                 rgb, hit = engine.render_to_host(W, H, want_hit=True)
                 assert np.array_equal(rgb, rgb0) and np.array_equal(hit, hit0), (thr, rep)
     engine.set_option("split_min_cost", 0)
+    engine.set_option("split32_min_cost", 0)

@@ -13,8 +13,8 @@ eng = pkg.Engine(0)
 eng.upload_scene(s, p, l); eng.upload_images(0, tex); eng.upload_images(1, sky)
 eng.set_camera(host.camera(W=W, H=H, **host.RAYPNG_CAMERA))
 ref_frame = None
-for v in (64, 56, 48, 40, 32, 24, 16, 8):
-    eng.set_option("split_min_cost", v)
+for v, v32 in ((64, 64), (48, 64), (40, 64), (40, 50), (40, 48), (42, 48), (42, 50), (0, 0)):
+    eng.set_option("split_min_cost", v); eng.set_option("split32_min_cost", v32)
     row = []
     for parts in (1, 2, 4, 8):
         worst = 0.0
@@ -27,5 +27,5 @@ for v in (64, 56, 48, 40, 32, 24, 16, 8):
         row.append(worst)
     rgb, _ = eng.render_to_host(W, H, want_hit=False)
     if ref_frame is None: ref_frame = rgb
-    print("split_min_cost=%2d  kernel ms (slowest part): N=1 %.3f  N=2 %.3f  N=4 %.3f  N=8 %.3f  same_pixels=%s" %
-          (v, row[0], row[1], row[2], row[3], bool(np.array_equal(rgb, ref_frame))), flush=True)
+    print("split4>=%2d split32>=%2d  kernel ms (slowest part): N=1 %.3f  N=2 %.3f  N=4 %.3f  N=8 %.3f  same_pixels=%s" %
+          (v, v32, row[0], row[1], row[2], row[3], bool(np.array_equal(rgb, ref_frame))), flush=True)
