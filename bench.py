@@ -458,7 +458,8 @@ def gpu_body(args, pkg, eng, world, rank, local):
                     "readback": rb_stats,
                     "api": "cl_wrap_load_single_data x6 + cl_wrap_output(raygen) + cl_wrap_output(raytracer, read-back)"
                     if world == 1 else "rtb_set_camera + rtb_render(band, %s exchange) + D2H of the frame on rank 0" % exchange},
-            "gpu_launches": args.steps * world,
+            # per frame and rank: tile_cost_history + tile_order + render_frame (+ assemble_bands on rank 0 with --exchange nccl)
+            "gpu_launches": args.steps * (3 * world + (1 if exchange == "nccl" else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": ncu_traffic(wl["name"]),
                          "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/r01_v4_*); algorithmic bytes: 33.2 MB "

@@ -326,11 +326,14 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
         const bool same = e->time_valid && e->tk_W == W && e->tk_H == H && e->tk_total == total && e->tk_band == pp.band_rows &&
                           e->tk_parts == pp.parts && e->tk_part == pp.part && e->tk_scene_gen == e->scene_gen + e->T;
         if (e->opt_history && mode == 0) {
-            if (e->tile_time[0].ensure(nt * 4) || e->tile_time[1].ensure(nt * 4)) return -2;
-            fp.tile_time = (uint32_t*)e->tile_time[e->time_cur].p;
-            CU(cudaMemsetAsync(fp.tile_time, 0, nt * 4, e->stream), "reset tile times");
+            /* each buffer: 16 bytes for the frame's sum, then one word per tile */
+            if (e->tile_time[0].ensure(nt * 4 + 16) || e->tile_time[1].ensure(nt * 4 + 16)) return -2;
+            fp.tile_time_sum = (unsigned long long*)e->tile_time[e->time_cur].p;
+            fp.tile_time = (uint32_t*)((char*)e->tile_time[e->time_cur].p + 16);
+            CU(cudaMemsetAsync(e->tile_time[e->time_cur].p, 0, nt * 4 + 16, e->stream), "reset tile times");
             if (same) {
-                fp.tile_time_prev = (const uint32_t*)e->tile_time[1 - e->time_cur].p;
+                fp.tile_time_sum_prev = (const unsigned long long*)e->tile_time[1 - e->time_cur].p;
+                fp.tile_time_prev = (const uint32_t*)((const char*)e->tile_time[1 - e->time_cur].p + 16);
                 /* measured costs: heavy tiles go to four warps.  Automatic threshold from the sweep in tools/exp/sweep_split.py:
                  * ~500 us (cost 40) when the frame is a partition or small enough for one tile to bound the kernel,
                  * ~2 ms (48) for a whole 4K frame, where splitting only costs lane occupancy. */

@@ -76,6 +76,7 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
     Tally<COUNT> tl;
     tl.clear();
 
+    unsigned long long warp_time = 0; /* sum of this warp's tile times: the frame total gives the mean the next frame's costs are relative to */
     uint32_t next = 0;
     if (lane == 0) next = atomicAdd(fp.tile_counter, 1u);
     for (;;) {
@@ -111,7 +112,11 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
         __syncwarp();
         /* measured cost of this tile in units of 1024 SM clocks (sub-tiles add up): the next frame's scheduling hint.
          * (Segments traced -- nseg -- were tried as a split-invariant metric: worse order, tools/exp/sweep_split.py.) */
-        if (fp.tile_time && lane == 0) atomicAdd(fp.tile_time + tile, (uint32_t)((clock64() - tile_clk0) >> 10) + 1u);
+        if (fp.tile_time && lane == 0) {
+            const uint32_t dt = (uint32_t)((clock64() - tile_clk0) >> 10) + 1u;
+            atomicAdd(fp.tile_time + tile, dt);
+            warp_time += dt;
+        }
 #ifdef RT_TILE_TIMING
         {
             unsigned long long t_end;
@@ -163,6 +168,8 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
             if (AOV && fp.hit) fp.hit[at] = hid;
         }
     }
+
+    if (fp.tile_time && lane == 0 && warp_time) atomicAdd(fp.tile_time_sum, warp_time);
 
     if (COUNT) {
 #pragma unroll
@@ -315,16 +322,20 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
         if (shist[i]) atomicAdd(&hist[i], shist[i]);
 }
 
-/* ---- tile_cost_history: the previous frame's measured tile times as cost (4*log2 scale: 16 us ~ 20, 150 us ~ 33,
- * 800 us ~ 42).  Replaces the skeleton trace whenever a frame of the same geometry has just been rendered. ---- */
-__global__ void tile_cost_history(const uint32_t* __restrict__ prev, uint32_t* __restrict__ cost_out,
+/* ---- tile_cost_history: the previous frame's measured tile times as cost, RELATIVE to that frame's mean tile time:
+ * cost = 24 + 4*log2(t / mean), so the mean tile sits at 24, 16x the mean at 40, 64x at 48 -- whatever the scene's
+ * absolute speed (render.map: mean 29 us; the 1,024-sphere grid: 4.5 ms).  Replaces the skeleton trace whenever a frame of the same geometry has just been rendered. ---- */
+__global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsigned long long* __restrict__ prev_sum,
+                                  uint32_t* __restrict__ cost_out,
                                   uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost, uint32_t split32_min_cost) {
     __shared__ uint32_t shist[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
     __syncthreads();
     const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
     if (tile < ntiles) {
-        uint32_t c = (uint32_t)(4.0f * __log2f((float)prev[tile] + 1.0f));
+        const float mean = fmaxf((float)(*prev_sum) / (float)ntiles, 1.0f);
+        const float rel = 24.0f + 4.0f * __log2f(fmaxf((float)prev[tile], 0.5f) / mean);
+        uint32_t c = rel <= 0.0f ? 0u : (uint32_t)rel;
         c = c < kCostBuckets ? c : kCostBuckets - 1u;
         cost_out[tile] = c;
         atomicAdd(&shist[c], split_ways(c, split_min_cost, split32_min_cost));
@@ -517,7 +528,7 @@ cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d
     cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, (2 * kCostBuckets + 1) * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
     const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
-    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost);
+    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost);
     else tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;

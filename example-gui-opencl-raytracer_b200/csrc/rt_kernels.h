@@ -70,6 +70,8 @@ struct RtFrameParams {
     uint32_t tiles_x, tiles_y;
     const uint32_t* cost;       /* per-tile cost estimate (tile_cost), or NULL */
     uint32_t* tile_time;        /* per-tile wall time of THIS frame in units of 1024 SM clocks (zeroed before launch), or NULL */
+    unsigned long long* tile_time_sum;            /* sum of tile_time over the frame (zeroed before launch) */
+    const unsigned long long* tile_time_sum_prev; /* the previous frame's */
     const uint32_t* tile_time_prev; /* the previous frame's, used as next cost estimate instead of the skeleton trace, or NULL */
     const uint32_t* queue_len;  /* number of queue entries when `order` is set (tiles + 3 per split tile) */
     uint32_t split32_min_cost;  /* ... into 32 single-pixel entries (64 = never) */

@@ -13,7 +13,7 @@ eng = pkg.Engine(0)
 eng.upload_scene(s, p, l); eng.upload_images(0, tex); eng.upload_images(1, sky)
 eng.set_camera(host.camera(W=W, H=H, **host.RAYPNG_CAMERA))
 ref_frame = None
-for v, v32 in ((64, 64), (48, 64), (40, 64), (40, 50), (40, 48), (42, 48), (42, 50), (0, 0)):
+for v, v32 in ((64, 64), (48, 64), (44, 64), (40, 64), (40, 48), (36, 48), (40, 44), (0, 0)):
     eng.set_option("split_min_cost", v); eng.set_option("split32_min_cost", v32)
     row = []
     for parts in (1, 2, 4, 8):
