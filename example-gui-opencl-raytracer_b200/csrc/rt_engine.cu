@@ -1,6 +1,7 @@
 /* rt_engine.cu -- the C ABI of include/rtb200.h: device memory, uploads, launch bookkeeping.
  * No CPU rendering path exists here: every render call ends in rt_launch_render (rt_kernels.cu). */
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -334,11 +335,19 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
             if (same) {
                 fp.tile_time_sum_prev = (const unsigned long long*)e->tile_time[1 - e->time_cur].p;
                 fp.tile_time_prev = (const uint32_t*)((const char*)e->tile_time[1 - e->time_cur].p + 16);
-                /* measured costs: heavy tiles go to four warps.  Automatic threshold from the sweep in tools/exp/sweep_split.py:
-                 * ~500 us (cost 40) when the frame is a partition or small enough for one tile to bound the kernel,
-                 * ~2 ms (48) for a whole 4K frame, where splitting only costs lane occupancy. */
-                if (mode == 0) fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : (nt >= 200000 ? 48u : 40u);
-                if (mode == 0) fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : (nt >= 200000 ? 64u : 48u);
+                /* measured costs: a tile is a tail risk when its time is comparable to the time the whole queue needs,
+                 * T = mean * tiles / resident warps.  Automatic thresholds (they reproduce the optima of the sweeps in
+                 * tools/exp/sweep_split.py at N = 1, 2, 4, 8): four warps from 0.75 T, one pixel per warp from 3 T.
+                 * On the relative cost scale (24 + 4*log2(t / mean)) that is 24 + 4*log2(0.75 * tiles / warps) etc. */
+                if (mode == 0) {
+                    const double per_warp = (double)nt / (double)(e->sm_count * 20);
+                    auto thr = [&](double alpha, double floor_cost) { /* never below 16x (64x) the mean tile: splitting costs occupancy */
+                        double c = 24.0 + 4.0 * log2(alpha * per_warp) + 0.5;
+                        return (uint32_t)(c < floor_cost ? floor_cost : (c > 64.0 ? 64.0 : c));
+                    };
+                    fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(0.75, 40.0);
+                    fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : thr(3.0, 48.0);
+                }
             }
             e->time_cur = 1 - e->time_cur;
             e->time_valid = true;

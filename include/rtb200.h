@@ -111,9 +111,9 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * "history": 1 (default) = a frame of the same size/partition/scene as the previous one is scheduled from that frame's
  * MEASURED per-tile times (4*log2 cost scale) instead of the skeleton trace; 0 = always the skeleton trace.
  * "split_min_cost" (history frames only): tiles whose cost estimate reaches this value are dealt to four warps (one 8-pixel tile row each,
- * the other 24 lanes only run shadow tasks) so that no single warp owns a whole glass/mirror tile (64 = never, 0 = automatic: 40 for partitions, 48 for whole 4K+ frames).
- * "split32_min_cost": ... and from this value on to 32 warps, one pixel each (64 = never, 0 = automatic: 48 for
- * partitions, never for whole 4K+ frames).
+ * the other 24 lanes only run shadow tasks) so that no single warp owns a whole glass/mirror tile (64 = never, 0 = automatic: tiles longer than 0.75 x the queue's expected drain time).
+ * "split32_min_cost": ... and from this value on to 32 warps, one pixel each (64 = never, 0 = automatic: tiles
+ * longer than 3 x the expected drain time).
  * "coop_min_cost": tiles whose cost estimate (0..63) reaches this value use the cooperative walk, cheaper tiles the
  * per-lane walk (0 = all cooperative, 64 = none; scheduling only, pixels do not change). */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
