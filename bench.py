@@ -44,7 +44,7 @@ def ncu_traffic(workload):
         return None
     try:
         tot = 0.0
-        for ln in open(os.path.join(ROOT, "profiles", "r01_v4_render_frame_key_metrics.txt")):
+        for ln in open(os.path.join(ROOT, "profiles", "r01_v8_render_frame_key_metrics.txt")):
             k, unit, v = ln.split()[0], ln.split()[1], ln.split()[-1]
             if k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                 tot += float(v) * {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}[unit]
@@ -416,13 +416,44 @@ def gpu_body(args, pkg, eng, world, rank, local):
     if world == 1:
         e2e_ms, h2d, d2h, rb_stats = e2e_cl_wrap(pkg, wl, args, host_frame)
     else:
+        # e2e at N > 1: the frame must end up in HOST memory on rank 0.  Every rank maps the same POSIX shared-memory
+        # frame (each process page-locks its own mapping) and its render kernel stores its bands straight into it over
+        # its own PCIe link (rtb_set_mirror_frame with the host view): no gather, no D2H copy; the 4-byte all-reduce
+        # tells rank 0 that every rank's stream has drained.
+        shm_path = "/dev/shm/rtb200_frame_%s" % os.environ.get("MASTER_PORT", "0")
+        ok = torch.ones(1, dtype=torch.int32, device=dev)
+        if rank == 0:
+            try:
+                shm = np.memmap(shm_path, dtype=np.uint32, mode="w+", shape=(H * W,))
+                shm[:] = 0xFFFFFFFF
+            except Exception as ex:   # /dev/shm too small for this frame
+                print("shared host frame unavailable (%s)" % ex, file=sys.stderr)
+                ok.zero_()
+        dist.broadcast(ok, 0)
+        if int(ok.item()) == 0:
+            raise SystemExit("bench.py: cannot create the shared host frame in /dev/shm")
+        if rank != 0:
+            shm = np.memmap(shm_path, dtype=np.uint32, mode="r+", shape=(H * W,))
+        host_view, registered = eng.host_map(shm.ctypes.data, H * W * 4)
+        e2e_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+
         def step_e2e():
             eng.set_camera(wl["cam"])
-            step_device()
-            if rank == 0:
-                host_frame.copy_(frame, non_blocking=True)
+            eng.set_mirror_frame(host_view)
+            eng.render(W, H, part=part, d_out=band_buf.data_ptr())
+            dist.all_reduce(e2e_flag)
         t, _ = timed(step_e2e, args.steps, args.warmup, do_flush=False)
-        e2e_ms, h2d, d2h, rb_stats = t / args.steps, 14 * 4, H * W * 4, None
+        e2e_ok = None
+        if rank == 0:
+            e2e_ok = bool(np.array_equal(shm, frame.cpu().numpy().view(np.uint32)))
+        dist.barrier()
+        if registered:
+            eng.host_unregister(shm.ctypes.data)
+        del shm
+        dist.barrier()
+        if rank == 0:
+            os.unlink(shm_path)
+        e2e_ms, h2d, d2h, rb_stats = t / args.steps, 14 * 4, H * W * 4, {"shared_host_frame_equals_device_frame": e2e_ok}
 
     t_ms = torch.tensor([total_ms, e2e_ms, float(np.mean(kernel_ms))], dtype=torch.float64, device=dev)
     if world > 1:
@@ -457,12 +488,13 @@ def gpu_body(args, pkg, eng, world, rank, local):
                     "frames_per_s": 1e3 / e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "readback": rb_stats,
                     "api": "cl_wrap_load_single_data x6 + cl_wrap_output(raygen) + cl_wrap_output(raytracer, read-back)"
-                    if world == 1 else "rtb_set_camera + rtb_render(band, %s exchange) + D2H of the frame on rank 0" % exchange},
+                    if world == 1 else "rtb_set_camera + rtb_render(band) on every rank with the frame mirrored into a shared HOST frame "
+                                          "(POSIX shm, page-locked by each rank) + 4-byte all-reduce"},
             # per frame and rank: tile_cost_history + tile_order + render_frame (+ assemble_bands on rank 0 with --exchange nccl)
             "gpu_launches": args.steps * (3 * world + (1 if exchange == "nccl" else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": ncu_traffic(wl["name"]),
-                         "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/r01_v4_*); algorithmic bytes: 33.2 MB "
+                         "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/r01_v8_*); algorithmic bytes: 33.2 MB "
                                          "frame + <= 4 B per texel fetch; the kernel is FP32-issue bound, not HBM bound",
                          "kernel": "render_frame", "kernel_ms": float(np.mean(kernel_ms)),
                          "peak_source": "%d SMs x 128 lanes x 2 flop x %.0f MHz (MEASURED_PEAKS.json sm_max_mhz); no tensor/HBM bound applies"

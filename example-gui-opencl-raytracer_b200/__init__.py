@@ -212,6 +212,17 @@ class Engine:
         """The next render also stores every word at d_frame[y*W + x] (a full frame, typically a peer GPU's)."""
         _check(lib().rtb_set_mirror_frame(self._h, C.c_void_p(d_frame)), "rtb_set_mirror_frame")
 
+    @staticmethod
+    def host_map(host_ptr, nbytes):
+        """Device-visible alias of a host buffer (page-locks it if needed) -> (device view, registered_here)."""
+        d, r = C.c_void_p(), C.c_int()
+        _check(lib().rtb_host_map(C.c_void_p(host_ptr), nbytes, C.byref(d), C.byref(r)), "rtb_host_map")
+        return d.value, bool(r.value)
+
+    @staticmethod
+    def host_unregister(host_ptr):
+        lib().rtb_host_unregister(C.c_void_p(host_ptr))
+
     def ipc_export(self, dptr):
         h = C.create_string_buffer(64)
         _check(lib().rtb_ipc_export(self._h, dptr, h), "rtb_ipc_export")
