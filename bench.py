@@ -336,6 +336,8 @@ def gpu_body(args, pkg, eng, world, rank, local):
     def step_device():
         """One frame, everything on the engine's stream; frame stays in HBM (rank 0)."""
         if exchange == "p2p":
+            if dbg is not None:
+                e0 = torch.cuda.Event(enable_timing=True); e0.record(stream)
             eng.set_mirror_frame(target)
             eng.render(W, H, part=part, d_out=band_buf.data_ptr())
             if dbg is not None:
@@ -343,7 +345,7 @@ def gpu_body(args, pkg, eng, world, rank, local):
             dist.all_reduce(done_flag)               # completion only: the pixels already travelled with the stores
             if dbg is not None:
                 e2 = torch.cuda.Event(enable_timing=True); e2.record(stream)
-                dbg.append((eng, e1, e2))
+                dbg.append((e0, e1, e2, eng.last_kernel_ms() if len(dbg) % 8 == 7 else None))
             return
         eng.render(W, H, part=part, d_out=band_buf.data_ptr())
         if world > 1:
@@ -408,9 +410,10 @@ def gpu_body(args, pkg, eng, world, rank, local):
     clocks = clk.summary()
     if dbg:
         torch.cuda.synchronize()
-        ar = [a.elapsed_time(b) for _, a, b in dbg[-10:]]
-        print("rank %d: all_reduce span ms (kernel end -> collective end): %s; last_render_ms %.3f" %
-              (rank, ["%.3f" % x for x in ar], eng.last_render_ms()), file=sys.stderr)
+        rs = [a.elapsed_time(b) for a, b, _, _ in dbg[-12:]]
+        ar = [b.elapsed_time(c) for _, b, c, _ in dbg[-12:]]
+        print("rank %d: render span (memsets+hint+order+kernel) median %.3f max %.3f; all_reduce span median %.3f max %.3f" %
+              (rank, float(np.median(rs)), max(rs), float(np.median(ar)), max(ar)), file=sys.stderr)
 
     # ---- end to end through the public API with host buffers ----
     if world == 1:
