@@ -320,17 +320,40 @@ def gpu_body(args, pkg, eng, world, rank, local):
         class _Raw:
             def __init__(self, ptr, n):
                 self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 3}
+        okf = torch.ones(1, dtype=torch.int32, device=dev)
+        handle = torch.zeros(64, dtype=torch.uint8, device=dev)
         if rank == 0:
-            raw_frame = eng.dev_alloc(H * W * 4)
-            handle = torch.tensor(list(eng.ipc_export(raw_frame)), dtype=torch.uint8, device=dev)
-            frame = torch.as_tensor(_Raw(raw_frame.value, H * W), device=dev)
-            target = raw_frame.value
-        else:
-            handle = torch.empty(64, dtype=torch.uint8, device=dev)
+            try:
+                if os.environ.get("BENCH_FORCE_NO_IPC"):
+                    raise RuntimeError("forced by BENCH_FORCE_NO_IPC")
+                raw_frame = eng.dev_alloc(H * W * 4)
+                handle = torch.tensor(list(eng.ipc_export(raw_frame)), dtype=torch.uint8, device=dev)
+            except Exception as ex:
+                print("CUDA IPC export failed (%s): falling back to --exchange nccl" % ex, file=sys.stderr)
+                okf.zero_()
         dist.broadcast(handle, 0)
-        if rank != 0:
-            peer_frame = eng.ipc_open(bytes(handle.cpu().tolist()))
-            target = peer_frame.value
+        dist.broadcast(okf, 0)
+        if int(okf.item()) == 1 and rank != 0:
+            try:
+                peer_frame = eng.ipc_open(bytes(handle.cpu().tolist()))
+                target = peer_frame.value
+            except Exception as ex:
+                print("CUDA IPC open failed on rank %d (%s): falling back to --exchange nccl" % (rank, ex), file=sys.stderr)
+                okf.zero_()
+        dist.all_reduce(okf, op=dist.ReduceOp.MIN)
+        if int(okf.item()) == 1:
+            if rank == 0:
+                frame = torch.as_tensor(_Raw(raw_frame.value, H * W), device=dev)
+                target = raw_frame.value
+        else:
+            if peer_frame is not None:
+                eng.ipc_close(peer_frame)
+                peer_frame = None
+            dist.barrier()
+            if raw_frame is not None:
+                eng.dev_free(raw_frame)
+                raw_frame = None
+            exchange = "nccl"
         done_flag = torch.zeros(1, dtype=torch.int32, device=dev)
 
     def step_device():
@@ -425,38 +448,59 @@ def gpu_body(args, pkg, eng, world, rank, local):
         # tells rank 0 that every rank's stream has drained.
         shm_path = "/dev/shm/rtb200_frame_%s" % os.environ.get("MASTER_PORT", "0")
         ok = torch.ones(1, dtype=torch.int32, device=dev)
+        shm = None
         if rank == 0:
             try:
+                if os.environ.get("BENCH_FORCE_NO_SHM"):
+                    raise RuntimeError("forced by BENCH_FORCE_NO_SHM")
                 shm = np.memmap(shm_path, dtype=np.uint32, mode="w+", shape=(H * W,))
                 shm[:] = 0xFFFFFFFF
-            except Exception as ex:   # /dev/shm too small for this frame
-                print("shared host frame unavailable (%s)" % ex, file=sys.stderr)
+            except Exception as ex:   # /dev/shm missing or too small for this frame
+                print("shared host frame unavailable (%s): e2e falls back to a D2H copy on rank 0" % ex, file=sys.stderr)
                 ok.zero_()
         dist.broadcast(ok, 0)
-        if int(ok.item()) == 0:
-            raise SystemExit("bench.py: cannot create the shared host frame in /dev/shm")
-        if rank != 0:
-            shm = np.memmap(shm_path, dtype=np.uint32, mode="r+", shape=(H * W,))
-        host_view, registered = eng.host_map(shm.ctypes.data, H * W * 4)
-        e2e_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        use_shm = int(ok.item()) == 1
+        if use_shm and rank != 0:
+            try:
+                shm = np.memmap(shm_path, dtype=np.uint32, mode="r+", shape=(H * W,))
+            except Exception:
+                ok.zero_()
+        if use_shm:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            use_shm = int(ok.item()) == 1
+        if use_shm:
+            host_view, registered = eng.host_map(shm.ctypes.data, H * W * 4)
+            e2e_flag = torch.zeros(1, dtype=torch.int32, device=dev)
 
-        def step_e2e():
-            eng.set_camera(wl["cam"])
-            eng.set_mirror_frame(host_view)
-            eng.render(W, H, part=part, d_out=band_buf.data_ptr())
-            dist.all_reduce(e2e_flag)
-        t, _ = timed(step_e2e, args.steps, args.warmup, do_flush=False)
-        e2e_ok = None
-        if rank == 0:
-            e2e_ok = bool(np.array_equal(shm, frame.cpu().numpy().view(np.uint32)))
+            def step_e2e():
+                eng.set_camera(wl["cam"])
+                eng.set_mirror_frame(host_view)
+                eng.render(W, H, part=part, d_out=band_buf.data_ptr())
+                dist.all_reduce(e2e_flag)
+            t, _ = timed(step_e2e, args.steps, args.warmup, do_flush=False)
+            e2e_ok = None
+            if rank == 0:
+                e2e_ok = bool(np.array_equal(shm, frame.cpu().numpy().view(np.uint32)))
+            dist.barrier()
+            if registered:
+                eng.host_unregister(shm.ctypes.data)
+            rb_stats = {"shared_host_frame_equals_device_frame": e2e_ok}
+            e2e_api = ("rtb_set_camera + rtb_render(band) on every rank with the frame mirrored into a shared HOST frame "
+                       "(POSIX shm, page-locked by each rank) + 4-byte all-reduce")
+        else:
+            def step_e2e():
+                eng.set_camera(wl["cam"])
+                step_device()
+                if rank == 0:
+                    host_frame.copy_(frame, non_blocking=True)
+            t, _ = timed(step_e2e, args.steps, args.warmup, do_flush=False)
+            rb_stats = None
+            e2e_api = "rtb_set_camera + rtb_render(band, %s exchange) + D2H of the frame on rank 0" % exchange
+        shm = None
         dist.barrier()
-        if registered:
-            eng.host_unregister(shm.ctypes.data)
-        del shm
-        dist.barrier()
-        if rank == 0:
+        if rank == 0 and os.path.exists(shm_path):
             os.unlink(shm_path)
-        e2e_ms, h2d, d2h, rb_stats = t / args.steps, 14 * 4, H * W * 4, {"shared_host_frame_equals_device_frame": e2e_ok}
+        e2e_ms, h2d, d2h = t / args.steps, 14 * 4, H * W * 4
 
     t_ms = torch.tensor([total_ms, e2e_ms, float(np.mean(kernel_ms))], dtype=torch.float64, device=dev)
     if world > 1:
@@ -491,8 +535,7 @@ def gpu_body(args, pkg, eng, world, rank, local):
                     "frames_per_s": 1e3 / e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "readback": rb_stats,
                     "api": "cl_wrap_load_single_data x6 + cl_wrap_output(raygen) + cl_wrap_output(raytracer, read-back)"
-                    if world == 1 else "rtb_set_camera + rtb_render(band) on every rank with the frame mirrored into a shared HOST frame "
-                                          "(POSIX shm, page-locked by each rank) + 4-byte all-reduce"},
+                    if world == 1 else e2e_api},
             # per frame and rank: tile_cost_history + tile_order + render_frame (+ assemble_bands on rank 0 with --exchange nccl)
             "gpu_launches": args.steps * (3 * world + (1 if exchange == "nccl" else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
