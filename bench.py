@@ -435,8 +435,11 @@ def gpu_body(args, pkg, eng, world, rank, local):
         torch.cuda.synchronize()
         rs = [a.elapsed_time(b) for a, b, _, _ in dbg[-12:]]
         ar = [b.elapsed_time(c) for _, b, c, _ in dbg[-12:]]
-        print("rank %d: render span (memsets+hint+order+kernel) median %.3f max %.3f; all_reduce span median %.3f max %.3f" %
-              (rank, float(np.median(rs)), max(rs), float(np.median(ar)), max(ar)), file=sys.stderr)
+        kin = [k for _, _, _, k in dbg if k is not None]
+        print("rank %d: render span (memsets+hint+order+kernel) median %.3f max %.3f; all_reduce span median %.3f max %.3f; "
+              "render_frame alone inside the loop %s; loop wall per step %.3f ms" %
+              (rank, float(np.median(rs)), max(rs), float(np.median(ar)), max(ar), ["%.3f" % k for k in kin],
+               wall * 1e3 / (args.steps + args.warmup)), file=sys.stderr)
 
     # ---- end to end through the public API with host buffers ----
     if world == 1:
