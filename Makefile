@@ -41,9 +41,14 @@ timing: all
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -DRT_TILE_TIMING -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_timing.o 2> /dev/null
 	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
 
+# A/B build of the render kernels with extra defines: make variant NAME=narrow DEFS=-DRT_COOP_WIDE=0 ; RTB_LIB=.../librtb200_narrow.so
+variant: all
+	$(NVCC) $(NVFLAGS) $(KFLAGS) $(DEFS) -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_$(NAME).o 2> /dev/null
+	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_$(NAME).so /tmp/rt_kernels_$(NAME).o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
+
 oracle:
 	$(MAKE) -C oracle
 
 clean:
 	rm -f $(OBJS) $(PKG)/librtb200.so $(CSRC)/*.ptxas.log
-.PHONY: all oracle clean timing
+.PHONY: all oracle clean timing variant

@@ -205,7 +205,8 @@ void cl_wrap_load_images(cl_wrap* wrap, cl_uint kernel_id, cl_uint arg_id, cl_me
             printf("ERROR:\t\"%s\" must have a depth of 8 bits and be RGB\n", filename);
             exit(1);
         }
-        rc = rtpng_read_rgb8_to_rgba(filename, images + (size_t)i * 4 * w * h, w, h);
+        /* RTB_IMAGE_CACHE=<dir>: decoded texels are kept there and re-read on the next start (N3) */
+        rc = rtpng_read_rgb8_to_rgba_cached(filename, images + (size_t)i * 4 * w * h, w, h, getenv("RTB_IMAGE_CACHE"), NULL);
         if (rc != RTPNG_OK) {
             free(images);
             printf("ERROR:\tCould not decode \"%s\" (%d)\n", filename, rc);

@@ -1,7 +1,13 @@
 /* png_io.c -- see png_io.h. */
+#ifndef _GNU_SOURCE
+#define _GNU_SOURCE /* realpath, st_mtim */
+#endif
 #include "png_io.h"
 
+#include <limits.h>
 #include <stdio.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <stdlib.h>
 #include <string.h>
 #include <zlib.h>
@@ -113,17 +119,26 @@ int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t
         const unsigned char* up = y ? raw + (stride + 1) * (y - 1) + 1 : NULL;
         int ft = cur[-1];
         if (ft > 4) { free(raw); return RTPNG_ECORRUPT; }
-        for (size_t i = 0; i < stride; i++) {
-            int a = i >= 3 ? cur[i - 3] : 0, b = up ? up[i] : 0, c = (up && i >= 3) ? up[i - 3] : 0;
-            int x = cur[i];
-            switch (ft) {
-                case 1: x += a; break;
-                case 2: x += b; break;
-                case 3: x += (a + b) >> 1; break;
-                case 4: x += paeth(a, b, c); break;
-                default: break;
-            }
-            cur[i] = (unsigned char)x;
+        /* one loop per filter type (the type is per row); the first pixel has no left neighbour */
+        const size_t head = stride < 3 ? stride : 3;
+        switch (ft) {
+            case 1:
+                for (size_t i = 3; i < stride; i++) cur[i] = (unsigned char)(cur[i] + cur[i - 3]);
+                break;
+            case 2:
+                if (up) for (size_t i = 0; i < stride; i++) cur[i] = (unsigned char)(cur[i] + up[i]);
+                break;
+            case 3:
+                for (size_t i = 0; i < head; i++) cur[i] = (unsigned char)(cur[i] + ((up ? up[i] : 0) >> 1));
+                if (up) for (size_t i = 3; i < stride; i++) cur[i] = (unsigned char)(cur[i] + ((cur[i - 3] + up[i]) >> 1));
+                else for (size_t i = 3; i < stride; i++) cur[i] = (unsigned char)(cur[i] + (cur[i - 3] >> 1));
+                break;
+            case 4:
+                for (size_t i = 0; i < head; i++) cur[i] = (unsigned char)(cur[i] + paeth(0, up ? up[i] : 0, 0));
+                if (up) for (size_t i = 3; i < stride; i++) cur[i] = (unsigned char)(cur[i] + paeth(cur[i - 3], up[i], up[i - 3]));
+                else for (size_t i = 3; i < stride; i++) cur[i] = (unsigned char)(cur[i] + cur[i - 3]); /* paeth(a,0,0) = a */
+                break;
+            default: break;
         }
         uint8_t* o = dst + (size_t)y * w * 4;
         for (uint32_t xx = 0; xx < w; xx++) {
@@ -131,6 +146,60 @@ int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t
         }
     }
     free(raw);
+    return RTPNG_OK;
+}
+
+/* ---- N3: decoded-texel cache ------------------------------------------------------------
+ * One file per source image under cache_dir: a 40-byte header {magic, w, h, source size, source mtime (ns)}
+ * followed by the w*h RGBA8 texels exactly as rtpng_read_rgb8_to_rgba produces them.  A hit is a plain read;
+ * any mismatch (other size/mtime/dimensions, short file) is a miss and the entry is rewritten.  Failing to
+ * write the cache is not an error. */
+typedef struct {
+    char magic[8];
+    uint32_t w, h;
+    uint64_t src_size, src_mtime_ns;
+    uint64_t reserved;
+} tex_cache_header;
+
+static uint64_t fnv1a64(const char* s) {
+    uint64_t hsh = 1469598103934665603ull;
+    for (; *s; s++) { hsh ^= (unsigned char)*s; hsh *= 1099511628211ull; }
+    return hsh;
+}
+
+int rtpng_read_rgb8_to_rgba_cached(const char* path, uint8_t* dst, uint32_t w, uint32_t h, const char* cache_dir, int* hit) {
+    if (hit) *hit = 0;
+    struct stat sb;
+    if (!cache_dir || !*cache_dir || stat(path, &sb) != 0) return rtpng_read_rgb8_to_rgba(path, dst, w, h);
+    char full[PATH_MAX];
+    if (!realpath(path, full)) return rtpng_read_rgb8_to_rgba(path, dst, w, h);
+    tex_cache_header want;
+    memset(&want, 0, sizeof want);
+    memcpy(want.magic, "RTBTEX1", 8);
+    want.w = w; want.h = h;
+    want.src_size = (uint64_t)sb.st_size;
+    want.src_mtime_ns = (uint64_t)sb.st_mtim.tv_sec * 1000000000ull + (uint64_t)sb.st_mtim.tv_nsec;
+    const size_t nbytes = (size_t)w * h * 4;
+    char entry[PATH_MAX + 64];
+    snprintf(entry, sizeof entry, "%s/%016llx.rgba", cache_dir, (unsigned long long)fnv1a64(full));
+    FILE* fp = fopen(entry, "rb");
+    if (fp) {
+        tex_cache_header got;
+        int ok = fread(&got, sizeof got, 1, fp) == 1 && memcmp(&got, &want, sizeof got) == 0 &&
+                 fread(dst, 1, nbytes, fp) == nbytes && fgetc(fp) == EOF;
+        fclose(fp);
+        if (ok) { if (hit) *hit = 1; return RTPNG_OK; }
+    }
+    int rc = rtpng_read_rgb8_to_rgba(path, dst, w, h);
+    if (rc != RTPNG_OK) return rc;
+    char tmp[PATH_MAX + 96];
+    snprintf(tmp, sizeof tmp, "%s.%ld.tmp", entry, (long)getpid());
+    fp = fopen(tmp, "wb");
+    if (fp) { /* write aside, then rename: readers never see a half-written entry */
+        int ok = fwrite(&want, sizeof want, 1, fp) == 1 && fwrite(dst, 1, nbytes, fp) == nbytes;
+        ok = (fclose(fp) == 0) && ok;
+        if (!ok || rename(tmp, entry) != 0) remove(tmp);
+    }
     return RTPNG_OK;
 }
 

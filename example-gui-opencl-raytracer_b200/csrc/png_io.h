@@ -15,6 +15,10 @@ enum { RTPNG_OK = 0, RTPNG_EOPEN = -1, RTPNG_ENOTPNG = -2, RTPNG_EFORMAT = -3, R
 int rtpng_info(const char* path, uint32_t* w, uint32_t* h, int* bit_depth, int* colour_type, int* interlace);
 /* Decode an 8-bit RGB file into w*h RGBA8 texels with A = 255 (png_set_filler(255, AFTER)), row 0 = top. */
 int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t h);
+/* Same texels through a decoded-texel cache: cache_dir NULL or "" = no cache.  *hit (may be
+ * NULL) is set to 1 when the texels came from the cache.  The entry is keyed by the source's real path and
+ * validated against its size, mtime and dimensions. */
+int rtpng_read_rgb8_to_rgba_cached(const char* path, uint8_t* dst, uint32_t w, uint32_t h, const char* cache_dir, int* hit);
 /* Write w*h RGB8 pixels (row 0 = top) as a non-interlaced 8-bit RGB PNG. */
 int rtpng_write_rgb8(const char* path, const uint8_t* rgb, uint32_t w, uint32_t h);
 /* Same, onto an open stream (left open). */

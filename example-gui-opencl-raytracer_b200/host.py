@@ -121,9 +121,14 @@ def orbit_camera(frame, frames, W, H, centre=(0.5, 1.0, 1.0), radius=9.5, height
 
 
 # ---- image arrays ---------------------------------------------------------------------------------
-def load_png_layers(paths):
-    """-> (layers, h, w, 4) uint8, A = 255; every file must be 8-bit RGB of equal size."""
+def load_png_layers(paths, cache_dir=None):
+    """-> (layers, h, w, 4) uint8, A = 255; every file must be 8-bit RGB of equal size.
+    cache_dir (default: $RTB_IMAGE_CACHE, like cl_wrap_load_images): decoded texels are kept there."""
     L = lib()
+    if cache_dir is None:
+        cache_dir = os.environ.get("RTB_IMAGE_CACHE", "")
+    L.rtpng_read_rgb8_to_rgba_cached.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_char_p, C.POINTER(C.c_int)]
+    L.rtpng_read_rgb8_to_rgba_cached.restype = C.c_int
     L.rtpng_info.argtypes = [C.c_char_p] + [C.POINTER(C.c_uint32)] * 2 + [C.POINTER(C.c_int)] * 3
     L.rtpng_info.restype = C.c_int
     L.rtpng_read_rgb8_to_rgba.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
@@ -141,7 +146,8 @@ def load_png_layers(paths):
             out = np.empty((len(paths), h.value, w.value, 4), np.uint8)
         elif (h.value, w.value) != out.shape[1:3]:
             raise ValueError("All images must have same dimensions")
-        rc = L.rtpng_read_rgb8_to_rgba(p.encode(), out[i].ctypes.data_as(C.c_void_p), w.value, h.value)
+        rc = L.rtpng_read_rgb8_to_rgba_cached(p.encode(), out[i].ctypes.data_as(C.c_void_p), w.value, h.value,
+                                              cache_dir.encode(), None)
         if rc != 0:
             raise IOError("%s: cannot decode (%d)" % (p, rc))
     return out

@@ -90,6 +90,94 @@ def test_png_codec_decodes_assets_exactly(pkg, ref):
         host.load_png_layers(["/tmp/rtb_gray.png"])
 
 
+def _png_with_filter(path, img, ftype):
+    """Hand-made 8-bit RGB PNG whose every row (the first included) uses filter `ftype`."""
+    import struct, zlib
+    h, w, _ = img.shape
+    rows = img.reshape(h, w * 3).astype(np.int32)
+    raw = bytearray()
+    for y in range(h):
+        cur = rows[y]
+        up = rows[y - 1] if y else np.zeros_like(cur)
+        a = np.concatenate([np.zeros(3, np.int32), cur[:-3]])
+        c = np.concatenate([np.zeros(3, np.int32), up[:-3]])
+        if ftype == 0: pred = 0
+        elif ftype == 1: pred = a
+        elif ftype == 2: pred = up
+        elif ftype == 3: pred = (a + up) >> 1
+        else:
+            pp = a + up - c
+            pa, pb, pc = abs(pp - a), abs(pp - up), abs(pp - c)
+            pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, up, c))
+        raw.append(ftype)
+        raw += ((cur - pred) & 255).astype(np.uint8).tobytes()
+    def chunk(t, d):
+        return struct.pack(">I", len(d)) + t + d + struct.pack(">I", zlib.crc32(t + d))
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 0)) +
+                chunk(b"IDAT", zlib.compress(bytes(raw))) + chunk(b"IEND", b""))
+
+
+def test_png_decoder_every_filter_type(pkg, tmp_path):
+    from example_gui_opencl_raytracer_b200 import host
+    rng = np.random.default_rng(7)
+    for (h, w) in ((1, 1), (5, 2), (19, 33)):
+        img = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+        for ft in range(5):
+            p = str(tmp_path / ("f%d_%dx%d.png" % (ft, w, h)))
+            _png_with_filter(p, img, ft)
+            got = host.load_png_layers([p], cache_dir="")
+            assert np.array_equal(got[0, :, :, :3], img), (ft, h, w)
+            assert (got[..., 3] == 255).all()
+
+
+def test_decoded_texel_cache(pkg, tmp_path):
+    """a hit returns the decoder's bytes; a changed source or a damaged entry is a miss."""
+    from example_gui_opencl_raytracer_b200 import host
+    L = pkg.lib()
+    fn = L.rtpng_read_rgb8_to_rgba_cached
+    fn.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_char_p, C.POINTER(C.c_int)]
+    cache = tmp_path / "cache"
+    cache.mkdir()
+    src = str(tmp_path / "a.png")
+    img = np.random.default_rng(3).integers(0, 256, size=(21, 40, 3), dtype=np.uint8)
+    _png_with_filter(src, img, 4)
+
+    def read():
+        out = np.zeros((21, 40, 4), np.uint8)
+        hit = C.c_int(-1)
+        assert fn(src.encode(), out.ctypes.data_as(C.c_void_p), 40, 21, str(cache).encode(), C.byref(hit)) == 0
+        return out, hit.value
+
+    a, h0 = read()
+    b, h1 = read()
+    assert (h0, h1) == (0, 1) and np.array_equal(a, b) and np.array_equal(a[..., :3], img)
+    entries = os.listdir(cache)
+    assert len(entries) == 1 and entries[0].endswith(".rgba")
+    # damaged entry (truncated): miss, rewritten
+    e = os.path.join(cache, entries[0])
+    blob = open(e, "rb").read()
+    assert len(blob) == 40 + 21 * 40 * 4
+    open(e, "wb").write(blob[:-5])
+    c, h2 = read()
+    d, h3 = read()
+    assert (h2, h3) == (0, 1) and np.array_equal(c, a) and np.array_equal(d, a)
+    # the source changes (other pixels, other mtime/size): miss, new texels
+    img2 = 255 - img
+    _png_with_filter(src, img2, 1)
+    os.utime(src, ns=(1, 1))
+    f, h4 = read()
+    assert h4 == 0 and np.array_equal(f[..., :3], img2)
+    # no cache directory -> plain decode; unwritable cache directory is not an error
+    out = np.zeros((21, 40, 4), np.uint8)
+    assert fn(src.encode(), out.ctypes.data_as(C.c_void_p), 40, 21, b"", None) == 0
+    assert fn(src.encode(), out.ctypes.data_as(C.c_void_p), 40, 21, b"/nonexistent/dir", None) == 0
+    assert np.array_equal(out[..., :3], img2)
+    # the Python loader takes the same cache
+    g = host.load_png_layers([src], cache_dir=str(cache))
+    assert np.array_equal(g[0, :, :, :3], img2)
+
+
 def test_synthetic_scene_is_deterministic(pkg):
     from example_gui_opencl_raytracer_b200 import host
     a = host.sphere_grid_scene(32)
