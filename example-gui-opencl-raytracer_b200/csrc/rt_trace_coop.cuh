@@ -32,8 +32,8 @@ namespace RT_NS {
 #endif
 constexpr int kCoopLights = RT_COOP_LIGHTS;                      /* lights per chunk */
 constexpr int kPreS = RT_PRE_S, kPreRec = kPreS ? kPreS + 1 : 0;                    /* R8: per-owner records: <= 8 padded spheres + 1 of <= 4 plane numerators */
-constexpr int kCoopTasks = 32 * kCoopLights * kShadowSamples;    /* 192 */
-constexpr uint32_t kCoopBytesPerWarp = 32 * 16 + kCoopTasks * 16 + 32 * kCoopLights * 16 + 32 * kPreRec * 16; /* 9728 */
+constexpr int kCoopTasks = 32 * kCoopLights * kShadowSamples;    /* 256 */
+constexpr uint32_t kCoopBytesPerWarp = 32 * 16 + kCoopTasks * 16 + 32 * kCoopLights * 16 + 32 * kPreRec * 16; /* 6656 */
 
 struct CoopSmem {
     float4* owner; /* [32] {ip.xyz, -} */
@@ -173,7 +173,7 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
                     bool post = false;
                     float th0 = 0.0f, ph0 = 0.0f, th1 = 0.0f, ph1 = 0.0f;
                     float dist = 1.0f, sx = 0.0f, dif = 0.0f;
-                    uint32_t bits = 0; /* bit 0: tasks posted; bit 1: spec_zero; bit 2: diff_zero; bits 8..: first task slot */
+                    uint32_t bits = 0; /* bit 0: tasks posted; bit 1: spec_zero; bit 2: diff_zero; bit 3: pow may be inf; bits 8..: first task slot */
                     if (shade) {
                         const float4 l0 = g.lgeo[i];
                         V3 sdir = normalize_len(xyz(l0) - ip, dist);
@@ -183,8 +183,10 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
                         sx = 0.0f < ndh ? ndh : 0.0f;
                         float ndl = dot3(nrm, sdir);
                         dif = 0.0f < ndl ? ndl : 0.0f;
-                        /* R5: exact zeros */
-                        const bool spec_zero = (fs == 0.0f) || (sx == 0.0f && shin > 0.0f);
+                        /* R5: exact zeros -- only while pow(sx, shin) is finite (see rt_trace_fast.cuh) */
+                        const bool tame = sx <= 1.0f && shin >= 0.0f;
+                        if (!tame) bits |= 8u;
+                        const bool spec_zero = tame && ((fs == 0.0f) || (sx == 0.0f && shin > 0.0f));
                         const bool diff_zero = (fd == 0.0f) || (dif == 0.0f);
                         if (spec_zero) bits |= 2u;
                         if (diff_zero) bits |= 4u;
@@ -229,7 +231,7 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
                         const float r0 = reinterpret_cast<const float*>(cs.task + a)[0];
                         const float r1 = reinterpret_cast<const float*>(cs.task + a + 1)[0];
                         const float soft = (0.0f + r0) + r1;
-                        if (soft == 0.0f) continue; /* light_rgb *= 0: both terms are exact zeros */
+                        if (soft == 0.0f && !(bits & 8u)) continue; /* light_rgb *= 0: both terms are exact zeros */
                         const float ssr = soft / (float)kShadowSamples;
                         const float4 l1 = g.laux[c0 + k];
                         V3 lrgb = div3_pos(xyz(l1) * 1.0f, rec.x * rec.x) * ssr;

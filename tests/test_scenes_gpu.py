@@ -76,6 +76,23 @@ def test_plane_with_undefined_tangent_basis(fresh, ref, scene, host):
              ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA), W, H)
 
 
+@pytest.mark.parametrize("trace", [0, 2, 3])
+def test_infinite_specular_in_shadow_is_nan_not_zero(fresh, ref, scene, host, trace):
+    """A non-unit plane normal makes max(0, n.h) exceed 1, so pow(.., 100) overflows to +inf.  In full shadow the reference computes (0 * specular) * inf = NaN and the pixel packs
+    to black; where lit it saturates.  The fast traces' "exact zero" shortcuts (R5) must not apply there
+    (found by tests/test_fuzz_gpu.py seed 32)."""
+    shiny = dict(host.STONE, rgb=(.6, .5, .9), diffuse=0.0, specular=0.6, shininess=100)
+    odd = dict(host.PLASTIC, rgb=(.2, .8, .3), shininess=0)
+    pl = host.plane((0, 6.0, 0), (0, 0, 0), shiny) + host.plane((0, 0, -1), (0, 0, 8), odd)
+    sp = host.sphere((0.0, 1.0, 2.0), 1.0, dict(host.PLASTIC, rgb=(1, 0, 0))) + \
+        host.sphere((-2.5, 0.8, 3.0), 0.8, dict(host.PLASTIC, rgb=(0, 0, 1), shininess=0))
+    li = host.light((1.5, 4.0, 0.0), .1, 30.0, (1, 1, 1)) + host.light((-3.0, 2.0, -1.0), .1, 12.0, (1, .8, .6))
+    W, H = 192, 128
+    fresh.set_option("trace", trace)
+    run_both(ref, scene, fresh, sp, pl, li, host.camera(origin=(0.5, 2.5, -5.0), look=(0, -0.25, 1.0), fov=90.0,
+                                                       focal=1.0, W=W, H=H), W, H)
+
+
 def test_glass_in_glass_and_mirror_corridor(fresh, ref, scene, host):
     """Nested dielectric spheres (Q4: no nested media), two facing mirrors (stack runs to MAX_DEPTH), a light
     in view (Q20) and a glass sphere in front of it (Q19)."""
