@@ -282,6 +282,9 @@ def gpu_body(args, pkg, eng, world, rank, local):
     eng.upload_images(0, tex)
     eng.upload_images(1, sky)
     eng.set_camera(wl["cam"])
+    for kv in filter(None, os.environ.get("BENCH_ENGINE_OPTS", "").split(",")):   # A/B hook: name=value,...
+        k, v = kv.split("=")
+        eng.set_option(k, int(v))
 
     band = args.band_rows
     part = pkg.Partition(band, world, rank) if world > 1 else None

@@ -28,14 +28,19 @@ namespace RT_NS {
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 5
 #endif
+#ifndef RT_WIDE_BLOCKS
+#define RT_WIDE_BLOCKS 4 /* the WIDE variant: scenes large enough for it fill shared memory to 4 CTAs per SM anyway; 128 registers, no spills */
+#endif
 extern __shared__ __align__(128) unsigned char rt_smem[];
 
 /* MODE: 0 = cooperative trace (production), 1 = literal + counters (reference accounting), 2 = cooperative +
- * counters (executed work), 3 = per-lane fast trace (the previous production path, kept for A/B) */
+ * counters (executed work), 3 = per-lane fast trace (the previous production path, kept for A/B),
+ * 4 = cooperative trace, WIDE variant (rt_trace_coop.cuh: one ray over 32 lanes; scenes with many spheres) */
 template <bool RESIDENT, int MODE, bool AOV>
-__global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __grid_constant__ RtFrameParams fp) {
+__global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BLOCKS) render_frame(const __grid_constant__ RtFrameParams fp) {
     constexpr bool COUNT = MODE == 1 || MODE == 2;
-    constexpr bool COOP = MODE == 0 || MODE == 2;
+    constexpr bool COOP = MODE == 0 || MODE == 2 || MODE == 4;
+    constexpr bool WIDE = MODE == 4;
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
     Geo g;
@@ -104,7 +109,7 @@ __global__ void __launch_bounds__(kBlock, RT_MIN_BLOCKS) render_frame(const __gr
          * per-lane walk has less lock-step overhead on the cheap majority.  Same words either way. */
         const bool heavy = COOP && (!fp.cost || __ldg(fp.cost + tile) >= fp.coop_min_cost);
         if (heavy) {
-            word = trace_tile_coop<COUNT, AOV>(fp, g, cs, id, live, lane, hid, nseg, tl);
+            word = trace_tile_coop<COUNT, AOV, WIDE>(fp, g, cs, id, live, lane, hid, nseg, tl);
         } else if (live) {
             if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);
             else word = trace_pixel_fast<COUNT, AOV>(fp, g, id, hid, tl);
@@ -541,12 +546,19 @@ cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp, int mode, int s
     const uint32_t blob_bytes = fp.lay.total * 16u;
     /* keep the geometry resident while it leaves room for >= 2 CTAs per SM */
     const bool resident = blob_bytes <= 96u * 1024u;
-    const bool coop = mode == 0 || mode == 2;
+#if !RT_TRIANGLES
+    if (mode == 0 && fp.T == 0u && fp.lay.Lpad + fp.lay.Spad >= fp.wide_min_records) mode = 4; /* many spheres: WIDE variant */
+#endif
+    const bool coop = mode == 0 || mode == 2 || mode == 4;
     const uint32_t smem = (resident ? blob_bytes : 0u) + (coop ? (kBlock / 32) * kCoopBytesPerWarp : 0u);
     const bool aov = fp.hit != nullptr;
 #define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape)
 #define RT_GO_A(R, M) do { if (aov) RT_GO(R, M, true); else RT_GO(R, M, false); } while (0)
+#if RT_TRIANGLES
 #define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else RT_GO_A(R, 3); } while (0)
+#else
+#define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else if (mode == 4) RT_GO_A(R, 4); else RT_GO_A(R, 3); } while (0)
+#endif
     if (resident) RT_GO_M(true);
     else RT_GO_M(false);
 #undef RT_GO

@@ -76,6 +76,8 @@ struct RtFrameParams {
     const uint32_t* queue_len;  /* number of queue entries when `order` is set (tiles + 3 per split tile) */
     uint32_t split32_min_cost;  /* ... into 32 single-pixel entries (64 = never) */
     uint32_t split_min_cost;    /* tiles whose estimate reaches this are split into four 8x1 sub-tiles (64 = never) */
+    uint32_t wide_min_records;  /* light+sphere records (padded) from which the WIDE kernel variant is launched */
+    int32_t wide_max_live;      /* < 0: automatic break-even; else rounds with <= this many tracing lanes go ray by ray */
     uint32_t coop_min_cost;     /* tiles whose estimate reaches this walk in cooperative mode, the rest lane per pixel */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
 };

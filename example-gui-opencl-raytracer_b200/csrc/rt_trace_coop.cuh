@@ -58,8 +58,144 @@ __device__ __forceinline__ float coop_run_task(const Geo& g, const CoopSmem& cs,
     return shadow_path_fast(sample, xyz(ipo), g, tl);
 }
 
+/* ---- WIDE scenes: one ray, 32 lanes ------------------------------------------------------------------------
+ * With hundreds of spheres a ray's pass over the records is long, and it is paid by the whole warp even when
+ * only a few lanes still trace (tile tails; the split entries of the heaviest tiles).  In the WIDE variant of the
+ * kernel (chosen by the launcher for scenes with >= fp.wide_min_records light+sphere records and no triangles)
+ * a round with at most `max_live` tracing lanes handles their rays ONE AFTER THE OTHER, the sphere records dealt
+ * over the 32 lanes in groups of four; likewise the last, partial pass of shadow tasks.  The outcome per ray is
+ * the serial one: the closest hit is the (t, index) minimum -- "first of equal t wins" is the lowest index --,
+ * occlusion is an OR, a shadow ray's opacity is kGlassPass multiplied in once per glass hit (a count), blocked
+ * is an OR.  A NaN hit distance makes the serial update order-dependent (!(t1 >= t)), so such a ray is re-run
+ * serially by its owner.
+ * Break-even: a serial pass costs the warp ~17 instructions per record, a cooperative ray 68 per 128 records plus
+ * a fixed part (broadcast, ray set-up, lights and planes on every lane, reductions) that the sweeps put at ~900
+ * instruction-equivalents -- measured optimum 12..14 lanes for 1,028 records (4K grid: 188 ms vs 193 at 24, 199 at
+ * 31) and 3..5 for 260 (8K: 149 ms vs 161 at 6, 182 at 20).  max_live = 17 n / (900 + 68 n / 128). */
+__device__ __forceinline__ uint32_t wide_max_live(const RtFrameParams& fp, const Geo& g) {
+    if (fp.wide_max_live >= 0) return (uint32_t)fp.wide_max_live;
+    const uint32_t n = g.Lpad + g.Spad;
+    const uint32_t m = (17u * n) / (900u + (68u * n) / 128u);
+    return m > 31u ? 31u : m;
+}
+
+/* closest_pass for the tracing lanes of a warp; every lane calls it. */
+template <bool COUNT>
+__device__ __forceinline__ void closest_pass_warp(const RayF& r, V3 o, V3 d, bool tracing, const Geo& g, Tally<COUNT>& tl,
+                                                  Closest& c, uint32_t lane, uint32_t max_live) {
+    constexpr uint32_t kFull = 0xffffffffu;
+    uint32_t mask = __ballot_sync(kFull, tracing);
+    if ((uint32_t)__popc(mask) > max_live) {
+        if (tracing) closest_pass(r, g, tl, c);
+        return;
+    }
+    const uint32_t L = g.L, Lpad = g.Lpad, S = g.S, end = g.Lpad + g.Spad;
+    while (mask) {
+        const int src = __ffs((int)mask) - 1;
+        mask &= mask - 1u;
+        const V3 oo = mk(__shfl_sync(kFull, o.x, src), __shfl_sync(kFull, o.y, src), __shfl_sync(kFull, o.z, src));
+        const V3 dd = mk(__shfl_sync(kFull, d.x, src), __shfl_sync(kFull, d.y, src), __shfl_sync(kFull, d.z, src));
+        RayF rr;
+        ray_setup_fast(rr, oo, dd);
+        Closest cc;
+        cc.t = CUDART_INF_F; cc.tL = CUDART_INF_F;
+        cc.who = -1; cc.whop = -1; cc.whot = -1; cc.k = -1;
+        cc.occluded = false;
+        /* lights: few, and tL must be final before the spheres -- every lane runs them */
+        for_sphere_hits(rr, g.lgeo, 0, Lpad, tl, [&](uint32_t i, float t1) {
+            if (i < L && !(t1 >= cc.tL)) { cc.tL = t1; cc.k = (int)i; }
+            return false;
+        });
+        float bt = CUDART_INF_F;
+        int bw = -1;
+        bool occ = false, odd = false;
+#pragma unroll 1
+        for (uint32_t i0 = Lpad + 4u * lane; i0 < end; i0 += 128u) {
+            for_sphere_hits(rr, g.lgeo, i0, i0 + 4u, tl, [&](uint32_t i, float t1) {
+                const uint32_t s = i - Lpad;
+                if (s < S) {
+                    if (t1 != t1) odd = true;
+                    if (!(t1 >= bt)) { bt = t1; bw = (int)s; }
+                    if (t1 <= cc.tL && !g.flag[s]) occ = true;
+                }
+                return false;
+            });
+        }
+        if (__any_sync(kFull, odd)) { /* NaN distance: order-dependent, the owner walks the records itself */
+            if ((int)lane == src) closest_pass(r, g, tl, c);
+            continue;
+        }
+        /* hit distances are > 0 (sphere_root), so their bit patterns order like unsigned integers; +inf = none */
+        const uint32_t tb = __float_as_uint(bt);
+        const uint32_t tmin = __reduce_min_sync(kFull, tb);
+        const uint32_t wmin = __reduce_min_sync(kFull, (tb == tmin && bw >= 0) ? (uint32_t)bw : 0x7fffffffu);
+        cc.t = __uint_as_float(tmin);
+        cc.who = wmin == 0x7fffffffu ? -1 : (int)wmin;
+        cc.occluded = __any_sync(kFull, occ);
+        for (uint32_t j = 0; j < g.P; j++) { /* planes: few; every lane, same values */
+            float t1;
+            if (!hit_plane_fast(rr, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl)) continue;
+            if (!(t1 >= cc.t)) { cc.t = t1; cc.whop = (int)j; }
+            if (t1 <= cc.tL) cc.occluded = true;
+        }
+        for (uint32_t k = 0; k < g.T; k++) { /* not reached: the launcher keeps triangle scenes off this variant */
+            float t1;
+            if (!hit_triangle(rr.o, rr.d, g.tri + 3 * k, t1, tl)) continue;
+            if (!(t1 >= cc.t)) { cc.t = t1; cc.whot = (int)k; }
+            if (t1 <= cc.tL) cc.occluded = true;
+        }
+        if ((int)lane == src) c = cc;
+    }
+}
+
+/* Phase B for one task, all 32 lanes on it; every lane returns the opacity. */
+template <bool COUNT>
+__device__ __forceinline__ float coop_run_task_warp(const Geo& g, const CoopSmem& cs, float4 tk, uint32_t lane, Tally<COUNT>& tl) {
+    constexpr uint32_t kFull = 0xffffffffu;
+    const uint32_t li = __float_as_uint(tk.z), ow = __float_as_uint(tk.w);
+    const float4 l0 = g.lgeo[li];
+    const float radius = g.laux[li].w;
+    const V3 from = xyz(cs.owner[ow]);
+    float sp, cp, sth, cth;
+    sincos_bounded(tk.y, sp, cp);
+    sincos_bounded(tk.x, sth, cth);
+    const float rs = radius * sp;
+    const V3 to = xyz(l0) + mk(rs * cth, rs * sth, radius * cp); /* raytracing.cl:101-106 */
+    V3 diff = to - from;
+    float len;
+    V3 dir = normalize_len(diff, len);
+    RayF r;
+    ray_setup_fast(r, from, dir);
+    const uint32_t S = g.S;
+    uint32_t nglass = 0;
+    bool blocked = false;
+#pragma unroll 1
+    for (uint32_t i0 = 4u * lane; i0 < g.Spad && !blocked; i0 += 128u) {
+        blocked = for_sphere_hits(r, g.sph, i0, i0 + 4u, tl, [&](uint32_t i, float t1) {
+            if (i >= S || t1 >= len) return false;
+            if (g.flag[i]) { nglass++; return false; }
+            return true;
+        });
+    }
+    if (__any_sync(kFull, blocked)) return 0.0f;
+    const uint32_t n = __reduce_add_sync(kFull, nglass);
+    float opacity = 1.0f;
+    for (uint32_t k = 0; k < n; k++) opacity *= kGlassPass; /* primitives.cl:396-442: one factor per glass hit */
+    for (uint32_t j = 0; j < g.P; j++) {
+        float t1;
+        if (!hit_plane_fast(r, xyz(g.pln[4 * j]), xyz(g.pln[4 * j + 1]), t1, tl) || t1 >= len) continue;
+        return 0.0f;
+    }
+    for (uint32_t k = 0; k < g.T; k++) {
+        float t1;
+        if (!hit_triangle(r.o, r.d, g.tri + 3 * k, t1, tl) || t1 >= len) continue;
+        return 0.0f;
+    }
+    return opacity;
+}
+
 /* One 8x4 tile, all 32 lanes in lock step.  `live` = this lane owns a pixel of the frame.  Returns the pixel word. */
-template <bool COUNT, bool AOV>
+template <bool COUNT, bool AOV, bool WIDE = false>
 __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, const Geo& g, const CoopSmem& cs, uint32_t id,
                                                     bool live, uint32_t lane, uint32_t& hit_id, uint32_t& nseg, Tally<COUNT>& tl) {
     constexpr uint32_t kFull = 0xffffffffu;
@@ -74,6 +210,8 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
     if (AOV) hit_id = 0;
     const uint32_t lt = (1u << lane) - 1u;
     const uint32_t L = g.L;
+    static_assert(!(WIDE && COUNT), "the wide variant does not keep executed-work counters");
+    const uint32_t wide_live = WIDE ? wide_max_live(fp, g) : 0u;
 
     for (;;) {
         if (!done) {
@@ -93,13 +231,16 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
         Material m;
         m.shininess = 0; m.transperent = 0; m.dielectric = 0;
         m.n = 1.0f; m.reflectivity = 0.0f; m.specular = 0.0f; m.diffuse = 0.0f;
+        RayF r;
+        Closest c;
         if (!done) {
             tl.add(RTB_SEGMENTS);
             nseg++;
-            RayF r;
             ray_setup_fast(r, o, d);
-            Closest c;
-            closest_pass(r, g, tl, c);
+            if (!WIDE) closest_pass(r, g, tl, c);
+        }
+        if (WIDE) closest_pass_warp(r, o, d, !done, g, tl, c, lane, wide_live);
+        if (!done) {
             if (c.k >= 0 && !c.occluded) { /* a visible light ends the chain, raytracing.cl:48-54 */
                 V3 lp = o + d * c.tL;
                 V3 od = o - lp;
@@ -214,10 +355,20 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
                 __syncwarp();
                 /* ---- phase B: every lane, finished or not, takes tasks ---- */
 #pragma unroll 1
-                for (uint32_t t = lane; t < ntask; t += 32u) {
+                uint32_t lane_end = ntask;
+                if (WIDE && (ntask & 31u) && (ntask & 31u) <= wide_live) lane_end = ntask & ~31u; /* partial pass: one task, 32 lanes */
+                for (uint32_t t = lane; t < lane_end; t += 32u) {
                     const float4 tk = cs.task[t];
                     const float op = coop_run_task(g, cs, tk, tl);
                     reinterpret_cast<float*>(cs.task + t)[0] = op;
+                }
+                if (WIDE) {
+#pragma unroll 1
+                    for (uint32_t t = lane_end; t < ntask; t++) {
+                        const float4 tk = cs.task[t];
+                        const float op = coop_run_task_warp(g, cs, tk, lane, tl);
+                        if (lane == 0u) reinterpret_cast<float*>(cs.task + t)[0] = op;
+                    }
                 }
                 __syncwarp();
                 /* ---- phase C: owners fold their lights in, in order ---- */

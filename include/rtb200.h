@@ -115,7 +115,11 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * "split32_min_cost": ... and from this value on to 32 warps, one pixel each (64 = never, 0 = automatic: tiles
  * longer than 3 x the expected drain time).
  * "coop_min_cost": tiles whose cost estimate (0..63) reaches this value use the cooperative walk, cheaper tiles the
- * per-lane walk (0 = all cooperative, 64 = none; scheduling only, pixels do not change). */
+ * per-lane walk (0 = all cooperative, 64 = none; scheduling only, pixels do not change).
+ * "wide_min_records": scenes without triangles whose padded light + sphere records reach this number (default 64;
+ * negative = never) run the WIDE variant of the production trace: rounds with few tracing lanes walk the records one
+ * ray at a time over all 32 lanes.  "wide_max_live": -1 (default) = those are the rounds below the instruction
+ * break-even; 0..32 = fixed limit (32 = every round, used by the tests).  Pixels do not change. */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
 /* Brute-force check of the arithmetic routines against IEEE division / sqrt (trials per thread on 592x256
  * threads).  out[0] = division mismatches, out[1] = normalize mismatches, out[2] = max |sincos - libdevice|

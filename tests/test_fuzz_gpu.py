@@ -73,5 +73,12 @@ def test_random_scene(pkg, ref, scene, host, seed):
             same = float((hit == want_hit).mean())
             assert same == 1.0, (seed, trace, same)
             assert c["within1"] >= 0.999 and c["psnr"] >= 50.0, (seed, trace, c)
+            if trace == 0:
+                # the WIDE variant (one ray over 32 lanes), forced onto these small scenes: every round, then a mix
+                for max_live in (32, 3):
+                    eng.set_option("wide_min_records", 0); eng.set_option("wide_max_live", max_live)
+                    rgb_w, hit_w = eng.render_to_host(W, H, want_hit=True)
+                    eng.set_option("wide_min_records", 64); eng.set_option("wide_max_live", -1)
+                    assert np.array_equal(rgb_w, rgb) and np.array_equal(hit_w, hit), (seed, "wide", max_live)
     finally:
         eng.close()

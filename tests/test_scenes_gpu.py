@@ -47,6 +47,23 @@ def test_sphere_grid_matches_oracle(fresh, ref, scene, host, n_side, W, H):
     run_both(ref, scene, fresh, s, p, l, host.camera(W=W, H=H, **camp), W, H)
 
 
+@pytest.mark.parametrize("n_side,W,H", [(15, 384, 216), (32, 256, 144)])
+def test_wide_variant_is_bit_identical(fresh, scene, host, n_side, W, H):
+    """Scenes with >= 64 records run the WIDE kernel variant (rt_trace_coop.cuh); the narrow one must give the same
+    words, at the automatic break-even and with every round forced ray-by-ray."""
+    s, p, l, camp = host.sphere_grid_scene(n_side)
+    fresh.upload_scene(s, p, l)
+    fresh.set_camera(host.camera(W=W, H=H, **camp))
+    fresh.set_option("wide_min_records", -1)
+    narrow, nh = fresh.render_to_host(W, H, want_hit=True)
+    fresh.set_option("wide_min_records", 64)
+    for max_live in (-1, 32, 8):
+        fresh.set_option("wide_max_live", max_live)
+        for _ in range(2):      # second frame: history-ordered queue with split tiles
+            wide, wh = fresh.render_to_host(W, H, want_hit=True)
+            assert np.array_equal(wide, narrow) and np.array_equal(wh, nh), max_live
+
+
 def test_max_uchar_counts(fresh, ref, scene, host):
     """255 spheres, 255 planes and 255 lights would take minutes on the CPU; 255 spheres + 7 planes + 5 lights."""
     s, _, _, camp = host.sphere_grid_scene(16)
