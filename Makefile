@@ -44,7 +44,8 @@ timing: all
 # A/B build of the render kernels with extra defines: make variant NAME=narrow DEFS=-DRT_COOP_WIDE=0 ; RTB_LIB=.../librtb200_narrow.so
 variant: all
 	$(NVCC) $(NVFLAGS) $(KFLAGS) $(DEFS) -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_$(NAME).o 2> /dev/null
-	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_$(NAME).so /tmp/rt_kernels_$(NAME).o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
+	$(NVCC) $(NVFLAGS) $(KFLAGS) $(DEFS) -c $(CSRC)/rt_kernels_tri.cu -o /tmp/rt_kernels_tri_$(NAME).o 2> /dev/null
+	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_$(NAME).so /tmp/rt_kernels_$(NAME).o /tmp/rt_kernels_tri_$(NAME).o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
 
 oracle:
 	$(MAKE) -C oracle

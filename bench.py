@@ -40,11 +40,13 @@ _JSON_FD = 1
 def ncu_traffic(workload):
     """dram__bytes_read.sum + dram__bytes_write.sum of one render_frame launch, from the committed `ncu --set full`
     capture of this same command (profiles/); None for workloads that were not captured."""
-    if workload != "render_map_4k":
+    captured = {"render_map_4k": "r01_v9_render_frame_key_metrics.txt",
+                "spheres1024_4k": "r01_v9_render_frame_wide_key_metrics.txt"}
+    if workload not in captured:
         return None
     try:
         tot = 0.0
-        for ln in open(os.path.join(ROOT, "profiles", "r01_v8_render_frame_key_metrics.txt")):
+        for ln in open(os.path.join(ROOT, "profiles", captured[workload])):
             k, unit, v = ln.split()[0], ln.split()[1], ln.split()[-1]
             if k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                 tot += float(v) * {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}[unit]
@@ -546,7 +548,7 @@ def gpu_body(args, pkg, eng, world, rank, local):
             "gpu_launches": args.steps * (3 * world + (1 if exchange == "nccl" else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": ncu_traffic(wl["name"]),
-                         "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/r01_v8_*); algorithmic bytes: 33.2 MB "
+                         "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/r01_v9_*); algorithmic bytes: 33.2 MB "
                                          "frame + <= 4 B per texel fetch; the kernel is FP32-issue bound, not HBM bound",
                          "kernel": "render_frame", "kernel_ms": float(np.mean(kernel_ms)),
                          "peak_source": "%d SMs x 128 lanes x 2 flop x %.0f MHz (MEASURED_PEAKS.json sm_max_mhz); no tensor/HBM bound applies"

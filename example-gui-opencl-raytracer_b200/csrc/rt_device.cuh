@@ -22,6 +22,9 @@
 #ifndef RT_NS
 #define RT_NS rt
 #endif
+#ifndef RT_TRI_PREFILTER
+#define RT_TRI_PREFILTER 1 /* hit_triangle: decide the common u-test rejects without the division (exact outcome) */
+#endif
 
 namespace RT_NS {
 
@@ -195,9 +198,21 @@ __device__ __forceinline__ bool hit_triangle(V3 o, V3 d, const float4* rec, floa
     V3 p = cross3(d, e2);
     float det = dot3(e1, p);
     if (det == 0.0f) return false;
-    float inv = 1.0f / det;
     V3 s = o - v0;
-    float u = dot3(s, p) * inv;
+    const float a = dot3(s, p);
+#if RT_TRI_PREFILTER
+    /* Exact-outcome shortcut that keeps the division off the common reject path (most triangles fail the u test):
+     * opposite signs and |a| > |det|*1e-30  =>  u = RN(a*RN(1/det)) is a normal negative number (no underflow to -0);
+     * equal signs and |a| > |det|*1.0001     =>  u > 1 whatever the two roundings (each <= 2^-22 relative).
+     * NaN / inf / zero operands make the comparisons false and fall through to the defining sequence below
+     * (tests/test_extensions_cpu.py::test_triangle_prefilter_is_exact checks the claim in float32). */
+    {
+        const float ad = fabsf(det), aa = fabsf(a);
+        if (((a < 0.0f) != (det < 0.0f)) ? (aa > ad * 1e-30f) : (aa > ad * 1.0001f)) return false;
+    }
+#endif
+    float inv = 1.0f / det;
+    float u = a * inv;
     if (u < 0.0f || u > 1.0f) return false;
     V3 q = cross3(s, e1);
     float v = dot3(d, q) * inv;

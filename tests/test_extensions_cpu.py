@@ -107,3 +107,33 @@ def test_oracle_triangle_scene_is_deterministic_and_visible(ref, scene, host):
     assert (hit1 == 1).sum() > 100 and (base_hit == 1).sum() == 0          # id 1+S+P+0 with S = P = 0
     rgb3, _ = port.render(sc, cam, W, H)
     assert np.array_equal(rgb3, base_rgb)                                   # reset really removes them
+
+
+def test_triangle_prefilter_is_exact():
+    """rt_device.cuh:hit_triangle decides most u-test rejects without the division (RT_TRI_PREFILTER).  Claim checked
+    here in IEEE binary32 (numpy): whenever the shortcut fires, the defining sequence u = (s.p) * (1/det),
+    `u < 0 || u > 1` (oracle/rt_oracle.c:hit_triangle) rejects as well -- over ordinary, near-boundary, tiny, huge,
+    zero, infinite and NaN operands."""
+    rng = np.random.default_rng(0x7E1)
+    f = np.float32
+    n = 400_000
+    mag = lambda k: (rng.standard_normal(k) * np.exp2(rng.uniform(-140, 127, k))).astype(f)
+    det = np.concatenate([rng.standard_normal(n).astype(f), mag(n), mag(n), rng.standard_normal(n).astype(f)])
+    ratio = np.concatenate([rng.uniform(-2, 3, n), rng.uniform(-2, 3, n), np.exp2(rng.uniform(-160, 60, n)) * rng.choice([-1, 1], n),
+                            1 + rng.uniform(-3e-4, 3e-4, n)])
+    with np.errstate(all="ignore"):
+        a = (det.astype(np.float64) * ratio).astype(f)
+        special = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 1e-45, -1e-45, 3.4e38, -3.4e38, 1.17549435e-38, 1.0, -1.0], dtype=f)
+        sa, sd = np.meshgrid(special, special)
+        a = np.concatenate([a, sa.ravel(), rng.permutation(a)[:n]])
+        det = np.concatenate([det, sd.ravel(), det[:n]])
+        keep = det != 0
+        a, det = a[keep], det[keep]
+        ad, aa = np.abs(det), np.abs(a)
+        opposite = (a < 0) != (det < 0)
+        fires = np.where(opposite, aa > ad * f(1e-30), aa > ad * f(1.0001))
+        inv = f(1.0) / det
+        u = a * inv
+        rejects = (u < 0) | (u > 1)
+    assert fires.sum() > 100_000 and (~fires).sum() > 100_000
+    assert not np.any(fires & ~rejects)
