@@ -23,4 +23,13 @@ eng.upload_triangles(tris)
 for _ in range(2):
     eng.render_to_host(W, H, want_hit=True)
 eng.render_counted(W, H)
+# WIDE variant (>= 64 light+sphere records, no triangles): a fresh engine on a 9x9 sphere grid
+gs, gp, gl, cam = host.sphere_grid_scene(9)
+eng2 = pkg.Engine(0)
+eng2.upload_scene(gs, gp, gl); eng2.upload_images(0, tex); eng2.upload_images(1, sky)
+eng2.set_camera(host.camera(W=W, H=H, **cam))
+w0, hw0 = eng2.render_to_host(W, H, want_hit=True)
+eng2.set_option("wide_min_records", -1)
+w1, hw1 = eng2.render_to_host(W, H, want_hit=True)
+assert np.array_equal(w0, w1) and np.array_equal(hw0, hw1)
 print("ok")
