@@ -18,9 +18,6 @@ int fail(int code, const char* what, cudaError_t ce = cudaSuccess) {
     else snprintf(g_err, sizeof g_err, "%s", what);
     return code;
 }
-#ifndef RT_SOLO_DEFAULT
-#define RT_SOLO_DEFAULT 0 /* rt_trace_solo.cuh: off until measured faster on the GPU */
-#endif
 #define CU(call, what)                                        \
     do {                                                      \
         cudaError_t ce_ = (call);                             \
@@ -82,7 +79,7 @@ struct rtb_engine {
     bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
     uint32_t tk_W = 0, tk_H = 0, tk_total = 0, tk_band = 0, tk_parts = 0, tk_part = 0;
     unsigned long long scene_gen = 0, tk_scene_gen = 0;
-    int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0, opt_split_min_cost = 0 /* 0 = automatic */, opt_split32_min_cost = 0 /* 0 = automatic */, opt_history = 1, opt_wide_min_records = 64, opt_wide_max_live = -1, opt_solo = RT_SOLO_DEFAULT;
+    int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0, opt_split_min_cost = 0 /* 0 = automatic */, opt_split32_min_cost = 0 /* 0 = automatic */, opt_history = 1, opt_wide_min_records = 64, opt_wide_max_live = -1;
     uint32_t* mirror = nullptr; /* one-shot, see rtb_set_mirror */
     bool mirror_global = false;
     rtb_launch_info last{};
@@ -322,7 +319,6 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.coop_min_cost = (uint32_t)e->opt_coop_min_cost;
     fp.wide_min_records = (uint32_t)e->opt_wide_min_records;
     fp.wide_max_live = e->opt_wide_max_live;
-    fp.solo = (uint32_t)e->opt_solo;
     fp.split_min_cost = 64u;
     fp.split32_min_cost = 64u;
     if (e->opt_tile_order && e->last.tiles >= 4096) { /* small frames: the queue is short enough as it is */
@@ -416,7 +412,6 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!strcmp(name, "coop_min_cost")) { e->opt_coop_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "wide_min_records")) { e->opt_wide_min_records = value < 0 ? 0x7fffffff : value; return 0; }
     if (!strcmp(name, "wide_max_live")) { e->opt_wide_max_live = value > 32 ? 32 : value; return 0; }
-    if (!strcmp(name, "solo")) { e->opt_solo = value < 0 ? RT_SOLO_DEFAULT : (value ? 1 : 0); return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     return fail(-1, "rtb_set_option: unknown option");
 }

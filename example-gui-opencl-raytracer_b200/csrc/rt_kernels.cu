@@ -21,7 +21,6 @@
 #include "rt_device.cuh"
 #include "rt_trace_fast.cuh"
 #include "rt_trace_coop.cuh"
-#include "rt_trace_solo.cuh"
 #include "rt_trace_literal.cuh"
 
 namespace RT_NS {
@@ -109,15 +108,7 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
         /* hybrid: the cooperative walk shortens the heavy tiles (glass, mirrors) that bound the kernel's tail; the
          * per-lane walk has less lock-step overhead on the cheap majority.  Same words either way. */
         const bool heavy = COOP && (!fp.cost || __ldg(fp.cost + tile) >= fp.coop_min_cost);
-        if (heavy && !COUNT && !WIDE && sub >= 5u && fp.solo && g.L >= 1u && g.L <= 16u) {
-            /* single-pixel entry: the warp walks the pixel together and shades its segments in batches (rt_trace_solo.cuh) */
-            const bool any_live = __any_sync(0xffffffffu, live);
-            if (any_live) {
-                const uint32_t src = sub - 5u;
-                const uint32_t w = trace_pixel_solo<AOV>(fp, g, cs, __shfl_sync(0xffffffffu, id, src), lane, hid, nseg);
-                if (live) word = w;
-            }
-        } else if (heavy) {
+        if (heavy) {
             word = trace_tile_coop<COUNT, AOV, WIDE>(fp, g, cs, id, live, lane, hid, nseg, tl);
         } else if (live) {
             if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);

@@ -79,7 +79,6 @@ struct RtFrameParams {
     uint32_t wide_min_records;  /* light+sphere records (padded) from which the WIDE kernel variant is launched */
     int32_t wide_max_live;      /* < 0: automatic break-even; else rounds with <= this many tracing lanes go ray by ray */
     uint32_t coop_min_cost;     /* tiles whose estimate reaches this walk in cooperative mode, the rest lane per pixel */
-    uint32_t solo;              /* != 0: single-pixel queue entries are walked by the whole warp, segments shaded in batches (rt_trace_solo.cuh) */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
 };
 

@@ -82,33 +82,3 @@ def test_random_scene(pkg, ref, scene, host, seed):
                     assert np.array_equal(rgb_w, rgb) and np.array_equal(hit_w, hit), (seed, "wide", max_live)
     finally:
         eng.close()
-
-
-@pytest.mark.parametrize("seed", range(16))
-def test_random_scene_solo_walk(pkg, scene, host, seed):
-    """The batched single-pixel walk (rt_trace_solo.cuh) on the fuzz scenes: frames large enough for the tile queue
-    (>= 4096 tiles), every tile forced into single-pixel entries from the second frame on; same words as without."""
-    rng = np.random.default_rng(1000 + seed)
-    s, p, l = random_scene(host, rng)
-    W, H = 512, 256
-    origin = tuple(rng.normal(size=3) * 2 + np.array([0, 1.5, -4]))
-    if seed % 5 == 0 and len(s):
-        origin = tuple(np.frombuffer(s[:12], np.float32).astype(float))
-    cam = host.camera(origin=origin, look=tuple(rng.normal(size=3) * 0.3 + np.array([0, -0.1, 1])),
-                      fov=float(rng.choice([60.0, 90.0, 120.0])), focal=1.0, W=W, H=H)
-    eng = pkg.Engine(0)
-    try:
-        eng.upload_images(0, scene.tex); eng.upload_images(1, scene.sky)
-        eng.upload_scene(s, p, l)
-        eng.set_camera(cam)
-        eng.set_option("wide_min_records", -1)
-        eng.set_option("solo", 0)
-        rgb0, hit0 = eng.render_to_host(W, H, want_hit=True)
-        eng.set_option("solo", 1)
-        eng.set_option("split_min_cost", 1); eng.set_option("split32_min_cost", 1)
-        for rep in range(3):
-            rgb, hit = eng.render_to_host(W, H, want_hit=True)
-            assert np.array_equal(hit, hit0), (seed, rep)
-            assert np.array_equal(rgb, rgb0), (seed, rep, int((rgb != rgb0).sum()))
-    finally:
-        eng.close()

@@ -169,35 +169,3 @@ def test_history_scheduling_does_not_change_pixels(engine, ref):
                 assert np.array_equal(rgb, rgb0) and np.array_equal(hit, hit0), (thr, rep)
     engine.set_option("split_min_cost", 0)
     engine.set_option("split32_min_cost", 0)
-
-
-def test_solo_walk_is_bit_identical(engine, ref):
-    """rt_trace_solo.cuh: single-pixel queue entries walked by the whole warp with segments shaded in batches (the
-    split of oracle/rt_split.c) must carry the same words as the segment-per-round walk -- every tile forced into
-    single-pixel entries, then the automatic thresholds."""
-    W, H = 1024, 512
-    cams = [ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA),
-            ref.camera(origin=(1.2, 2.2, -7.5), look=(0.15, -0.05, 1.0), fov=90.0, focal=1.0, W=W, H=H),
-            ref.camera(origin=(0.8, 0.9, 0.2), look=(0.0, -0.02, 1.0), fov=60.0, focal=1.0, W=W, H=H)]  # close to the glass
-    engine.set_option("solo", 0)
-    engine.set_option("history", 0)
-    want = []
-    for c in cams:
-        engine.set_camera(c)
-        want.append(engine.render_to_host(W, H, want_hit=True))
-    engine.set_option("history", 1)
-    engine.set_option("solo", 1)
-    try:
-        for thr, thr32 in ((1, 1), (0, 0), (20, 30)):
-            engine.set_option("split_min_cost", thr)
-            engine.set_option("split32_min_cost", thr32)
-            for rep in range(3):
-                for c, (rgb0, hit0) in zip(cams, want):
-                    engine.set_camera(c)
-                    rgb, hit = engine.render_to_host(W, H, want_hit=True)
-                    assert np.array_equal(hit, hit0), (thr, rep)
-                    assert np.array_equal(rgb, rgb0), (thr, rep, int((rgb != rgb0).sum()))
-    finally:
-        engine.set_option("split_min_cost", 0)
-        engine.set_option("split32_min_cost", 0)
-        engine.set_option("solo", -1)

@@ -1,3 +1,16 @@
+/* NOT BUILT.  Kept as the record of a measured experiment: bit-identical frames (17 GPU tests:
+ * every tile forced into single-pixel entries on render.map at 1024x512, three cameras, and on 16 fuzz scenes at
+ * 512x256) but SLOWER on render.map at 4K: slowest rank's share N=4 0.87 -> 1.00 ms, N=8 0.60 -> 0.70 ms, whole frame
+ * unchanged (no single-pixel entries at the automatic thresholds); inlining it also cost the main kernel 1.2 %
+ * (2.732 -> 2.769 ms per frame).  The RT_SOLO_PROFILE clocks below say why: for a 109-segment glass pixel (75 shaded,
+ * 16 batches) the WALK took 816,541 clocks, the batched shading 121,138 and the replay 110,558; the segment-per-round
+ * walk of rt_trace_coop.cuh needs 1,053,166 for the same pixel.  A heavy pixel's chain is ~7,500 clocks per step of the
+ * walk itself (closest hit, material and texel loads, Fresnel, stack) -- batching the shading cannot shorten that.
+ * What would: walking the reflection and refraction sub-trees of a pixel on different lanes (the geometry of the
+ * two is independent; oracle/rt_split.c shows how the RNG ordinals and the addition order are rebuilt afterwards).
+ * To build it again: include it after rt_trace_coop.cuh, add `uint32_t solo` to RtFrameParams, and in render_frame
+ * call trace_pixel_solo for entries with sub >= 5 when (!COUNT && !WIDE && fp.solo && 1 <= g.L <= 16), passing the
+ * live lane's id by __shfl_sync (git history: the commit after "oracle/rt_split.c"). */
 /* rt_trace_solo.cuh -- one heavy pixel, a whole warp: segments shaded in batches.
  *
  * The heaviest tiles are queued one pixel per warp (rt_kernels.cu: split_ways == 32).  In trace_tile_coop such a
@@ -49,8 +62,15 @@ __device__ __forceinline__ uint32_t trace_pixel_solo(const RtFrameParams& fp, co
     bool first = true, finished = false;
     if (AOV) hit_id = 0;
 
+#ifdef RT_SOLO_PROFILE
+    long long pc_walk = 0, pc_shade = 0, pc_replay = 0;
+    uint32_t pc_batches = 0, pc_shaded = 0, pc_events = 0;
+#endif
     while (!finished) {
         uint32_t nev = 0, nb = 0;
+#ifdef RT_SOLO_PROFILE
+        long long pc0 = clock64();
+#endif
         /* ---- walk: uniform over the warp; lane 0 writes the lists ---- */
         while (nb < B && nev + 20u <= kSoloEvents) {
             while (depth >= kMaxDepth) { /* entry finished: fold it into its parent (raytracing.cl:183-190) */
@@ -159,6 +179,9 @@ __device__ __forceinline__ uint32_t trace_pixel_solo(const RtFrameParams& fp, co
             }
         }
         __syncwarp();
+#ifdef RT_SOLO_PROFILE
+        long long pc1 = clock64();
+#endif
 
         /* ---- shade: lane j = (segment, light, sample) ---- */
         if (nb) {
@@ -216,6 +239,9 @@ __device__ __forceinline__ uint32_t trace_pixel_solo(const RtFrameParams& fp, co
             }
         }
         __syncwarp();
+#ifdef RT_SOLO_PROFILE
+        long long pc2 = clock64();
+#endif
 
         /* ---- replay: additions in the reference's order (every lane, same values) ---- */
 #pragma unroll 1
@@ -241,7 +267,19 @@ __device__ __forceinline__ uint32_t trace_pixel_solo(const RtFrameParams& fp, co
             }
         }
         __syncwarp(); /* the next batch reuses the lists */
+#ifdef RT_SOLO_PROFILE
+        {
+            long long pc3 = clock64();
+            pc_walk += pc1 - pc0; pc_shade += pc2 - pc1; pc_replay += pc3 - pc2;
+            pc_batches++; pc_shaded += nb; pc_events += nev;
+        }
+#endif
     }
+#ifdef RT_SOLO_PROFILE
+    if (lane == 0u && nseg > 60u && (id % 31u) == 0u)
+        printf("SOLO id %u nseg %u shaded %u batches %u events %u walk %lld shade %lld replay %lld\n", id, nseg, pc_shaded,
+               pc_batches, pc_events, pc_walk, pc_shade, pc_replay);
+#endif
     return pack_rgb(rgb);
 }
 
