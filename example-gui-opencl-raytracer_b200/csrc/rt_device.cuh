@@ -222,6 +222,66 @@ __device__ __forceinline__ bool hit_triangle(V3 o, V3 d, const float4* rec, floa
     t = t2;
     return true;
 }
+/* The triangle walk of the fast traces: RT_TRI_BATCH records per step, their 3*RT_TRI_BATCH loads issued together and
+ * the cheap half of every test (det, the u numerator, the exact-outcome prefilter) run side by side, so the L1/L2
+ * latency of a record is paid once per batch instead of once per triangle; survivors finish one by one IN INDEX
+ * ORDER (same operations as hit_triangle, same visiting order => same closest hit under "first of equal t wins").
+ * on_hit(k, t) returns true to stop the walk (shadow rays); the function then returns true. */
+#ifndef RT_TRI_BATCH
+#define RT_TRI_BATCH 4
+#endif
+template <bool COUNT, class F>
+__device__ __forceinline__ bool for_triangle_hits(V3 o, V3 d, const float4* __restrict__ tri, uint32_t T, Tally<COUNT>& tl, F&& on_hit) {
+    constexpr uint32_t kB = RT_TRI_BATCH;
+    uint32_t k = 0;
+#pragma unroll 1
+    for (; k + kB <= T; k += kB) {
+        tl.add(RTB_TRI_TESTS, kB);
+        float4 rv0[kB], re1[kB], re2[kB];
+#pragma unroll
+        for (uint32_t j = 0; j < kB; j++) {
+            rv0[j] = __ldg(tri + 3u * (k + j));
+            re1[j] = __ldg(tri + 3u * (k + j) + 1u);
+            re2[j] = __ldg(tri + 3u * (k + j) + 2u);
+        }
+        float det[kB], a[kB];
+        uint32_t cand = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < kB; j++) {
+            const V3 p = cross3(d, xyz(re2[j]));
+            det[j] = dot3(xyz(re1[j]), p);
+            const V3 s = o - xyz(rv0[j]);
+            a[j] = dot3(s, p);
+            bool live = det[j] != 0.0f;
+#if RT_TRI_PREFILTER
+            const float ad = fabsf(det[j]), aa = fabsf(a[j]);
+            if (((a[j] < 0.0f) != (det[j] < 0.0f)) ? (aa > ad * 1e-30f) : (aa > ad * 1.0001f)) live = false;
+#endif
+            if (live) cand |= 1u << j;
+        }
+        if (cand == 0u) continue;
+#pragma unroll
+        for (uint32_t j = 0; j < kB; j++) {
+            if (!(cand >> j & 1u)) continue;
+            const float inv = 1.0f / det[j];
+            const float u = a[j] * inv;
+            if (u < 0.0f || u > 1.0f) continue;
+            const V3 s = o - xyz(rv0[j]);
+            const V3 q = cross3(s, xyz(re1[j]));
+            const float v = dot3(d, q) * inv;
+            if (v < 0.0f || u + v > 1.0f) continue;
+            const float t2 = dot3(xyz(re2[j]), q) * inv;
+            if (t2 <= 0.0f) continue;
+            if (on_hit(k + j, t2)) return true;
+        }
+    }
+    for (; k < T; k++) {
+        float t1;
+        if (!hit_triangle(o, d, tri + 3u * k, t1, tl)) continue;
+        if (on_hit(k, t1)) return true;
+    }
+    return false;
+}
 __device__ __forceinline__ V3 triangle_normal(const float4* rec) {
     V3 n = cross3(xyz(__ldg(rec + 1)), xyz(__ldg(rec + 2)));
     return n / sqrtf(dot3(n, n));
