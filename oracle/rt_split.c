@@ -214,3 +214,140 @@ int rto_split_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_
     free(plan.ev); free(plan.rec);
     return 0;
 }
+
+/* =====================================================================================================================
+ * Tree form: the same pixel with its segments evaluated in BREADTH-FIRST order.
+ *
+ * A shaded segment has up to two continuations whose geometry is independent of one another: the refraction child
+ * (a new stack entry, raytracing.cl:161-179) and the reflection continuation of its own entry (:150-159).  Both are
+ * functions of the segment's ray state {origin, direction, depth, n, f, stack height} alone, so the segments of a
+ * pixel form a binary tree that can be expanded level by level -- on a GPU: one frontier node per lane -- instead of
+ * one after the other.  The stack machine's order is the tree's pre-order with the refraction sub-tree first; the
+ * k of "k-th shaded segment" (hence the RNG state, 4L draws each) is the pre-order rank among shaded nodes, and the
+ * colour is the pre-order list of additions with PUSH before / POP after every refraction entry (an entry pushed at
+ * depth 15 has no segment but is still pushed and popped: parent += 0).  rto_tree_render builds the tree from a FIFO
+ * queue, ranks it, shades the nodes from the LAST to the first, replays -- and must equal rto_render word for word.
+ * ===================================================================================================================== */
+enum { ND_LIGHT = 0, ND_SKY = 1, ND_SHADED = 2 };
+typedef struct {
+    v3 o, d; int depth; float n, f; uint32_t sz;   /* ray state on entry to the segment */
+    int kind; v3 term;                              /* light / sky term, or the ambient term */
+    int entry_child;                                /* a refraction entry was pushed after this segment */
+    int32_t refr, refl;                             /* first segment of that entry / next segment of this entry (-1: none) */
+    uint32_t rank;                                  /* pre-order rank among shaded nodes */
+    shade_rec rec;
+} tree_node;
+
+typedef struct { tree_node* nd; size_t n, cap; } pixel_tree;
+
+static int32_t tree_new(pixel_tree* t, v3 o, v3 d, int depth, float n, float f, uint32_t sz) {
+    if (t->n == t->cap) { t->cap = t->cap ? 2 * t->cap : 32; t->nd = realloc(t->nd, t->cap * sizeof(tree_node)); }
+    tree_node* x = &t->nd[t->n];
+    x->o = o; x->d = d; x->depth = depth; x->n = n; x->f = f; x->sz = sz;
+    x->entry_child = 0; x->refr = x->refl = -1; x->rank = 0; x->rec.nterms = 0;
+    return (int32_t)t->n++;
+}
+
+/* One segment (raytracing.cl:42-179 without :87-136), from the node's own state; appends its continuations. */
+static void tree_expand(pixel_tree* t, int32_t at, const scene_t* sc) {
+    tree_node x = t->nd[at];            /* by value: tree_new may move the array */
+    v3 lcol;
+    if (find_light(x.o, x.d, sc, &lcol, 0)) { t->nd[at].kind = ND_LIGHT; t->nd[at].term = scl(lcol, x.f); return; }
+    v3 ip, nrm; w_material m;
+    if (!find_solid(x.o, x.d, sc, &ip, &nrm, &m, 0)) {
+        int u, v;
+        cube_uv(x.d, (uint32_t)(sc->sw / 4), &u, &v);
+        t->nd[at].kind = ND_SKY;
+        t->nd[at].term = scl(texel(sc->sky, sc->sw, sc->sh, 1, u, sc->sh - v, 0), x.f);
+        return;
+    }
+    t->nd[at].kind = ND_SHADED;
+    t->nd[at].term = scl(scl(ld3(m.rgb), x.f), m.ambient);
+    t->nd[at].rec.ip = ip; t->nd[at].rec.nrm = nrm; t->nd[at].rec.from = x.o; t->nd[at].rec.f = x.f; t->nd[at].rec.m = m;
+    float n1 = x.n, n2 = (n1 == AIR_N) ? m.n : AIR_N;
+    float refl = m.reflectivity;
+    if (m.dielectric) refl = m.reflectivity + (1.0f - m.reflectivity) * fresnel_schlick(n1, n2, x.d, nrm);
+    float f_refl = x.f * refl;
+    v3 d_refl = mirror_dir(x.d, nrm);
+    int depth = x.depth + 1;
+    if (m.transperent && x.sz < STACK_MAX && refl < 1.0f) {
+        v3 co = ip, nn = nrm, cd;
+        if (n1 < n2) co = sub(ip, scl(nrm, 2.0f * EPS_OFFSET));
+        else nn = scl(nrm, -1.0f);
+        if (bend_dir(n1, n2, x.d, nn, &cd) && !(cd.x != cd.x)) {
+            t->nd[at].entry_child = 1;
+            if (depth < STACK_MAX) {
+                int32_t c = tree_new(t, co, cd, depth, n2, x.f * (1.0f - refl), x.sz + 1);
+                t->nd[at].refr = c;
+            }
+        }
+    }
+    if (depth < STACK_MAX) {
+        int32_t c = tree_new(t, ip, d_refl, depth, x.n, f_refl, x.sz);
+        t->nd[at].refl = c;
+    }
+}
+
+static void tree_rank(pixel_tree* t, int32_t at, uint32_t* next) {     /* pre-order: refraction entry first */
+    while (at >= 0) {
+        tree_node* x = &t->nd[at];
+        if (x->kind != ND_SHADED) return;
+        x->rank = (*next)++;
+        if (x->refr >= 0) tree_rank(t, x->refr, next);
+        at = t->nd[at].refl;
+    }
+}
+
+static v3 tree_replay(const pixel_tree* t, int32_t at) {                 /* the colour of one stack entry */
+    v3 acc = mk(0, 0, 0);
+    while (at >= 0) {
+        const tree_node* x = &t->nd[at];
+        acc = add(acc, x->term);
+        if (x->kind != ND_SHADED) break;
+        for (uint32_t i = 0; i < x->rec.nterms; i++) acc = add(acc, x->rec.terms[i]);
+        if (x->entry_child) acc = add(acc, tree_replay(t, x->refr));      /* PUSH ... POP: parent += child (0 if empty) */
+        at = x->refl;
+    }
+    return acc;
+}
+
+int rto_tree_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t y0, uint32_t y1,
+                    const void* spheres, uint32_t S, const void* planes, uint32_t P, const void* lights, uint32_t L,
+                    const uint8_t* tex, int tw, int th, int tl, const uint8_t* sky, int sw, int sh, uint32_t* out,
+                    uint32_t* levels /* may be NULL: warp steps << 24 | levels << 16 | segments */) {
+    if (!wide && (S > 255 || P > 255 || L > 255)) return -1;
+    if (y1 > H || y0 > y1 || W == 0 || L > 255) return -1;
+    scene_t sc = {(const w_sphere*)spheres, S, (const w_plane*)planes, P, (const w_light*)lights, L,
+                  tex, tw, th, tl, sky, sw, sh, g_tri, g_T};
+    jump_table jt;
+    jump_init(&jt, 2u * SHADOW_SAMPLES * L);
+    pixel_tree t = {0};
+    for (uint32_t id = y0 * W; id < y1 * W; id++) {
+        t.n = 0;
+        v3 o, d;
+        primary_ray(cam, W, id, &o, &d);
+        tree_new(&t, o, d, 0, AIR_N, 1.0f, 1);
+        uint32_t nlev = 0, steps = 0;                         /* steps: passes of a 32-lane warp taking one level at a time */
+        for (size_t head = 0; head < t.n;) {                 /* FIFO = level order; a level is what a warp would take at once */
+            size_t level_end = t.n;
+            steps += (uint32_t)((level_end - head + 31) / 32);
+            for (; head < level_end; head++) tree_expand(&t, (int32_t)head, &sc);
+            nlev++;
+        }
+        uint32_t nshaded = 0;
+        tree_rank(&t, 0, &nshaded);
+        for (size_t k = t.n; k-- > 0;)                        /* last node first: the records are independent */
+            if (t.nd[k].kind == ND_SHADED) {
+                shade_rec* r = &t.nd[k].rec;
+                shade_segment(r, jump_to_segment(&jt, id, t.nd[k].rank), &sc);
+                for (uint32_t i = 1; i < r->nterms; i++) r->terms[i - 1] = r->terms[i];   /* the ambient term lives in node.term */
+                r->nterms--;
+            }
+        v3 c = tree_replay(&t, 0);
+        float r = CLAMP01(c.x) * 255.0f, g = CLAMP01(c.y) * 255.0f, b = CLAMP01(c.z) * 255.0f;
+        out[id] = ((uint32_t)r << 16) | ((uint32_t)g << 8) | (uint32_t)b;
+        if (levels) levels[id] = ((steps > 255 ? 255u : steps) << 24) | (nlev << 16) | (uint32_t)(t.n > 0xffff ? 0xffff : t.n);
+    }
+    free(t.nd);
+    return 0;
+}

@@ -20,6 +20,8 @@ def split():
     lib.rto_split_render.argtypes = [C.c_int, f32p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                      C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32,
                                      u8p, C.c_int, C.c_int, C.c_int, u8p, C.c_int, C.c_int, u32p, u32p]
+    lib.rto_tree_render.restype = C.c_int
+    lib.rto_tree_render.argtypes = lib.rto_split_render.argtypes
     lib.rto_split_jump.restype = C.c_uint32
     lib.rto_split_jump.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
     return lib
@@ -31,11 +33,13 @@ def host(pkg):
     return h
 
 
-def split_render(lib, sc, cam, W, H, wide=False):
+def split_render(lib, sc, cam, W, H, wide=False, tree=False):
+    """tree=False: walk / shade / replay in program order of the walk; tree=True: segments expanded breadth-first
+    (second output: warp passes << 24 | levels << 16 | segments instead of the shaded-segment count)."""
     cam = np.ascontiguousarray(cam, np.float32)
     out = np.zeros(W * H, np.uint32)
     shaded = np.zeros(W * H, np.uint32)
-    rc = lib.rto_split_render(int(wide), cam.ctypes.data_as(f32p), W, H, 0, H, sc.spheres.ctypes.data, sc.S,
+    rc = (lib.rto_tree_render if tree else lib.rto_split_render)(int(wide), cam.ctypes.data_as(f32p), W, H, 0, H, sc.spheres.ctypes.data, sc.S,
                               sc.planes.ctypes.data, sc.P, sc.lights.ctypes.data, sc.L,
                               sc.tex.ctypes.data_as(u8p), sc.tex.shape[2], sc.tex.shape[1], sc.tex.shape[0],
                               sc.sky.ctypes.data_as(u8p), sc.sky.shape[2], sc.sky.shape[1],
@@ -66,6 +70,13 @@ def test_split_equals_stack_machine_on_render_map(ref, scene, split, W, H):
     got, shaded = split_render(split, scene, cam, W, H)
     assert np.array_equal(got, want)
     assert shaded.max() > 15          # glass pixels: more shaded segments than one chain can hold -> real sub-trees
+    got, shape = split_render(split, scene, cam, W, H, tree=True)
+    assert np.array_equal(got, want)
+    nodes, levels, steps = shape & 0xffff, (shape >> 16) & 0xff, shape >> 24
+    heavy = int(np.argmax(nodes))
+    print("breadth-first: heaviest pixel %d segments in %d levels (%d passes of 32 lanes); mean %.2f segments in %.2f levels" % (
+        nodes[heavy], levels[heavy], steps[heavy], nodes.mean(), levels.mean()))
+    assert levels.max() <= 16 and nodes.max() > 4 * levels.max()   # the chain a warp would walk: levels, not segments
 
 
 @pytest.mark.parametrize("n_side,W,H", [(8, 96, 54), (17, 64, 36)])
@@ -77,6 +88,8 @@ def test_split_equals_stack_machine_on_sphere_grids(ref, scene, split, host, n_s
     want, _ = ref.port().render(sc, cam, W, H, wide=wide)
     got, shaded = split_render(split, sc, cam, W, H, wide=wide)
     assert np.array_equal(got, want)
+    got_t, _ = split_render(split, sc, cam, W, H, wide=wide, tree=True)
+    assert np.array_equal(got_t, want)
     print("n_side %d: shaded segments per pixel max %d mean %.2f" % (n_side, shaded.max(), shaded.mean()))
 
 
@@ -95,5 +108,7 @@ def test_split_equals_stack_machine_on_random_scenes(ref, scene, split, host, se
     sc = ref.Scene(s, p, l, scene.tex, scene.sky)
     want, _ = ref.port().render(sc, cam, W, H)
     got, _ = split_render(split, sc, cam, W, H)
+    got_t, _ = split_render(split, sc, cam, W, H, tree=True)
+    assert np.array_equal(got_t, want)
     # NaN colours pack through an undefined float->uint conversion on the CPU; both sides run the same code, so equal
     assert np.array_equal(got, want)
