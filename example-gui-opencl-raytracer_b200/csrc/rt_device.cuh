@@ -252,17 +252,19 @@ __device__ __forceinline__ bool for_triangle_hits(V3 o, V3 d, const float4* __re
             det[j] = dot3(xyz(re1[j]), p);
             const V3 s = o - xyz(rv0[j]);
             a[j] = dot3(s, p);
-            bool live = det[j] != 0.0f;
 #if RT_TRI_PREFILTER
+            /* det == 0 is left to the survivors' pass: with det == 0 the prefilter rejects every a != 0 by itself */
             const float ad = fabsf(det[j]), aa = fabsf(a[j]);
-            if (((a[j] < 0.0f) != (det[j] < 0.0f)) ? (aa > ad * 1e-30f) : (aa > ad * 1.0001f)) live = false;
+            const bool live = !(((a[j] < 0.0f) != (det[j] < 0.0f)) ? (aa > ad * 1e-30f) : (aa > ad * 1.0001f));
+#else
+            const bool live = det[j] != 0.0f;
 #endif
             if (live) cand |= 1u << j;
         }
         if (cand == 0u) continue;
 #pragma unroll
         for (uint32_t j = 0; j < kB; j++) {
-            if (!(cand >> j & 1u)) continue;
+            if (!(cand >> j & 1u) || det[j] == 0.0f) continue;
             const float inv = 1.0f / det[j];
             const float u = a[j] * inv;
             if (u < 0.0f || u > 1.0f) continue;

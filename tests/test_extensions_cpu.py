@@ -137,3 +137,20 @@ def test_triangle_prefilter_is_exact():
         rejects = (u < 0) | (u > 1)
     assert fires.sum() > 100_000 and (~fires).sum() > 100_000
     assert not np.any(fires & ~rejects)
+
+
+def test_triangle_batch_defers_the_zero_determinant_check():
+    """rt_device.cuh:for_triangle_hits tests `det == 0` only for the records that survive the prefilter.  Same outcome
+    as hit_triangle (which rejects det == 0 first): with det = +-0 the prefilter either rejects (a is a non-zero number)
+    or lets the record through to the survivors' pass, whose first test is det == 0."""
+    f = np.float32
+    special = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 1e-45, -1e-45, 3.4e38, -3.4e38, 1.17549435e-38, 1.0, -1.0, 7.5, -0.3], dtype=f)
+    for det in (f(0.0), f(-0.0)):
+        for a in special:
+            ad, aa = np.abs(det), np.abs(a)
+            with np.errstate(all="ignore"):
+                fires = (aa > ad * f(1e-30)) if ((a < 0) != (det < 0)) else (aa > ad * f(1.0001))
+            batch_rejects = bool(fires) or det == 0      # prefilter, else the survivors' det == 0 test
+            assert batch_rejects                          # hit_triangle: det == 0 -> no hit
+            if not (a == 0 or np.isnan(a)):
+                assert fires                              # ... and the hot loop alone already says so
