@@ -311,6 +311,57 @@ static v3 tree_replay(const pixel_tree* t, int32_t at) {                 /* the 
     return acc;
 }
 
+/* The same two steps without recursion, the way a warp would do them over the flat, level-ordered node array
+ * (children always have larger indices than their parent):
+ *   ranks   shaded-node counts of every sub-tree by one pass from the last node to the first (a level at a time on a
+ *           GPU), then ranks from the first node to the last: rank(refr child) = rank + 1,
+ *           rank(refl child) = rank + 1 + count(refr sub-tree);
+ *   replay  pre-order with an explicit stack of {node to resume at, partial sum}: <= 15 frames (raytracing.cl:9). */
+static void tree_rank_flat(pixel_tree* t, uint32_t* count /* t->n scratch */) {
+    for (size_t i = t->n; i-- > 0;) {
+        const tree_node* x = &t->nd[i];
+        count[i] = (x->kind == ND_SHADED ? 1u : 0u) + (x->refr >= 0 ? count[x->refr] : 0u) + (x->refl >= 0 ? count[x->refl] : 0u);
+    }
+    t->nd[0].rank = 0;
+    for (size_t i = 0; i < t->n; i++) {
+        const tree_node* x = &t->nd[i];
+        if (x->kind != ND_SHADED) continue;
+        if (x->refr >= 0) t->nd[x->refr].rank = x->rank + 1u;
+        if (x->refl >= 0) t->nd[x->refl].rank = x->rank + 1u + (x->refr >= 0 ? count[x->refr] : 0u);
+    }
+}
+static v3 tree_replay_flat(const pixel_tree* t) {
+    struct { int32_t resume; v3 acc; } fr[STACK_MAX];
+    int sp = 0;
+    int32_t cur = 0;
+    v3 acc = mk(0, 0, 0);
+    for (;;) {
+        int ended = 1;
+        if (cur >= 0) {
+            const tree_node* x = &t->nd[cur];
+            acc = add(acc, x->term);
+            if (x->kind == ND_SHADED) {
+                for (uint32_t i = 0; i < x->rec.nterms; i++) acc = add(acc, x->rec.terms[i]);
+                if (x->entry_child) {                       /* PUSH */
+                    fr[sp].resume = x->refl; fr[sp].acc = acc; sp++;
+                    acc = mk(0, 0, 0);
+                    cur = x->refr;                          /* -1: an entry without segments, ends at once */
+                    ended = cur < 0;
+                } else if (x->refl >= 0) { cur = x->refl; ended = 0; }
+            }
+        }
+        while (ended) {                                     /* the entry is finished: POP into its parent and resume it */
+            if (sp == 0) return acc;
+            sp--;
+            acc = add(fr[sp].acc, acc);
+            cur = fr[sp].resume;
+            ended = cur < 0;
+        }
+    }
+}
+static int g_tree_flat = 0;
+void rto_tree_mode(int flat) { g_tree_flat = flat; }        /* 1: rank and replay without recursion */
+
 int rto_tree_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t y0, uint32_t y1,
                     const void* spheres, uint32_t S, const void* planes, uint32_t P, const void* lights, uint32_t L,
                     const uint8_t* tex, int tw, int th, int tl, const uint8_t* sky, int sw, int sh, uint32_t* out,
@@ -322,6 +373,7 @@ int rto_tree_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t
     jump_table jt;
     jump_init(&jt, 2u * SHADOW_SAMPLES * L);
     pixel_tree t = {0};
+    uint32_t* count = 0; size_t ncount = 0;
     for (uint32_t id = y0 * W; id < y1 * W; id++) {
         t.n = 0;
         v3 o, d;
@@ -335,7 +387,10 @@ int rto_tree_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t
             nlev++;
         }
         uint32_t nshaded = 0;
-        tree_rank(&t, 0, &nshaded);
+        if (g_tree_flat) {
+            if (t.n > ncount) { ncount = 2 * t.n; count = realloc(count, ncount * sizeof(uint32_t)); }
+            tree_rank_flat(&t, count);
+        } else tree_rank(&t, 0, &nshaded);
         for (size_t k = t.n; k-- > 0;)                        /* last node first: the records are independent */
             if (t.nd[k].kind == ND_SHADED) {
                 shade_rec* r = &t.nd[k].rec;
@@ -343,11 +398,11 @@ int rto_tree_render(int wide, const float* cam, uint32_t W, uint32_t H, uint32_t
                 for (uint32_t i = 1; i < r->nterms; i++) r->terms[i - 1] = r->terms[i];   /* the ambient term lives in node.term */
                 r->nterms--;
             }
-        v3 c = tree_replay(&t, 0);
+        v3 c = g_tree_flat ? tree_replay_flat(&t) : tree_replay(&t, 0);
         float r = CLAMP01(c.x) * 255.0f, g = CLAMP01(c.y) * 255.0f, b = CLAMP01(c.z) * 255.0f;
         out[id] = ((uint32_t)r << 16) | ((uint32_t)g << 8) | (uint32_t)b;
         if (levels) levels[id] = ((steps > 255 ? 255u : steps) << 24) | (nlev << 16) | (uint32_t)(t.n > 0xffff ? 0xffff : t.n);
     }
-    free(t.nd);
+    free(t.nd); free(count);
     return 0;
 }

@@ -34,6 +34,12 @@ def host(pkg):
 
 
 def split_render(lib, sc, cam, W, H, wide=False, tree=False):
+    if tree == "flat":                                   # ranks and replay without recursion, over the flat node array
+        lib.rto_tree_mode(1)
+        try:
+            return split_render(lib, sc, cam, W, H, wide=wide, tree=True)
+        finally:
+            lib.rto_tree_mode(0)
     """tree=False: walk / shade / replay in program order of the walk; tree=True: segments expanded breadth-first
     (second output: warp passes << 24 | levels << 16 | segments instead of the shaded-segment count)."""
     cam = np.ascontiguousarray(cam, np.float32)
@@ -72,6 +78,8 @@ def test_split_equals_stack_machine_on_render_map(ref, scene, split, W, H):
     assert shaded.max() > 15          # glass pixels: more shaded segments than one chain can hold -> real sub-trees
     got, shape = split_render(split, scene, cam, W, H, tree=True)
     assert np.array_equal(got, want)
+    got_f, shape_f = split_render(split, scene, cam, W, H, tree="flat")
+    assert np.array_equal(got_f, want) and np.array_equal(shape_f, shape)
     nodes, levels, steps = shape & 0xffff, (shape >> 16) & 0xff, shape >> 24
     heavy = int(np.argmax(nodes))
     print("breadth-first: heaviest pixel %d segments in %d levels (%d passes of 32 lanes); mean %.2f segments in %.2f levels" % (
@@ -88,8 +96,9 @@ def test_split_equals_stack_machine_on_sphere_grids(ref, scene, split, host, n_s
     want, _ = ref.port().render(sc, cam, W, H, wide=wide)
     got, shaded = split_render(split, sc, cam, W, H, wide=wide)
     assert np.array_equal(got, want)
-    got_t, _ = split_render(split, sc, cam, W, H, wide=wide, tree=True)
-    assert np.array_equal(got_t, want)
+    for mode in (True, "flat"):
+        got_t, _ = split_render(split, sc, cam, W, H, wide=wide, tree=mode)
+        assert np.array_equal(got_t, want), mode
     print("n_side %d: shaded segments per pixel max %d mean %.2f" % (n_side, shaded.max(), shaded.mean()))
 
 
@@ -108,7 +117,8 @@ def test_split_equals_stack_machine_on_random_scenes(ref, scene, split, host, se
     sc = ref.Scene(s, p, l, scene.tex, scene.sky)
     want, _ = ref.port().render(sc, cam, W, H)
     got, _ = split_render(split, sc, cam, W, H)
-    got_t, _ = split_render(split, sc, cam, W, H, tree=True)
-    assert np.array_equal(got_t, want)
+    for mode in (True, "flat"):
+        got_t, _ = split_render(split, sc, cam, W, H, tree=mode)
+        assert np.array_equal(got_t, want), mode
     # NaN colours pack through an undefined float->uint conversion on the CPU; both sides run the same code, so equal
     assert np.array_equal(got, want)
