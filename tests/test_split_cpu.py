@@ -122,3 +122,16 @@ def test_split_equals_stack_machine_on_random_scenes(ref, scene, split, host, se
         assert np.array_equal(got_t, want), mode
     # NaN colours pack through an undefined float->uint conversion on the CPU; both sides run the same code, so equal
     assert np.array_equal(got, want)
+
+
+def test_jump_tables_golden(split):
+    """tests/golden/xorshift_jump.npz (tools/make_jump_tables.py, numpy) against the C jump-ahead: the tables the
+    level-wise kernel will keep in constant memory, with known answers incl. a far jump (k = 123,457)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "xorshift_jump.npz"))
+    for L, seed, k, state in g["kat"].tolist():
+        assert split.rto_split_jump(int(seed), 4 * int(L), int(k)) == int(state), (L, seed, k)
+    tab = g["L3"]
+    assert tab.shape == (32, 32) and tab.dtype == np.uint32
+    # column i of pw[0] = 12 steps applied to bit i
+    for i in (0, 7, 31):
+        assert int(tab[0][i]) == split.rto_split_jump(1 << i, 12, 1)
