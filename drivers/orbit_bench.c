@@ -7,8 +7,11 @@
  * against the same cl_wrap_* boundary, using the reference's own host helpers (src/cpu_ray.c
  * rinit_camera/rgen_perspective, src/cpu_obj.c extract_robj) linked in unchanged.
  *
- *   orbit_bench [W H [frames [last_frame.png]]]      (run from a directory holding scenes/ and assets/)
+ *   orbit_bench [W H [frames [last_frame.png|- [count_every]]]]   (run from a directory holding scenes/ and assets/)
  * Prints one JSON line with frame-time p50/p99 (host clock around each frame: the API is synchronous).
+ * count_every > 0: after every count_every-th frame (outside the timed bracket) the same camera is rendered once more
+ * by the counted literal launch (rtb_render_counted: the reference's own work counts), so the line also carries the
+ * rays and algorithmic flop of those sample frames next to their render_frame kernel times (the roofline of config 5).
  */
 #define _GNU_SOURCE
 #include <CL/opencl.h>
@@ -19,6 +22,7 @@
 #include <time.h>
 
 #include "opencl_wrap.h"
+#include "rtb200.h"
 #include "cpu_ray.h"
 #include "cpu_obj.h"
 
@@ -35,7 +39,8 @@ static int cmp_d(const void* a, const void* b) { double x = *(const double*)a, y
 int main(int argc, char** argv) {
     cl_uint W = argc > 2 ? (cl_uint)atoi(argv[1]) : 2560, H = argc > 2 ? (cl_uint)atoi(argv[2]) : 1440;
     int frames = argc > 3 ? atoi(argv[3]) : 240;
-    const char* last_png = argc > 4 ? argv[4] : NULL;
+    const char* last_png = argc > 4 && strcmp(argv[4], "-") ? argv[4] : NULL;
+    const int count_every = argc > 5 ? atoi(argv[5]) : 0;
     if (W == 0 || H == 0 || frames < 1) { fprintf(stderr, "usage: orbit_bench [W H [frames [last.png]]]\n"); return 2; }
 
     rcamera camera = rinit_camera((cl_float3){.x = 0.8f, .y = 2.5f, .z = -8.0f}, (cl_float3){.x = 0.0f, .y = 0.0f, .z = 1.0f},
@@ -79,9 +84,10 @@ int main(int argc, char** argv) {
     cl_wrap_load_global_data(&wrap, 1, 10, NULL, buffer_size, CL_MEM_WRITE_ONLY);
 
     double* dt = malloc(sizeof(double) * (size_t)frames);
-    double kernel_ms = 0.0;
-    unsigned long long checksum = 0;
-    const double t_begin = now_ms();
+    double kernel_ms = 0.0, sampled_kernel_ms = 0.0;
+    unsigned long long checksum = 0, sampled_rays = 0, sampled_flop = 0;
+    int sampled = 0;
+    double total_ms = 0.0; /* sum of the frame brackets (the accounting launches are outside them) */
     for (int f = 0; f < frames; f++) {
         const double t0 = now_ms();
         /* KB_KEY_RIGHT then KB_KEY_D, each followed by the callback's tail (rayinteractive.c:86-103) */
@@ -108,19 +114,30 @@ int main(int argc, char** argv) {
         cl_wrap_output(&wrap, (size_t)W * H, 0, 0, 0, 0, NULL);
         cl_wrap_output(&wrap, (size_t)W * H, buffer_size, 1, 1, 10, buffer);
         dt[f] = now_ms() - t0;
-        kernel_ms += cuda_wrap_last_kernel_ms(&wrap);
+        total_ms += dt[f];
+        const double this_kernel_ms = cuda_wrap_last_kernel_ms(&wrap);
+        kernel_ms += this_kernel_ms;
         checksum = checksum * 1099511628211ull + buffer[((size_t)f * 7919u) % pixels];
+        if (count_every > 0 && f % count_every == count_every - 1) { /* untimed accounting launch, same camera */
+            uint64_t cnt[RTB_NCOUNTERS];
+            if (rtb_render_counted(cuda_wrap_engine(&wrap), W, H, pixels, NULL, NULL, NULL, 0, 0, cnt) == 0) {
+                sampled++;
+                sampled_kernel_ms += this_kernel_ms;
+                sampled_rays += cnt[RTB_SEGMENTS] + cnt[RTB_SHADOW_RAYS];
+                sampled_flop += 21ull * cnt[RTB_SPHERE_TESTS] + 5ull * cnt[RTB_SPHERE_DPOS] + 14ull * cnt[RTB_PLANE_TESTS];
+            }
+        }
     }
-    const double total_ms = now_ms() - t_begin;
     if (last_png) png_dump(last_png, buffer, (cl_int)W, (cl_int)H);
     cl_wrap_release(&wrap);
 
     qsort(dt, (size_t)frames, sizeof(double), cmp_d);
     printf("{\"workload\": \"orbit\", \"width\": %u, \"height\": %u, \"frames\": %d, \"frames_per_s\": %.3f, "
            "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"frame_ms_max\": %.4f, \"kernel_ms_mean\": %.4f, "
-           "\"d2h_bytes_per_frame\": %zu, \"checksum\": \"%016llx\"}\n",
+           "\"d2h_bytes_per_frame\": %zu, \"checksum\": \"%016llx\", \"sampled_frames\": %d, \"sampled_rays\": %llu, "
+           "\"sampled_flop\": %llu, \"sampled_kernel_ms\": %.4f}\n",
            W, H, frames, frames / (total_ms * 1e-3), dt[frames / 2], dt[(int)(0.99 * (frames - 1))], dt[frames - 1],
-           kernel_ms / frames, buffer_size, checksum);
+           kernel_ms / frames, buffer_size, checksum, sampled, sampled_rays, sampled_flop, sampled_kernel_ms);
     free(dt); free(spheres); free(planes); free(lights); free(buffer);
     return 0;
 }

@@ -22,13 +22,13 @@ COUNTER_NAMES = ("segments", "shadow_rays", "sphere_tests", "sphere_dpos", "plan
                  "tri_tests")
 NCOUNTERS = 8
 
-# Every symbol include/rtb200.h and include/cuda_wrap.h declare (checked by tests/test_abi.py).
+# Every symbol include/rtb200.h and include/cuda_wrap.h declare (checked by tests/test_host_cpu.py::test_library_exports_every_declared_symbol).
 ENGINE_SYMBOLS = (
     "rtb_last_error", "rtb_device_count", "rtb_create", "rtb_destroy", "rtb_upload_scene", "rtb_bind_scene_device",
     "rtb_upload_triangles", "rtb_bind_triangles_device", "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
-    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_set_mirror_frame", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
+    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_set_mirror_frame", "rtb_set_completion", "rtb_wait_flags", "rtb_wait_timeouts", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close", "rtb_assemble_bands", "rtb_last_launch", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
 )
 WRAP_SYMBOLS = (
     "cl_wrap_init", "cl_wrap_load_global_data", "cl_wrap_load_single_data", "cl_wrap_load_images", "cl_wrap_output",
@@ -102,6 +102,9 @@ def lib():
             "rtb_host_map": (i, [vp, sz, C.POINTER(vp), C.POINTER(i)]),
             "rtb_set_mirror": (i, [vp, vp]),
             "rtb_set_mirror_frame": (i, [vp, vp]),
+            "rtb_set_completion": (i, [vp, vp, u32]),
+            "rtb_wait_flags": (i, [vp, vp, u32, u32, u32]),
+            "rtb_wait_timeouts": (i, [vp, C.POINTER(u32)]),
             "rtb_ipc_export": (i, [vp, vp, C.c_char_p]),
             "rtb_ipc_open": (i, [vp, C.c_char_p, C.POINTER(vp)]),
             "rtb_ipc_close": (i, [vp, vp]),
@@ -211,6 +214,19 @@ class Engine:
     def set_mirror_frame(self, d_frame):
         """The next render also stores every word at d_frame[y*W + x] (a full frame, typically a peer GPU's)."""
         _check(lib().rtb_set_mirror_frame(self._h, C.c_void_p(d_frame)), "rtb_set_mirror_frame")
+
+    def set_completion(self, d_flag, value):
+        """The next render's last CTA release-stores `value` into the device-visible word at d_flag."""
+        _check(lib().rtb_set_completion(self._h, C.c_void_p(d_flag), int(value) & 0xFFFFFFFF), "rtb_set_completion")
+
+    def wait_flags(self, d_flags, stride_words, n, value):
+        """Enqueue the wait kernel: returns (on the stream) when n flags have reached `value`."""
+        _check(lib().rtb_wait_flags(self._h, C.c_void_p(d_flags), stride_words, n, int(value) & 0xFFFFFFFF), "rtb_wait_flags")
+
+    def wait_timeouts(self):
+        out = C.c_uint32()
+        _check(lib().rtb_wait_timeouts(self._h, C.byref(out)), "rtb_wait_timeouts")
+        return int(out.value)
 
     @staticmethod
     def host_map(host_ptr, nbytes):

@@ -25,6 +25,16 @@ typedef struct {
     size_t idat_len;
 } png_file;
 
+/* Reads `len` payload bytes + the 4-byte CRC of a chunk whose type is `type` and checks the CRC (PNG spec 5.3). */
+static int read_checked(FILE* fp, const unsigned char* type, unsigned char* dst, uint32_t len) {
+    unsigned char c[4];
+    if (len && fread(dst, 1, len, fp) != len) return 0;
+    if (fread(c, 1, 4, fp) != 4) return 0;
+    uLong crc = crc32(0L, (const Bytef*)type, 4);
+    if (len) crc = crc32(crc, dst, len);
+    return (uint32_t)crc == be32(c);
+}
+
 static int parse(const char* path, png_file* pf, int want_idat) {
     memset(pf, 0, sizeof *pf);
     FILE* fp = fopen(path, "rb");
@@ -40,11 +50,10 @@ static int parse(const char* path, png_file* pf, int want_idat) {
         if (len > 0x7fffffffu) break;
         if (!memcmp(ch + 4, "IHDR", 4)) {
             unsigned char ih[13];
-            if (len != 13 || fread(ih, 1, 13, fp) != 13) break;
+            if (len != 13 || !read_checked(fp, ch + 4, ih, 13)) break;
             pf->w = be32(ih); pf->h = be32(ih + 4);
             pf->depth = ih[8]; pf->ctype = ih[9]; pf->interlace = ih[12];
             have_ihdr = 1;
-            if (fseek(fp, 4, SEEK_CUR)) break;
             if (!want_idat) { rc = RTPNG_OK; break; }
         } else if (!memcmp(ch + 4, "IDAT", 4) && want_idat) {
             if (pf->idat_len + len > cap) {
@@ -53,9 +62,8 @@ static int parse(const char* path, png_file* pf, int want_idat) {
                 if (!n) { rc = RTPNG_ENOMEM; break; }
                 pf->idat = n;
             }
-            if (fread(pf->idat + pf->idat_len, 1, len, fp) != len) break;
+            if (!read_checked(fp, ch + 4, pf->idat + pf->idat_len, len)) break; /* short read or bad chunk CRC */
             pf->idat_len += len;
-            if (fseek(fp, 4, SEEK_CUR)) break;
         } else if (!memcmp(ch + 4, "IEND", 4)) {
             rc = have_ihdr ? RTPNG_OK : RTPNG_ECORRUPT;
             break;
@@ -85,41 +93,15 @@ static inline int paeth(int a, int b, int c) {
     return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
 }
 
-int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t h) {
-    png_file pf;
-    int rc = parse(path, &pf, 1);
-    if (rc) return rc;
-    if (pf.w != w || pf.h != h || pf.depth != 8 || pf.ctype != 2 || pf.interlace != 0) { free(pf.idat); return RTPNG_EFORMAT; }
-    const size_t stride = (size_t)w * 3, raw_len = (stride + 1) * h;
-    unsigned char* raw = (unsigned char*)malloc(raw_len ? raw_len : 1);
-    if (!raw) { free(pf.idat); return RTPNG_ENOMEM; }
-    z_stream zs;
-    memset(&zs, 0, sizeof zs);
-    if (inflateInit(&zs) != Z_OK) { free(raw); free(pf.idat); return RTPNG_ECORRUPT; }
-    size_t in_off = 0, out_off = 0;
-    int zr = Z_OK;
-    while (zr != Z_STREAM_END && out_off < raw_len) { /* feed in < 4 GiB pieces: avail_in/out are 32-bit */
-        size_t in_n = pf.idat_len - in_off, out_n = raw_len - out_off;
-        if (in_n > 0x40000000u) in_n = 0x40000000u;
-        if (out_n > 0x40000000u) out_n = 0x40000000u;
-        zs.next_in = pf.idat + in_off; zs.avail_in = (uInt)in_n;
-        zs.next_out = raw + out_off; zs.avail_out = (uInt)out_n;
-        zr = inflate(&zs, Z_NO_FLUSH);
-        in_off += in_n - zs.avail_in;
-        out_off += out_n - zs.avail_out;
-        if (zr != Z_OK && zr != Z_STREAM_END) break;
-        if (zr == Z_OK && in_n == 0) break;
-    }
-    inflateEnd(&zs);
-    free(pf.idat);
-    if (out_off != raw_len) { free(raw); return RTPNG_ECORRUPT; }
-    /* undo the five PNG filters in place (bpp = 3), expanding to RGBA as we go */
+/* Undo the five PNG filters of one (sub-)image in place: h rows of {filter byte, w RGB8 pixels} (bpp = 3).
+ * One loop per filter type (the type is per row); the first pixel has no left neighbour. */
+static int unfilter_rgb8(unsigned char* raw, uint32_t w, uint32_t h) {
+    const size_t stride = (size_t)w * 3;
     for (uint32_t y = 0; y < h; y++) {
         unsigned char* cur = raw + (stride + 1) * y + 1;
         const unsigned char* up = y ? raw + (stride + 1) * (y - 1) + 1 : NULL;
         int ft = cur[-1];
-        if (ft > 4) { free(raw); return RTPNG_ECORRUPT; }
-        /* one loop per filter type (the type is per row); the first pixel has no left neighbour */
+        if (ft > 4) return RTPNG_ECORRUPT;
         const size_t head = stride < 3 ? stride : 3;
         switch (ft) {
             case 1:
@@ -140,10 +122,71 @@ int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t
                 break;
             default: break;
         }
-        uint8_t* o = dst + (size_t)y * w * 4;
-        for (uint32_t xx = 0; xx < w; xx++) {
-            o[4 * xx] = cur[3 * xx]; o[4 * xx + 1] = cur[3 * xx + 1]; o[4 * xx + 2] = cur[3 * xx + 2]; o[4 * xx + 3] = 255;
+    }
+    return RTPNG_OK;
+}
+
+/* Adam7 (PNG spec 8.2): pass p holds the pixels (x0 + i*dx, y0 + j*dy). */
+static const uint32_t kA7x0[7] = {0, 4, 0, 2, 0, 1, 0}, kA7y0[7] = {0, 0, 4, 0, 2, 0, 1};
+static const uint32_t kA7dx[7] = {8, 8, 4, 4, 2, 2, 1}, kA7dy[7] = {8, 8, 8, 4, 4, 2, 2};
+
+int rtpng_read_rgb8_to_rgba(const char* path, uint8_t* dst, uint32_t w, uint32_t h) {
+    png_file pf;
+    int rc = parse(path, &pf, 1);
+    if (rc) return rc;
+    if (pf.w != w || pf.h != h || pf.depth != 8 || pf.ctype != 2 || pf.interlace > 1) { free(pf.idat); return RTPNG_EFORMAT; }
+    /* the inflated stream: one image (interlace 0) or the seven Adam7 sub-images back to back, empty ones omitted */
+    uint32_t pw[7], ph[7];
+    int npass = 1;
+    size_t raw_len = 0;
+    if (pf.interlace == 0) { pw[0] = w; ph[0] = h; }
+    else {
+        npass = 7;
+        for (int p = 0; p < 7; p++) {
+            pw[p] = w > kA7x0[p] ? (w - kA7x0[p] + kA7dx[p] - 1) / kA7dx[p] : 0;
+            ph[p] = h > kA7y0[p] ? (h - kA7y0[p] + kA7dy[p] - 1) / kA7dy[p] : 0;
         }
+    }
+    for (int p = 0; p < npass; p++) if (pw[p] && ph[p]) raw_len += ((size_t)pw[p] * 3 + 1) * ph[p];
+    unsigned char* raw = (unsigned char*)malloc(raw_len + 16); /* the slack catches a stream that holds too much */
+    if (!raw) { free(pf.idat); return RTPNG_ENOMEM; }
+    z_stream zs;
+    memset(&zs, 0, sizeof zs);
+    if (inflateInit(&zs) != Z_OK) { free(raw); free(pf.idat); return RTPNG_ECORRUPT; }
+    size_t in_off = 0, out_off = 0;
+    int zr = Z_OK;
+    while (zr != Z_STREAM_END && out_off <= raw_len) { /* feed in < 4 GiB pieces: avail_in/out are 32-bit */
+        size_t in_n = pf.idat_len - in_off, out_n = raw_len + 16 - out_off;
+        if (in_n > 0x40000000u) in_n = 0x40000000u;
+        if (out_n > 0x40000000u) out_n = 0x40000000u;
+        zs.next_in = pf.idat + in_off; zs.avail_in = (uInt)in_n;
+        zs.next_out = raw + out_off; zs.avail_out = (uInt)out_n;
+        zr = inflate(&zs, Z_NO_FLUSH);
+        in_off += in_n - zs.avail_in;
+        out_off += out_n - zs.avail_out;
+        if (zr != Z_OK && zr != Z_STREAM_END) break;
+        if (zr == Z_OK && in_n == 0) break; /* input exhausted before the end of the stream */
+    }
+    inflateEnd(&zs);
+    free(pf.idat);
+    /* exactly the expected number of bytes AND the end of the zlib stream reached (inflate has then verified the
+     * Adler-32 trailer): a truncated or padded stream is a corrupt file, not a texture */
+    if (zr != Z_STREAM_END || out_off != raw_len) { free(raw); return RTPNG_ECORRUPT; }
+    unsigned char* sub = raw;
+    for (int p = 0; p < npass; p++) {
+        if (!pw[p] || !ph[p]) continue;
+        if (unfilter_rgb8(sub, pw[p], ph[p]) != RTPNG_OK) { free(raw); return RTPNG_ECORRUPT; }
+        const size_t stride = (size_t)pw[p] * 3 + 1;
+        const uint32_t x0 = pf.interlace ? kA7x0[p] : 0, y0 = pf.interlace ? kA7y0[p] : 0;
+        const uint32_t dx = pf.interlace ? kA7dx[p] : 1, dy = pf.interlace ? kA7dy[p] : 1;
+        for (uint32_t j = 0; j < ph[p]; j++) {
+            const unsigned char* cur = sub + stride * j + 1;
+            uint8_t* o = dst + ((size_t)(y0 + j * dy) * w + x0) * 4;
+            for (uint32_t i = 0; i < pw[p]; i++, o += 4 * (size_t)dx) {
+                o[0] = cur[3 * i]; o[1] = cur[3 * i + 1]; o[2] = cur[3 * i + 2]; o[3] = 255;
+            }
+        }
+        sub += stride * ph[p];
     }
     free(raw);
     return RTPNG_OK;

@@ -1,8 +1,10 @@
 /* png_io.h -- minimal PNG codec over zlib for the image-array upload path.
  * Stands in for the libpng calls of the reference's cl_wrap_load_images
  * (/root/reference/src/opencl_wrap.c:229-326): libpng is not installed in this image, zlib is.
- * Decodes non-interlaced PNGs of any colour type far enough to report (w, h, bit depth, colour
- * type); pixel data is produced only for 8-bit RGB, the one format the reference accepts (:299-307). */
+ * Reads PNGs of any colour type far enough to report (w, h, bit depth, colour type, interlace); pixel data is
+ * produced only for 8-bit RGB, the one format the reference accepts (:299-307), non-interlaced or Adam7 (libpng's
+ * png_read_image de-interlaces, so the reference takes both).  Chunk CRCs of IHDR/IDAT and the zlib Adler-32 trailer
+ * are verified: a damaged or truncated file is RTPNG_ECORRUPT, never a half-decoded texture. */
 #ifndef RT_PNG_IO_H
 #define RT_PNG_IO_H
 #include <stdint.h>

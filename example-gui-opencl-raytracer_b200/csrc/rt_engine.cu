@@ -74,6 +74,7 @@ struct rtb_engine {
 
     DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
     DevBuf tile_cost, tile_order, tile_hist;
+    DevBuf tree_slab;         /* per-warp node storage of the level-wise pixel-tree trace (rt_trace_tree.cuh) */
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
     int time_cur = 0;
     bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
@@ -82,6 +83,9 @@ struct rtb_engine {
     int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0, opt_split_min_cost = 0 /* 0 = automatic */, opt_split32_min_cost = 0 /* 0 = automatic */, opt_history = 1, opt_wide_min_records = 64, opt_wide_max_live = -1;
     uint32_t* mirror = nullptr; /* one-shot, see rtb_set_mirror */
     bool mirror_global = false;
+    uint32_t* done_flag = nullptr; /* one-shot, see rtb_set_completion */
+    uint32_t done_value = 0;
+    DevBuf wait_word;              /* timeout counter of rtb_wait_flags */
     rtb_launch_info last{};
 };
 
@@ -93,6 +97,32 @@ int rtb_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
     return n;
+}
+
+void rtb_destroy(rtb_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
+    e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
+    e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
+    e->tree_slab.release(); e->wait_word.release();
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    if (e->evk) cudaEventDestroy(e->evk);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+static int create_impl(rtb_engine* e) {
+    CU(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    CU(cudaEventCreate(&e->ev0), "cudaEventCreate");
+    CU(cudaEventCreate(&e->ev1), "cudaEventCreate");
+    CU(cudaEventCreate(&e->evk), "cudaEventCreate");
+    if (e->sched.ensure(256)) return -2;
+    CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "cudaMemsetAsync");
+    CU(cudaStreamSynchronize(e->stream), "cudaStreamSynchronize");
+    return 0;
 }
 
 int rtb_create(rtb_engine** out, int device) {
@@ -108,29 +138,14 @@ int rtb_create(rtb_engine** out, int device) {
     e->device = device;
     e->sm_count = prop.multiProcessorCount;
     e->smem_optin = prop.sharedMemPerBlockOptin;
-    CU(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking), "cudaStreamCreate");
-    CU(cudaEventCreate(&e->ev0), "cudaEventCreate");
-    CU(cudaEventCreate(&e->ev1), "cudaEventCreate");
-    CU(cudaEventCreate(&e->evk), "cudaEventCreate");
-    if (e->sched.ensure(256)) return -2;
-    CU(cudaMemset(e->sched.p, 0, 256), "cudaMemset");
     memset(e->cam, 0, sizeof e->cam);
+    const int rc = create_impl(e);
+    if (rc) { /* g_err already says why; nothing of the half-built engine survives */
+        rtb_destroy(e);
+        return rc;
+    }
     *out = e;
     return 0;
-}
-
-void rtb_destroy(rtb_engine* e) {
-    if (!e) return;
-    cudaSetDevice(e->device);
-    cudaStreamSynchronize(e->stream);
-    e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
-    e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
-    e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
-    cudaEventDestroy(e->ev0);
-    cudaEventDestroy(e->ev1);
-    cudaEventDestroy(e->evk);
-    cudaStreamDestroy(e->stream);
-    delete e;
 }
 
 static int prep_scene(rtb_engine* e) {
@@ -305,6 +320,10 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     e->mirror_global = false;
     if ((uintptr_t)fp.mirror & 15) return fail(-1, "rtb_render: mirror buffer must be 16-byte aligned");
     fp.tile_counter = (unsigned int*)e->sched.p;
+    fp.done_counter = (unsigned int*)((char*)e->sched.p + 32);
+    fp.done_flag = e->done_flag;
+    fp.done_value = e->done_value;
+    e->done_flag = nullptr;
     fp.counters = (unsigned long long*)((char*)e->sched.p + 64);
     fp.tiles_x = (W + 7) / 8;
     fp.tiles_y = (rows + 3) / 4;
@@ -321,7 +340,8 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.wide_max_live = e->opt_wide_max_live;
     fp.split_min_cost = 64u;
     fp.split32_min_cost = 64u;
-    if (e->opt_tile_order && e->last.tiles >= 4096) { /* small frames: the queue is short enough as it is */
+    /* queue entries carry the tile index in 24 bits (rt_kernels.cu): beyond 2^24 tiles (> 536 Mpixel) the queue stays row-major */
+    if (e->opt_tile_order && e->last.tiles >= 4096 && e->last.tiles < (1u << 24)) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
         if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 128) || e->tile_hist.ensure(1024)) return -2;
         /* scheduling hint: the previous frame's measured tile times when it had this geometry and scene (the camera may
@@ -355,9 +375,9 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
             e->time_valid = true;
             e->tk_W = W; e->tk_H = H; e->tk_total = total; e->tk_band = pp.band_rows; e->tk_parts = pp.parts; e->tk_part = pp.part;
             e->tk_scene_gen = e->scene_gen + e->T;
-        } else {
+        } else if (mode == 0) {
             e->time_valid = false;
-        }
+        } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
         CU((e->T ? rt_launch_tile_order_tri : rt_launch_tile_order)(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),
            "tile_order launch");
@@ -501,6 +521,33 @@ int rtb_set_mirror_frame(rtb_engine* e, uint32_t* frame) {
     if (!e) return fail(-1, "null engine");
     e->mirror = frame;
     e->mirror_global = true;
+    return 0;
+}
+int rtb_set_completion(rtb_engine* e, uint32_t* flag, uint32_t value) {
+    if (!e) return fail(-1, "null engine");
+    if ((uintptr_t)flag & 3) return fail(-1, "rtb_set_completion: flag must be 4-byte aligned");
+    e->done_flag = flag;
+    e->done_value = value;
+    return 0;
+}
+int rtb_wait_flags(rtb_engine* e, const uint32_t* d_flags, uint32_t stride_words, uint32_t n, uint32_t value) {
+    if (!e || !d_flags) return fail(-1, "rtb_wait_flags: null argument");
+    if (n > 1024) return fail(-1, "rtb_wait_flags: at most 1024 flags");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    if (!e->wait_word.p) {
+        if (e->wait_word.ensure(16)) return -2;
+        CU(cudaMemsetAsync(e->wait_word.p, 0, 16, e->stream), "cudaMemsetAsync");
+    }
+    CU(rt_launch_wait_flags(d_flags, stride_words, n, value, (uint32_t*)e->wait_word.p, e->stream), "wait_flags launch");
+    return 0;
+}
+int rtb_wait_timeouts(rtb_engine* e, uint32_t* out) {
+    if (!e || !out) return fail(-1, "rtb_wait_timeouts: null argument");
+    *out = 0;
+    if (!e->wait_word.p) return 0;
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaMemcpyAsync(out, e->wait_word.p, 4, cudaMemcpyDeviceToHost, e->stream), "D2H");
+    CU(cudaStreamSynchronize(e->stream), "rtb_wait_timeouts");
     return 0;
 }
 int rtb_ipc_export(rtb_engine* e, const void* dptr, unsigned char handle[64]) {

@@ -184,6 +184,20 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
             if (lane == 0 && s) atomicAdd(fp.counters + k, s);
         }
     }
+
+    /* completion signal: every thread fences its frame stores (they may target a peer GPU or host memory), the CTA
+     * joins, and the last CTA of the grid publishes the frame number */
+    if (fp.done_flag) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int prev = atomicAdd(fp.done_counter, 1u);
+            if (prev + 1u == gridDim.x) {
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(fp.done_flag), "r"(fp.done_value) : "memory");
+            }
+        }
+    }
 }
 
 /* ---- scene_prep: wire arrays -> compact blob (one thread per record slot) ---- */
@@ -401,6 +415,22 @@ __global__ void assemble_bands(const uint32_t* __restrict__ compact, size_t stri
     else for (uint32_t k = 0; k < 4u && 4u * xq + k < W; k++) dst[k] = src[k];
 }
 
+/* The gathering rank's side of the completion signal: lane i polls flag i (written by rank i's render_frame through
+ * NVLink / PCIe) with system-scope acquire loads.  Bounded: ~4e9 SM clocks, then the timeout word is bumped. */
+__global__ void wait_flags(const uint32_t* flags, uint32_t stride, uint32_t n, uint32_t value, uint32_t* timeouts) {
+    const uint32_t i = threadIdx.x;
+    if (i >= n) return;
+    const uint32_t* p = flags + (size_t)i * stride;
+    const long long t0 = clock64();
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+        if ((int32_t)(v - value) >= 0) break;
+        if (clock64() - t0 > 4000000000ll) { atomicAdd(timeouts, 1u); break; }
+        __nanosleep(200);
+    }
+}
+
 /* FP32 pipe calibration: 8 independent FMA chains per thread. */
 __global__ void fma_peak(float* sink, int iters) {
     float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.0f, a2 = a0 + 2.0f, a3 = a0 + 3.0f;
@@ -572,6 +602,14 @@ cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_wo
                                      uint32_t band_rows, uint32_t parts, cudaStream_t st) {
     const size_t n = (size_t)((W + 3u) / 4u) * H;
     assemble_bands<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_compact, stride_words, d_frame, W, H, band_rows, parts);
+    return cudaGetLastError();
+}
+
+cudaError_t rt_launch_wait_flags(const uint32_t* d_flags, uint32_t stride_words, uint32_t n, uint32_t value,
+                                 uint32_t* d_timeouts, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    if (n > 1024) return cudaErrorInvalidValue;
+    wait_flags<<<1, (n + 31u) & ~31u, 0, st>>>(d_flags, stride_words, n, value, d_timeouts);
     return cudaGetLastError();
 }
 

@@ -80,6 +80,12 @@ struct RtFrameParams {
     int32_t wide_max_live;      /* < 0: automatic break-even; else rounds with <= this many tracing lanes go ray by ray */
     uint32_t coop_min_cost;     /* tiles whose estimate reaches this walk in cooperative mode, the rest lane per pixel */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
+    /* completion signal (multi-GPU, fused into the render): when done_flag is set, the LAST CTA to finish stores
+     * done_value there with a system-scope release store -- after every store of the frame (band buffer, mirror / peer
+     * frame) has been fenced -- so the gathering rank can wait on a word in its own memory instead of a collective */
+    unsigned int* done_counter; /* zeroed before launch */
+    uint32_t* done_flag;        /* may be NULL; device-visible: a peer GPU's memory (CUDA IPC) or mapped host memory */
+    uint32_t done_value;
 };
 
 /* scene_prep: wire arrays -> blob. */
@@ -106,6 +112,11 @@ cudaError_t rt_launch_arith_selftest(uint32_t seed, uint32_t per_thread, uint32_
 /* Gathering rank: compact per-part band buffers (parts x stride_words) -> row-major frame. */
 cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W, uint32_t H,
                                      uint32_t band_rows, uint32_t parts, cudaStream_t st);
+
+/* Gathering rank: spin (on the stream) until flags[i * stride_words] has reached `value` for every i < n (wrap-safe
+ * compare); gives up after ~2 s of SM clocks and adds 1 to *d_timeouts instead of hanging the GPU. */
+cudaError_t rt_launch_wait_flags(const uint32_t* d_flags, uint32_t stride_words, uint32_t n, uint32_t value,
+                                 uint32_t* d_timeouts, cudaStream_t st);
 
 /* Extension X1 builds of the two launchers above (rt_kernels_tri.cu), used when the scene has triangles. */
 cudaError_t rt_launch_render_tri(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);

@@ -63,7 +63,8 @@ __device__ __forceinline__ float coop_run_task(const Geo& g, const CoopSmem& cs,
  * only a few lanes still trace (tile tails; the split entries of the heaviest tiles).  In the WIDE variant of the
  * kernel (chosen by the launcher for scenes with >= fp.wide_min_records light+sphere records and no triangles)
  * a round with at most `max_live` tracing lanes handles their rays ONE AFTER THE OTHER, the sphere records dealt
- * over the 32 lanes in groups of four; likewise the last, partial pass of shadow tasks.  The outcome per ray is
+ * over the 32 lanes interleaved (lane l tests records l, l+32, l+64, l+96 of each 128-record block: every LDS.128
+ * of the warp reads 32 consecutive records, no bank conflicts); likewise the last, partial pass of shadow tasks.  The outcome per ray is
  * the serial one: the closest hit is the (t, index) minimum -- "first of equal t wins" is the lowest index --,
  * occlusion is an OR, a shadow ray's opacity is kGlassPass multiplied in once per glass hit (a count), blocked
  * is an OR.  A NaN hit distance makes the serial update order-dependent (!(t1 >= t)), so such a ray is re-run
@@ -110,8 +111,8 @@ __device__ __forceinline__ void closest_pass_warp(const RayF& r, V3 o, V3 d, boo
         int bw = -1;
         bool occ = false, odd = false;
 #pragma unroll 1
-        for (uint32_t i0 = Lpad + 4u * lane; i0 < end; i0 += 128u) {
-            for_sphere_hits(rr, g.lgeo, i0, i0 + 4u, tl, [&](uint32_t i, float t1) {
+        for (uint32_t i0 = Lpad + lane; i0 < end; i0 += 128u) { /* records i0, i0+32, i0+64, i0+96: conflict-free LDS.128 */
+            for_sphere_hits_strided(rr, g.lgeo, i0, end, tl, [&](uint32_t i, float t1) {
                 const uint32_t s = i - Lpad;
                 if (s < S) {
                     if (t1 != t1) odd = true;
@@ -170,8 +171,8 @@ __device__ __forceinline__ float coop_run_task_warp(const Geo& g, const CoopSmem
     uint32_t nglass = 0;
     bool blocked = false;
 #pragma unroll 1
-    for (uint32_t i0 = 4u * lane; i0 < g.Spad && !blocked; i0 += 128u) {
-        blocked = for_sphere_hits(r, g.sph, i0, i0 + 4u, tl, [&](uint32_t i, float t1) {
+    for (uint32_t i0 = lane; i0 < g.Spad && !blocked; i0 += 128u) { /* records i0, i0+32, i0+64, i0+96 */
+        blocked = for_sphere_hits_strided(r, g.sph, i0, g.Spad, tl, [&](uint32_t i, float t1) {
             if (i >= S || t1 >= len) return false;
             if (g.flag[i]) { nglass++; return false; }
             return true;
@@ -354,9 +355,9 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
                 }
                 __syncwarp();
                 /* ---- phase B: every lane, finished or not, takes tasks ---- */
-#pragma unroll 1
                 uint32_t lane_end = ntask;
                 if (WIDE && (ntask & 31u) && (ntask & 31u) <= wide_live) lane_end = ntask & ~31u; /* partial pass: one task, 32 lanes */
+#pragma unroll 1
                 for (uint32_t t = lane; t < lane_end; t += 32u) {
                     const float4 tk = cs.task[t];
                     const float op = coop_run_task(g, cs, tk, tl);

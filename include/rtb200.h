@@ -161,6 +161,15 @@ int rtb_set_mirror(rtb_engine* e, uint32_t* mirror);
  * the partition: with a PEER GPU's frame buffer (rtb_ipc_open) each rank's bands land in the gathering rank's frame
  * over NVLink while the kernel runs -- the band exchange fused into the render. */
 int rtb_set_mirror_frame(rtb_engine* e, uint32_t* frame);
+/* Completion signal fused into the render (multi-GPU, replaces a per-frame collective): one-shot -- the NEXT
+ * rtb_render's last CTA stores `value` into *flag (system-scope release, after every frame store of that kernel has
+ * been fenced).  `flag` is any device-visible word: a slot in the gathering rank's frame allocation (rtb_ipc_open) or
+ * in mapped host memory.  The gathering rank enqueues rtb_wait_flags on its own stream: a one-warp-per-32-flags kernel
+ * that returns when flags[i * stride_words] has reached `value` for all i < n (wrap-safe; bounded at ~2 s, after which
+ * rtb_wait_timeouts reports a non-zero count instead of a hung GPU). */
+int rtb_set_completion(rtb_engine* e, uint32_t* flag, uint32_t value);
+int rtb_wait_flags(rtb_engine* e, const uint32_t* d_flags, uint32_t stride_words, uint32_t n, uint32_t value);
+int rtb_wait_timeouts(rtb_engine* e, uint32_t* out);
 /* CUDA IPC plumbing for that (one process per GPU): export a cudaMalloc'ed buffer of this engine's device as a 64-byte
  * handle / map a peer's handle into this process (peer access enabled lazily) / unmap. */
 int rtb_ipc_export(rtb_engine* e, const void* dptr, unsigned char handle[64]);

@@ -125,6 +125,20 @@ def have_ref():
     return os.path.exists(REF_SO)
 
 
+def judge():
+    """The oracle every GPU parity test, smoke() and the golden generators compare with: the reference's own .cl text
+    (oracle/_ref, kind "reference").  There is NO fallback to the port: a missing _ref library is an error, so a green
+    run always means "equal to the reference text" (the port is itself pinned to _ref by tests/test_oracle_pinning.py)."""
+    if not have_ref():
+        raise FileNotFoundError(
+            REF_SO + " is missing: parity cannot be judged.  Build it where /root/reference exists (`make -C oracle`); "
+            "it is git-ignored but travels to the GPU box with the snapshot.")
+    return ref()
+
+
+JUDGE_KIND = "reference (oracle/_ref/libref_cl.so: the reference's src/cl/*.cl text compiled as C++)"
+
+
 def camera(origin, look, fov, focal, W, H, normalize_look=True):
     """float32 restatement of rinit_camera + rgen_perspective (src/cpu_ray.c:8-35,42-106).
 

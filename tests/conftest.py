@@ -11,6 +11,13 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
 
 
+def pytest_report_header(config):
+    import __graft_entry__ as g
+    ref = g.load_oracle()
+    return "parity oracle: %s" % (ref.JUDGE_KIND if ref.have_ref() else
+                                   "MISSING (oracle/_ref/libref_cl.so absent: every GPU parity test will fail, by design)")
+
+
 @pytest.fixture(scope="session")
 def pkg():
     import __graft_entry__ as g

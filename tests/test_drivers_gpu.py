@@ -36,7 +36,7 @@ def test_raypng_unchanged_renders_scene_png(pkg, ref, scene, tmp_path):
     got = read_png_words(pkg, out).reshape(-1)
     W, H = 800, 600
     cam = ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA)
-    want, _ = (ref.ref() if ref.have_ref() else ref.port()).render(scene, cam, W, H, want_hit=False)
+    want, _ = ref.judge().render(scene, cam, W, H, want_hit=False)
     c = ref.compare_frames(got, want, W, H)
     print(c)
     assert c["within1"] >= 0.999 and c["psnr"] >= 50.0
@@ -91,7 +91,7 @@ def test_readback_mirror_equals_copy(pkg, ref, scene, mode, monkeypatch):
     monkeypatch.setenv("RTB_HOST_OUTPUT", mode)
     W, H = 640, 360
     cam = ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA)
-    want, _ = (ref.ref() if ref.have_ref() else ref.port()).render(scene, cam, W, H, want_hit=False)
+    want, _ = ref.judge().render(scene, cam, W, H, want_hit=False)
     ses = WrapSession(W, H, scene.spheres, scene.planes, scene.lights, cam)
     bufs = [np.zeros(W * H + 8, np.uint32) for _ in range(2)]
     for b in bufs:

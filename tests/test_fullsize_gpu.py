@@ -29,7 +29,7 @@ def test_4k_frame_matches_reference_rows(engine, ref, scene, golden):
         assert not bad_hit                        # hit ids are bit-exact
         if bad_rgb:                               # tolerance path: <= 1 LSB on >= 99.9 % of the frame, PSNR >= 50 dB
             assert len(bad_rgb) <= 128
-            o = ref.ref() if ref.have_ref() else ref.port()
+            o = ref.judge()
             diff_px, sq = 0, 0.0
             for y in bad_rgb:
                 want, _ = o.render(scene, cam, W, H, y0=y, y1=y + 1, want_hit=False)

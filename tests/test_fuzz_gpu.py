@@ -60,7 +60,7 @@ def test_random_scene(pkg, ref, scene, host, seed):
     cam = host.camera(origin=origin, look=tuple(rng.normal(size=3) * 0.3 + np.array([0, -0.1, 1])),
                       fov=float(rng.choice([60.0, 90.0, 120.0])), focal=1.0, W=W, H=H)
     sc = ref.Scene(s, p, l, scene.tex, scene.sky)
-    want_rgb, want_hit = (ref.ref() if ref.have_ref() else ref.port()).render(sc, cam, W, H)
+    want_rgb, want_hit = ref.judge().render(sc, cam, W, H)
     eng = pkg.Engine(0)
     try:
         eng.upload_images(0, scene.tex); eng.upload_images(1, scene.sky)

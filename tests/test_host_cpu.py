@@ -131,6 +131,79 @@ def test_png_decoder_every_filter_type(pkg, tmp_path):
             assert (got[..., 3] == 255).all()
 
 
+def _png_adam7(path, img, ftype):
+    """Hand-made Adam7-interlaced 8-bit RGB PNG (PNG spec 8.2); every row of every pass uses filter `ftype` (0..2)."""
+    import struct, zlib
+    h, w, _ = img.shape
+    raw = bytearray()
+    for x0, y0, dx, dy in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+        sub = img[y0::dy, x0::dx]
+        if sub.shape[0] == 0 or sub.shape[1] == 0:
+            continue
+        rows = sub.reshape(sub.shape[0], -1).astype(np.int32)
+        for y in range(rows.shape[0]):
+            cur = rows[y]
+            up = rows[y - 1] if y else np.zeros_like(cur)
+            a = np.concatenate([np.zeros(3, np.int32), cur[:-3]])
+            pred = 0 if ftype == 0 else (a if ftype == 1 else up)
+            raw.append(ftype)
+            raw += ((cur - pred) & 255).astype(np.uint8).tobytes()
+    def chunk(t, d):
+        return struct.pack(">I", len(d)) + t + d + struct.pack(">I", zlib.crc32(t + d))
+    z = zlib.compress(bytes(raw))
+    with open(path, "wb") as f:      # two IDAT chunks: the stream may be split anywhere
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 1)) +
+                chunk(b"IDAT", z[:len(z) // 2]) + chunk(b"IDAT", z[len(z) // 2:]) + chunk(b"IEND", b""))
+
+
+def test_png_decoder_adam7_interlace(pkg, tmp_path):
+    """libpng's png_read_image de-interlaces (opencl_wrap.c:318), so the reference accepts Adam7 files: so do we."""
+    from example_gui_opencl_raytracer_b200 import host
+    from PIL import Image
+    rng = np.random.default_rng(11)
+    for (h, w) in ((1, 1), (2, 3), (7, 5), (8, 8), (19, 33), (64, 40)):
+        img = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+        for ft in range(3):
+            p = str(tmp_path / ("a7_%d_%dx%d.png" % (ft, w, h)))
+            _png_adam7(p, img, ft)
+            assert np.array_equal(np.asarray(Image.open(p).convert("RGB")), img)      # the file is a valid PNG
+            got = host.load_png_layers([p], cache_dir="")
+            assert np.array_equal(got[0, :, :, :3], img), (ft, h, w)
+            assert (got[..., 3] == 255).all()
+
+
+def test_png_decoder_rejects_damaged_files(pkg, tmp_path):
+    """A flipped payload byte (chunk CRC), a truncated zlib stream, a wrong Adler-32 trailer and trailing garbage in the
+    stream are all decode errors -- never a silently half-decoded texture."""
+    import struct, zlib
+    from example_gui_opencl_raytracer_b200 import host
+    img = np.random.default_rng(3).integers(0, 256, size=(24, 31, 3), dtype=np.uint8)
+    good = str(tmp_path / "good.png")
+    _png_with_filter(good, img, 4)
+    assert np.array_equal(host.load_png_layers([good], cache_dir="")[0, :, :, :3], img)
+    data = bytearray(open(good, "rb").read())
+    at = data.index(b"IDAT") + 4
+
+    def chunk(t, d):
+        return struct.pack(">I", len(d)) + t + d + struct.pack(">I", zlib.crc32(t + d))
+    raw = b"".join(b"\0" + img[y].tobytes() for y in range(img.shape[0]))
+    z = zlib.compress(raw)
+    head = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", 31, 24, 8, 2, 0, 0, 0))
+    cases = {}
+    flipped = bytearray(data); flipped[at + 20] ^= 0x40
+    cases["payload byte flipped (chunk CRC)"] = bytes(flipped)
+    cases["zlib stream truncated, CRC of the chunk valid"] = head + chunk(b"IDAT", z[:-9]) + chunk(b"IEND", b"")
+    cases["Adler-32 trailer wrong, CRC of the chunk valid"] = head + chunk(b"IDAT", z[:-1] + bytes([z[-1] ^ 1])) + chunk(b"IEND", b"")
+    cases["stream holds one row too many"] = head + chunk(b"IDAT", zlib.compress(raw + raw[:94])) + chunk(b"IEND", b"")
+    cases["stream holds one row too few"] = head + chunk(b"IDAT", zlib.compress(raw[:-94])) + chunk(b"IEND", b"")
+    for what, blob in cases.items():
+        p = str(tmp_path / "bad.png")
+        open(p, "wb").write(blob)
+        with pytest.raises(IOError):
+            host.load_png_layers([p], cache_dir="")
+        print("rejected:", what)
+
+
 def test_decoded_texel_cache(pkg, tmp_path):
     """a hit returns the decoder's bytes; a changed source or a damaged entry is a miss."""
     from example_gui_opencl_raytracer_b200 import host

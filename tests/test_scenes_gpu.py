@@ -29,7 +29,7 @@ def run_both(ref, scene0, eng, s, p, l, cam, W, H):
     eng.upload_scene(s, p, l)
     eng.set_camera(cam)
     rgb, hit = eng.render_to_host(W, H, want_hit=True)
-    o = ref.ref() if ref.have_ref() else ref.port()
+    o = ref.judge()
     want_rgb, want_hit = o.render(sc, cam, W, H, wide=wide)
     c = ref.compare_frames(rgb, want_rgb, W, H)
     same = float((hit == want_hit).mean())
