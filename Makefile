@@ -13,11 +13,11 @@ OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_engine.o $(CSRC
 
 all: $(PKG)/librtb200.so
 
-$(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_coop.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
+$(CSRC)/rt_kernels.o: $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_coop.cuh $(CSRC)/rt_trace_tree.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels.ptxas.log || (cat $(CSRC)/rt_kernels.ptxas.log; false)
 	@grep -E "registers|spill" $(CSRC)/rt_kernels.ptxas.log | sort | uniq -c | sort -rn | head -20
 
-KDEPS := $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_coop.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
+KDEPS := $(CSRC)/rt_kernels.cu $(CSRC)/rt_kernels.h $(CSRC)/rt_device.cuh $(CSRC)/rt_trace_fast.cuh $(CSRC)/rt_trace_coop.cuh $(CSRC)/rt_trace_tree.cuh $(CSRC)/rt_trace_literal.cuh include/rtb200.h
 $(CSRC)/rt_kernels_tri.o: $(CSRC)/rt_kernels_tri.cu $(KDEPS)
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels_tri.ptxas.log || (cat $(CSRC)/rt_kernels_tri.ptxas.log; false)
 

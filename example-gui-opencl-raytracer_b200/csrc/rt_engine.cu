@@ -75,6 +75,9 @@ struct rtb_engine {
     DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
     DevBuf tile_cost, tile_order, tile_hist;
     DevBuf tree_slab;         /* per-warp node storage of the level-wise pixel-tree trace (rt_trace_tree.cuh) */
+    DevBuf jump;              /* [15][32] xorshift32 jump-ahead matrices for this scene's light count */
+    uint32_t jump_L = 0xffffffffu;
+    int opt_tree = 1, opt_tree_cap = 2048;
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
     int time_cur = 0;
     bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
@@ -106,7 +109,7 @@ void rtb_destroy(rtb_engine* e) {
     e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
     e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
-    e->tree_slab.release(); e->wait_word.release();
+    e->tree_slab.release(); e->wait_word.release(); e->jump.release();
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->evk) cudaEventDestroy(e->evk);
@@ -148,7 +151,35 @@ int rtb_create(rtb_engine** out, int device) {
     return 0;
 }
 
+/* xorshift32 (primitives.cl:111-125) is linear over GF(2).  T = step^(4L) advances the generator by one shaded segment
+ * (2 samples x 2 draws per light, raytracing.cl:96-113); table[j][i] = image of bit i under T^(2^j), j < 15 (a pixel
+ * has < 2^15 segments).  The k-th shaded segment of a pixel starts from prod_{j in bits(k)} T^(2^j) applied to the
+ * pixel id (oracle/rt_split.c:jump_init is the CPU proof; tests/test_split_cpu.py). */
+static uint32_t xs_step(uint32_t x) { x ^= x << 13; x ^= x >> 17; x ^= x << 5; return x; }
+static uint32_t bm_apply(const uint32_t* col, uint32_t x) {
+    uint32_t r = 0;
+    for (int i = 0; i < 32; i++) if ((x >> i) & 1u) r ^= col[i];
+    return r;
+}
+static int prep_jump(rtb_engine* e) {
+    if (e->jump_L == e->L && e->jump.p) return 0;
+    uint32_t tab[15][32];
+    for (int i = 0; i < 32; i++) {
+        uint32_t x = 1u << i;
+        for (uint32_t d = 0; d < 4u * e->L; d++) x = xs_step(x);
+        tab[0][i] = x;
+    }
+    for (int j = 1; j < 15; j++)
+        for (int i = 0; i < 32; i++) tab[j][i] = bm_apply(tab[j - 1], tab[j - 1][i]);
+    if (e->jump.ensure(sizeof tab)) return -2;
+    CU(cudaMemcpyAsync(e->jump.p, tab, sizeof tab, cudaMemcpyHostToDevice, e->stream), "H2D jump table");
+    CU(cudaStreamSynchronize(e->stream), "jump table upload"); /* tab is on this stack frame */
+    e->jump_L = e->L;
+    return 0;
+}
+
 static int prep_scene(rtb_engine* e) {
+    if (int rc = prep_jump(e)) return rc;
     e->lay = rt_blob_layout(e->S, e->P, e->L);
     if (e->blob.ensure((size_t)e->lay.total * 16)) return -2;
     CU(rt_launch_scene_prep(e->d_spheres, e->S, e->d_planes, e->P, e->d_lights, e->L, (float4*)e->blob.p, e->lay,
@@ -385,6 +416,24 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
         fp.cost = (const uint32_t*)e->tile_cost.p;
         fp.queue_len = (const uint32_t*)e->tile_hist.p + 128;
     }
+    /* level-wise pixel trees for the split entries of heavy tiles (rt_trace_tree.cuh): production trace only, and only
+     * while a node's 1 + 2L addition slots stay small */
+    fp.tree_mode = 0;
+    if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && (fp.order || e->opt_tree >= 2)) {
+        const uint32_t cap = (uint32_t)e->opt_tree_cap;
+        const uint32_t slots = (uint32_t)e->sm_count * 6u * 4u; /* >= resident warps: <= 5 CTAs of 4 warps per SM at 96 registers */
+        const size_t records = rt_tree_slab_records(cap, e->L);
+        if (e->tree_slab.ensure(records * 16 * slots) == 0) {
+            fp.tree_slab = (float4*)e->tree_slab.p;
+            fp.tree_records = records;
+            fp.tree_cap = cap;
+            fp.tree_slots = slots;
+            fp.tree_mode = (uint32_t)e->opt_tree;
+            fp.jump = (const uint32_t*)e->jump.p;
+        } else {
+            (void)cudaGetLastError(); /* no room for the slabs: the cooperative walk handles everything */
+        }
+    }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
     CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
@@ -433,6 +482,8 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!strcmp(name, "wide_min_records")) { e->opt_wide_min_records = value < 0 ? 0x7fffffff : value; return 0; }
     if (!strcmp(name, "wide_max_live")) { e->opt_wide_max_live = value > 32 ? 32 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
+    if (!strcmp(name, "tree")) { e->opt_tree = value < 0 ? 0 : (value > 3 ? 3 : value); return 0; }
+    if (!strcmp(name, "tree_cap")) { e->opt_tree_cap = value < 64 ? 64 : (value > 32768 ? 32768 : value); e->tree_slab.release(); return 0; }
     return fail(-1, "rtb_set_option: unknown option");
 }
 

@@ -21,6 +21,7 @@
 #include "rt_device.cuh"
 #include "rt_trace_fast.cuh"
 #include "rt_trace_coop.cuh"
+#include "rt_trace_tree.cuh"
 #include "rt_trace_literal.cuh"
 
 namespace RT_NS {
@@ -41,6 +42,7 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
     constexpr bool COUNT = MODE == 1 || MODE == 2;
     constexpr bool COOP = MODE == 0 || MODE == 2 || MODE == 4;
     constexpr bool WIDE = MODE == 4;
+    constexpr bool TREE = MODE == 0 || MODE == 4; /* split entries of heavy tiles may run as level-wise pixel trees */
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
     Geo g;
@@ -109,7 +111,27 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
          * per-lane walk has less lock-step overhead on the cheap majority.  Same words either way. */
         const bool heavy = COOP && (!fp.cost || __ldg(fp.cost + tile) >= fp.coop_min_cost);
         if (heavy) {
-            word = trace_tile_coop<COUNT, AOV, WIDE>(fp, g, cs, id, live, lane, hid, nseg, tl);
+            bool traced = false;
+            if (TREE && fp.tree_mode && (sub != 0u || fp.tree_mode >= 2u)) {
+                const uint32_t warp_slot = blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5);
+                if (warp_slot < fp.tree_slots) {
+                    const TreeSlab sl = {fp.tree_slab + (size_t)warp_slot * fp.tree_records, fp.tree_cap};
+                    uint32_t* lvl = reinterpret_cast<uint32_t*>(cs.owner); /* the cooperative walk's scratch is idle here */
+                    if (fp.tree_mode != 3u) {
+                        traced = trace_tile_tree<AOV>(fp, g, sl, lvl, id, live, lane, word, hid);
+                    } else { /* tests: every pixel of the tile on its own, as single-pixel queue entries are */
+                        traced = true;
+                        const uint32_t lm = __ballot_sync(0xffffffffu, live);
+                        for (uint32_t p = 0; p < 32u && traced; p++) {
+                            if (!((lm >> p) & 1u)) continue;
+                            uint32_t w1 = 0, h1 = 0;
+                            traced = trace_tile_tree<AOV>(fp, g, sl, lvl, id, lane == p, lane, w1, h1);
+                            if (lane == p) { word = w1; hid = h1; }
+                        }
+                    }
+                }
+            }
+            if (!traced) word = trace_tile_coop<COUNT, AOV, WIDE>(fp, g, cs, id, live, lane, hid, nseg, tl);
         } else if (live) {
             if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);
             else word = trace_pixel_fast<COUNT, AOV>(fp, g, id, hid, tl);

@@ -39,6 +39,14 @@ static inline RtBlobLayout rt_blob_layout(uint32_t S, uint32_t P, uint32_t L) {
     return b;
 }
 
+/* Level-wise pixel trees (rt_trace_tree.cuh): one warp's slab = RT_TREE_PLANES node planes of `cap` 16-byte records,
+ * `cap` shaded-list words, then an addition stream of cap * (3 + 2L) records (1 + 2L additions per shaded node plus a
+ * PUSH and a POP mark per refraction entry).  In 16-byte records. */
+#define RT_TREE_PLANES 8
+static inline size_t rt_tree_slab_records(uint32_t cap, uint32_t L) {
+    return (size_t)RT_TREE_PLANES * cap + (cap + 3u) / 4u + (size_t)cap * (3u + 2u * L);
+}
+
 struct RtFrameParams {
     /* raygen.cl:5-8 scalar arguments */
     float corner[3], origin[3], up[3], right[3], wf, hf;
@@ -79,6 +87,13 @@ struct RtFrameParams {
     uint32_t wide_min_records;  /* light+sphere records (padded) from which the WIDE kernel variant is launched */
     int32_t wide_max_live;      /* < 0: automatic break-even; else rounds with <= this many tracing lanes go ray by ray */
     uint32_t coop_min_cost;     /* tiles whose estimate reaches this walk in cooperative mode, the rest lane per pixel */
+    /* level-wise pixel trees (rt_trace_tree.cuh): per-warp slabs of tree_records 16-byte records each */
+    float4* tree_slab;          /* NULL: never */
+    unsigned long long tree_records;
+    uint32_t tree_cap;          /* nodes per slab */
+    uint32_t tree_slots;        /* slabs allocated: warp slot = blockIdx.x * warps per CTA + warp */
+    uint32_t tree_mode;         /* 0 off; 1 split queue entries (rows / single pixels of heavy tiles); 2 every tile; 3 every tile, pixel by pixel (tests) */
+    const uint32_t* jump;       /* [15][32] bit matrices (xorshift32^(4L))^(2^j), see rt_engine.cu */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
     /* completion signal (multi-GPU, fused into the render): when done_flag is set, the LAST CTA to finish stores
      * done_value there with a system-scope release store -- after every store of the frame (band buffer, mirror / peer

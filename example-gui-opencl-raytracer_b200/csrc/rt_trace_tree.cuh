@@ -1,0 +1,370 @@
+/* rt_trace_tree.cuh -- level-wise pixel trees: one pixel's segments spread over the lanes of a warp.
+ *
+ * The stack machine of raytracing.cl:41-190 runs a pixel's segments one after the other; a glass pixel of render.map
+ * has up to 166 of them at 3840x2160 and at ~7,500 clocks per step of the walk that chain (0.6 ms) was the floor of
+ * every multi-GPU frame and of the single-GPU tail.  But the segments of a pixel form a binary tree -- a shaded
+ * segment continues as the reflection of its own stack entry (:150-159) and, through glass, as a new entry for the
+ * refracted ray (:161-179) -- whose geometry depends on neither the RNG nor the accumulated colour.  oracle/rt_split.c
+ * (rto_tree_render, tree_rank_flat, tree_replay_flat) proves on the CPU that the following evaluation order gives the
+ * stack machine's words; this file is that order on a warp:
+ *
+ *   1 EXPAND  breadth-first.  The frontier is a queue of ray states {origin, direction, f, n, depth, stack height,
+ *             pixel} in the warp's slab; each pass, lane j takes frontier node j: closest hit (one pass over lights,
+ *             spheres, planes), classification, material / texel, ambient term, Fresnel, and its <= 2 continuations
+ *             appended at ballot-prefix positions.  All nodes of BFS level k have depth k, so there are <= 15 levels.
+ *   2 RANK    per node, last level to first: shaded segments and addition-stream slots of its sub-tree; then first
+ *             level to last: the pre-order rank among shaded nodes (refraction sub-tree first -- the stack machine's
+ *             order) and the position of the node's additions in the pixel's stream.  A shaded segment draws exactly
+ *             4L random numbers (raytracing.cl:96-113 has no early exit), so its RNG state is
+ *             xorshift32^(4L*rank)(pixel id): xorshift32 (primitives.cl:111-125) is linear over GF(2) and the state is
+ *             a product of <= 15 precomputed 32x32 bit matrices (fp.jump, built per scene by the engine).
+ *   3 SHADE   (shaded node, light) pairs dealt over the 32 lanes: shading geometry, the four draws, two shadow rays,
+ *             the light's specular and diffuse terms -- written straight into the stream slots.
+ *   4 REPLAY  each pixel's lane runs down its stream: ADD v / PUSH / POP on a <= 15-deep stack of partial sums --
+ *             additions only, in exactly the order the stack machine performs them.
+ *
+ * Terms that the cooperative trace skips because they are exact zeros (R5) are stored as +0 and added: x + 0 == x for
+ * every x but -0, and the sign of a zero cannot reach the packed word (clamp, *255, truncation).
+ * A tree that outgrows the slab (fp.tree_cap nodes) makes the function return false; the caller then runs the entry
+ * through trace_tile_coop -- same words, the old way.
+ */
+#pragma once
+#include "rt_trace_coop.cuh"
+
+namespace RT_NS {
+
+enum : uint32_t { kNdLight = 0u, kNdSky = 1u, kNdShaded = 2u };
+enum : uint32_t { kOpAdd = 0u, kOpPush = 1u, kOpPop = 2u };
+constexpr uint32_t kTreePlanes = RT_TREE_PLANES; /* R0 R1 M S0 S1 S2 T X, 16 bytes per node each (rt_kernels.h) */
+
+/* One warp's slab: kTreePlanes planes of `cap` 16-byte records, cap shaded-list words, then the addition stream of
+ * cap * (3 + 2L) 16-byte records.  SoA: lane j touching node base + j reads 512 contiguous bytes per plane. */
+struct TreeSlab {
+    float4* base;
+    uint32_t cap;
+    __device__ __forceinline__ float4* plane(uint32_t k) const { return base + (size_t)k * cap; }
+    __device__ __forceinline__ float4* R0() const { return plane(0); }   /* {o.xyz, f} */
+    __device__ __forceinline__ float4* R1() const { return plane(1); }   /* {d.xyz, n} */
+    __device__ __forceinline__ uint4* M() const { return reinterpret_cast<uint4*>(plane(2)); } /* {depth | sz<<8 | pix<<16 | kind<<24 | entry<<28, refr, refl, -} */
+    __device__ __forceinline__ float4* S0() const { return plane(3); }   /* {ip.xyz, f*specular} */
+    __device__ __forceinline__ float4* S1() const { return plane(4); }   /* {nrm.xyz, f*diffuse} */
+    __device__ __forceinline__ float4* S2() const { return plane(5); }   /* {v.xyz, shininess} */
+    __device__ __forceinline__ float4* T() const { return plane(6); }    /* {light / sky / ambient term, -} */
+    __device__ __forceinline__ uint4* X() const { return reinterpret_cast<uint4*>(plane(7)); } /* {shaded in sub-tree, stream slots of sub-tree, rank -> RNG state, stream position} */
+    __device__ __forceinline__ uint32_t* shaded() const { return reinterpret_cast<uint32_t*>(plane(kTreePlanes)); }
+    __device__ __forceinline__ float4* stream() const { return plane(kTreePlanes) + (cap + 3u) / 4u; }
+};
+/* xorshift32^(draws*k)(seed): jump[j*32 + i] = image of bit i under (step^draws)^(2^j).  The j loop is warp-uniform
+ * (runs to the highest set bit of any lane's k), so every table read is one broadcast load. */
+__device__ __forceinline__ uint32_t rng_jump(const uint32_t* __restrict__ jump, uint32_t seed, uint32_t k, uint32_t kmax) {
+    for (uint32_t j = 0; (kmax >> j) != 0u; j++) {
+        uint32_t r = 0;
+#pragma unroll 8
+        for (uint32_t i = 0; i < 32u; i++) r ^= __ldg(jump + j * 32u + i) & (0u - ((seed >> i) & 1u));
+        if ((k >> j) & 1u) seed = r;
+    }
+    return seed;
+}
+
+/* Returns false (warp-uniformly) when the tree does not fit the slab; otherwise `word` (and hit_id) are this lane's. */
+template <bool AOV>
+__device__ __noinline__ bool trace_tile_tree(const RtFrameParams& fp, const Geo& g, const TreeSlab sl, uint32_t* lvl /* shared: >= 17 words per warp */,
+                                             uint32_t id, bool live, uint32_t lane, uint32_t& word, uint32_t& hit_id) {
+    constexpr uint32_t kFull = 0xffffffffu;
+    Tally<false> tl;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t L = g.L, cap = sl.cap;
+    const uint32_t own_shaded = 1u + 2u * L;
+
+    /* ---- roots: one node per live pixel ---- */
+    const uint32_t live_mask = __ballot_sync(kFull, live);
+    const uint32_t nroots = (uint32_t)__popc(live_mask);
+    const uint32_t my_root = (uint32_t)__popc(live_mask & lt);
+    if (nroots == 0u) { word = 0; if (AOV) hit_id = 0; return true; }
+    if (live) {
+        V3 o, d;
+        primary_ray(fp, id, o, d);
+        sl.R0()[my_root] = make_float4(o.x, o.y, o.z, 1.0f);
+        sl.R1()[my_root] = make_float4(d.x, d.y, d.z, kAirN);
+        sl.M()[my_root] = make_uint4(0u | (1u << 8) | (lane << 16), 0xffffffffu, 0xffffffffu, 0u);
+    }
+    __syncwarp();
+
+    /* ---- 1 EXPAND ---- */
+    uint32_t n_nodes = nroots, n_shaded = 0, head = 0, nlev = 0, root_hid = 0;
+    while (head < n_nodes) {
+        const uint32_t level_end = n_nodes;
+        if (lane == 0) lvl[nlev] = head;
+        nlev++;
+#pragma unroll 1
+        for (uint32_t base = head; base < level_end; base += 32u) {
+            const uint32_t i = base + lane;
+            const bool act = i < level_end;
+            bool c_refr = false, c_refl = false, shaded = false;
+            V3 ro = mk(0.0f, 0.0f, 0.0f), rd = ro, lo = ro, ld = ro; /* refraction / reflection continuations */
+            float rf = 0.0f, rn = 0.0f, lf = 0.0f, ln = 0.0f;
+            uint32_t meta = 0;
+            if (act) {
+                const float4 r0 = sl.R0()[i], r1 = sl.R1()[i];
+                meta = sl.M()[i].x;
+                const V3 o = xyz(r0), d = xyz(r1);
+                const float f = r0.w, n_cur = r1.w;
+                const uint32_t depth = meta & 0xffu, sz = (meta >> 8) & 0xffu;
+                RayF r;
+                ray_setup_fast(r, o, d);
+                Closest c;
+                closest_pass(r, g, tl, c);
+                uint32_t kind, entry = 0u, hid = 0u;
+                V3 term;
+                if (c.k >= 0 && !c.occluded) { /* a visible light ends the chain, raytracing.cl:48-54 */
+                    V3 lp = o + d * c.tL;
+                    V3 od = o - lp;
+                    float dd = sqrtf(dot3(od, od));
+                    V3 col = xyz(g.laux[c.k]) * (1.0f / dd * dd); /* (1/d)*d, primitives.cl:288 */
+                    term = col * f;
+                    kind = kNdLight;
+                    hid = RTB_HIT_LIGHT | (uint32_t)c.k;
+                } else if (c.who < 0 && c.whop < 0 && c.whot < 0) { /* skybox, raytracing.cl:61-81 */
+                    int u, v;
+                    cube_uv(d, (uint32_t)(fp.sw / 4), u, v);
+                    V3 px = texel_rgb(fp.sky, fp.sw, fp.sh, 1, u, fp.sh - v, 0, g.lut255);
+                    term = px * f;
+                    kind = kNdSky;
+                } else {
+                    kind = kNdShaded;
+                    shaded = true;
+                    V3 ip = o + d * c.t, nrm;
+                    Material m;
+                    if (c.whot >= 0) { /* extension X1 */
+                        nrm = triangle_normal(g.tri + 3 * c.whot);
+                        m = load_material_at(fp.raw_tris + (size_t)c.whot * RT_TRIANGLE_BYTES + RT_TRI_MATERIAL_OFFSET);
+                        hid = 1u + g.S + g.P + (uint32_t)c.whot;
+                    } else if (c.whop >= 0) {
+                        nrm = xyz(g.pln[4 * c.whop]);
+                        m = load_material(fp.raw_planes + (size_t)c.whop * RT_PLANE_BYTES);
+                        if (m.texture_id >= 0) { /* primitives.cl:217-259; sampled once, for the plane that won */
+                            float4 b0 = g.pln[4 * c.whop + 2], b1 = g.pln[4 * c.whop + 3];
+                            float ui = dot3(xyz(b0), ip) * m.texture_scale;
+                            float vi = dot3(xyz(b1), ip) * m.texture_scale;
+                            m.rgb = texel_rgb(fp.tex, fp.tw, fp.th, fp.tl, emod(f2i_x86(ui), fp.tw), emod(f2i_x86(vi), fp.th),
+                                              m.texture_id, g.lut255);
+                        }
+                        hid = 1u + g.S + (uint32_t)c.whop;
+                    } else {
+                        float qlen;
+                        nrm = normalize_len(ip - xyz(g.sph[c.who]), qlen);
+                        m = load_material(fp.raw_spheres + (size_t)c.who * RT_SPHERE_BYTES);
+                        hid = 1u + (uint32_t)c.who;
+                    }
+                    ip = ip + nrm * kEps;
+                    term = (m.rgb * f) * m.ambient; /* raytracing.cl:83-84 */
+                    float vlen;
+                    const V3 vv = normalize_len(o - ip, vlen);
+                    sl.S0()[i] = make_float4(ip.x, ip.y, ip.z, f * m.specular);
+                    sl.S1()[i] = make_float4(nrm.x, nrm.y, nrm.z, f * m.diffuse);
+                    sl.S2()[i] = make_float4(vv.x, vv.y, vv.z, (float)m.shininess);
+                    /* Fresnel, reflection, refraction child (raytracing.cl:138-179) */
+                    const float n1 = n_cur;
+                    const float n2 = (n1 == kAirN) ? m.n : kAirN;
+                    const float cosI = -dot3(nrm, d);
+                    const float refl = reflect_amount(m, n1, n2, cosI);
+                    const uint32_t depth1 = depth + 1u;
+                    if (m.transperent && sz < (uint32_t)kMaxDepth && refl < 1.0f) {
+                        if (refract_child(ip, nrm, d, n1, n2, ro, rd)) {
+                            entry = 1u; /* the entry is pushed (and popped) even when it has no segment left to run */
+                            if (depth1 < (uint32_t)kMaxDepth) { c_refr = true; rf = f * (1.0f - refl); rn = n2; }
+                        }
+                    }
+                    if (depth1 < (uint32_t)kMaxDepth) {
+                        c_refl = true;
+                        lo = ip;
+                        ld = d + nrm * (2.0f * cosI); /* primitives.cl:127-130 */
+                        lf = f * refl;
+                        ln = n_cur;
+                    }
+                }
+                sl.T()[i] = make_float4(term.x, term.y, term.z, 0.0f);
+                meta |= (kind << 24) | (entry << 28);
+                if (AOV && base == 0u) root_hid = hid; /* level 0: lane j expanded root j */
+            }
+            const uint32_t m1 = __ballot_sync(kFull, c_refr), m2 = __ballot_sync(kFull, c_refl), ms = __ballot_sync(kFull, shaded);
+            const uint32_t total = (uint32_t)(__popc(m1) + __popc(m2));
+            if (n_nodes + total > cap) return false; /* warp-uniform */
+            if (act) {
+                const uint32_t child_meta = ((meta & 0xffu) + 1u) | (meta & 0x00ffff00u);
+                uint32_t refr = 0xffffffffu, refl_i = 0xffffffffu;
+                if (c_refr) {
+                    refr = n_nodes + (uint32_t)__popc(m1 & lt);
+                    sl.R0()[refr] = make_float4(ro.x, ro.y, ro.z, rf);
+                    sl.R1()[refr] = make_float4(rd.x, rd.y, rd.z, rn);
+                    sl.M()[refr] = make_uint4((child_meta & 0xffff00ffu) | ((((meta >> 8) & 0xffu) + 1u) << 8), 0xffffffffu, 0xffffffffu, 0u);
+                }
+                if (c_refl) {
+                    refl_i = n_nodes + (uint32_t)__popc(m1) + (uint32_t)__popc(m2 & lt);
+                    sl.R0()[refl_i] = make_float4(lo.x, lo.y, lo.z, lf);
+                    sl.R1()[refl_i] = make_float4(ld.x, ld.y, ld.z, ln);
+                    sl.M()[refl_i] = make_uint4(child_meta, 0xffffffffu, 0xffffffffu, 0u);
+                }
+                sl.M()[i] = make_uint4(meta, refr, refl_i, 0u);
+                if (shaded) sl.shaded()[n_shaded + (uint32_t)__popc(ms & lt)] = i;
+            }
+            n_nodes += total;
+            n_shaded += (uint32_t)__popc(ms);
+            __syncwarp();
+        }
+        head = level_end;
+    }
+    if (lane == 0) lvl[nlev] = n_nodes;
+    __syncwarp();
+    if (AOV) hit_id = __shfl_sync(kFull, root_hid, my_root & 31u);
+
+    /* ---- 2 RANK: sub-tree totals, last level first ---- */
+    for (uint32_t lv = nlev; lv-- > 0u;) {
+        const uint32_t b = lvl[lv], e = lvl[lv + 1u];
+        for (uint32_t i = b + lane; i < e; i += 32u) {
+            const uint4 mm = sl.M()[i];
+            const bool sh = ((mm.x >> 24) & 0xfu) == kNdShaded;
+            uint32_t cnt = sh ? 1u : 0u;
+            uint32_t size = (sh ? own_shaded : 1u) + (((mm.x >> 28) & 1u) ? 2u : 0u);
+            if (mm.y != 0xffffffffu) { const uint4 x = sl.X()[mm.y]; cnt += x.x; size += x.y; }
+            if (mm.z != 0xffffffffu) { const uint4 x = sl.X()[mm.z]; cnt += x.x; size += x.y; }
+            sl.X()[i] = make_uint4(cnt, size, 0u, 0u);
+        }
+        __syncwarp();
+    }
+    /* stream base of every pixel: exclusive scan of the roots' sizes (roots are nodes 0 .. nroots-1) */
+    uint32_t my_size = lane < nroots ? sl.X()[lane].y : 0u;
+    uint32_t scan = my_size;
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t v = __shfl_up_sync(kFull, scan, off);
+        if ((int)lane >= off) scan += v;
+    }
+    if (lane < nroots) { uint4 x = sl.X()[lane]; x.z = 0u; x.w = scan - my_size; sl.X()[lane] = x; }
+    const uint32_t pix_base = __shfl_sync(kFull, scan - my_size, my_root & 31u);
+    const uint32_t pix_size = __shfl_sync(kFull, my_size, my_root & 31u);
+    __syncwarp();
+    /* ranks and stream positions, first level first; the node's own first addition and the PUSH / POP marks */
+    float4* const stream = sl.stream();
+    for (uint32_t lv = 0; lv < nlev; lv++) {
+        const uint32_t b = lvl[lv], e = lvl[lv + 1u];
+        for (uint32_t i0 = b; i0 < e; i0 += 32u) {
+            const uint32_t i = i0 + lane;
+            const bool act = i < e;
+            uint32_t rank = 0, pixlane = 0;
+            bool sh = false;
+            if (act) {
+                const uint4 mm = sl.M()[i];
+                const uint4 x = sl.X()[i];
+                rank = x.z;
+                const uint32_t pos = x.w;
+                sh = ((mm.x >> 24) & 0xfu) == kNdShaded;
+                const float4 t = sl.T()[i];
+                stream[pos] = make_float4(t.x, t.y, t.z, __uint_as_float(kOpAdd));
+                if (sh) {
+                    uint32_t p = pos + own_shaded;
+                    uint32_t crank = rank + 1u;
+                    if ((mm.x >> 28) & 1u) {
+                        stream[p] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kOpPush));
+                        p += 1u;
+                        if (mm.y != 0xffffffffu) {
+                            uint4 cx = sl.X()[mm.y];
+                            const uint32_t ccnt = cx.x, csize = cx.y;
+                            cx.z = crank; cx.w = p;
+                            sl.X()[mm.y] = cx;
+                            crank += ccnt;
+                            p += csize;
+                        }
+                        stream[p] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kOpPop));
+                        p += 1u;
+                    }
+                    if (mm.z != 0xffffffffu) {
+                        uint4 cx = sl.X()[mm.z];
+                        cx.z = crank; cx.w = p;
+                        sl.X()[mm.z] = cx;
+                    }
+                    pixlane = (mm.x >> 16) & 31u;
+                }
+            }
+            /* RNG state on entry to the segment: xorshift32^(4L*rank)(pixel id); the pixel id (global: y*W + x,
+             * raytracing.cl:33) lives in the lane that owns that pixel of the tile */
+            const uint32_t seed = __shfl_sync(kFull, id, pixlane);
+            const uint32_t kmax = __reduce_max_sync(kFull, (act && sh) ? rank : 0u);
+            const uint32_t state = rng_jump(fp.jump, seed, (act && sh) ? rank : 0u, kmax);
+            if (act && sh) { uint4 x = sl.X()[i]; x.z = state; sl.X()[i] = x; }
+        }
+        __syncwarp();
+    }
+
+    /* ---- 3 SHADE: (shaded node, light) pairs over the lanes ---- */
+    const uint32_t items = n_shaded * L;
+#pragma unroll 1
+    for (uint32_t it = lane; it < items; it += 32u) {
+        const uint32_t k = it / L, li = it - k * L;
+        const uint32_t node = sl.shaded()[k];
+        const float4 s0 = sl.S0()[node], s1 = sl.S1()[node], s2 = sl.S2()[node];
+        const uint4 x = sl.X()[node];
+        const V3 ip = xyz(s0), nrm = xyz(s1), vv = xyz(s2);
+        const float fs = s0.w, fd = s1.w, shin = s2.w;
+        uint32_t rng = x.z;
+        for (uint32_t q = 0; q < 4u * li; q++) rng = xorshift_step(rng); /* the lights before this one drew 4 numbers each */
+        const float4 l0 = g.lgeo[li], l1 = g.laux[li];
+        float dist;
+        const V3 sdir = normalize_len(xyz(l0) - ip, dist);
+        float hlen;
+        const V3 hh = normalize_len(vv + sdir, hlen);
+        const float ndh = dot3(nrm, hh);
+        const float sx = 0.0f < ndh ? ndh : 0.0f;
+        const float ndl = dot3(nrm, sdir);
+        const float dif = 0.0f < ndl ? ndl : 0.0f;
+        /* R5: exact zeros -- only while pow(sx, shin) is finite (see rt_trace_fast.cuh) */
+        const bool tame = sx <= 1.0f && shin >= 0.0f;
+        const bool spec_zero = tame && ((fs == 0.0f) || (sx == 0.0f && shin > 0.0f));
+        const bool diff_zero = (fd == 0.0f) || (dif == 0.0f);
+        V3 spec = mk(0.0f, 0.0f, 0.0f), diffv = spec;
+        if (!(spec_zero && diff_zero)) {
+            float soft = 0.0f;
+#pragma unroll 1
+            for (int j = 0; j < kShadowSamples; j++) {
+                const float theta = (float)(kTwoPi * (double)rng_next(rng));
+                const float phi = (float)(kPi * (double)rng_next(rng));
+                float sp, cp, sth, cth;
+                sincos_bounded(phi, sp, cp);
+                sincos_bounded(theta, sth, cth);
+                const float rs = l1.w * sp;
+                const V3 sample = xyz(l0) + mk(rs * cth, rs * sth, l1.w * cp); /* raytracing.cl:101-106 */
+                soft += shadow_path_fast(sample, ip, g, tl);
+            }
+            if (!(soft == 0.0f && tame)) { /* else light_rgb *= 0: both terms are exact zeros */
+                const float ssr = soft / (float)kShadowSamples;
+                const V3 lrgb = div3_pos(xyz(l1) * 1.0f, dist * dist) * ssr;
+                if (!spec_zero) spec = (lrgb * fs) * pow_ieee(sx, shin);
+                if (!diff_zero) diffv = (lrgb * fd) * dif;
+            }
+        }
+        float4* slot = stream + x.w + 1u + 2u * li;
+        slot[0] = make_float4(spec.x, spec.y, spec.z, __uint_as_float(kOpAdd));
+        slot[1] = make_float4(diffv.x, diffv.y, diffv.z, __uint_as_float(kOpAdd));
+    }
+    __syncwarp();
+
+    /* ---- 4 REPLAY: additions in the stack machine's order ---- */
+    V3 acc = mk(0.0f, 0.0f, 0.0f);
+    if (live) {
+        V3 stk[kMaxDepth];
+        uint32_t sp = 0;
+        const float4* ev = stream + pix_base;
+#pragma unroll 4
+        for (uint32_t q = 0; q < pix_size; q++) {
+            const float4 r = ev[q];
+            const uint32_t op = __float_as_uint(r.w);
+            if (op == kOpAdd) acc = acc + xyz(r);
+            else if (op == kOpPush) { stk[sp++] = acc; acc = mk(0.0f, 0.0f, 0.0f); }
+            else { sp--; acc = stk[sp] + acc; }
+        }
+    }
+    word = pack_rgb(acc);
+    __syncwarp();
+    return true;
+}
+
+}  // namespace RT_NS

@@ -119,7 +119,12 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * "wide_min_records": scenes without triangles whose padded light + sphere records reach this number (default 64;
  * negative = never) run the WIDE variant of the production trace: rounds with few tracing lanes walk the records one
  * ray at a time over all 32 lanes.  "wide_max_live": -1 (default) = those are the rounds below the instruction
- * break-even; 0..32 = fixed limit (32 = every round, used by the tests).  Pixels do not change. */
+ * break-even; 0..32 = fixed limit (32 = every round, used by the tests).  Pixels do not change.
+ * "tree": level-wise pixel trees (csrc/rt_trace_tree.cuh: one pixel's segment tree expanded breadth-first over the
+ * 32 lanes, RNG jump-ahead, ordered replay).  1 (default) = the split queue entries of heavy tiles (rows of 8 pixels and
+ * single pixels); 0 = never; 2 = every tile; 3 = every tile, one pixel at a time (what a single-pixel entry does; tests).
+ * "tree_cap": nodes per warp slab (default 2048; a larger tree falls back to the cooperative walk).  Pixels do not
+ * change. */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
 /* Brute-force check of the arithmetic routines against IEEE division / sqrt (trials per thread on 592x256
  * threads).  out[0] = division mismatches, out[1] = normalize mismatches, out[2] = max |sincos - libdevice|

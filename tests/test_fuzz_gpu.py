@@ -80,5 +80,12 @@ def test_random_scene(pkg, ref, scene, host, seed):
                     rgb_w, hit_w = eng.render_to_host(W, H, want_hit=True)
                     eng.set_option("wide_min_records", 64); eng.set_option("wide_max_live", -1)
                     assert np.array_equal(rgb_w, rgb) and np.array_equal(hit_w, hit), (seed, "wide", max_live)
+                # the level-wise pixel-tree trace: every tile as one pooled tree (2), every pixel on its own (3) -- what
+                # the split queue entries of heavy tiles run; must be the stack machine's words
+                for tree in (2, 3):
+                    eng.set_option("tree", tree)
+                    rgb_t, hit_t = eng.render_to_host(W, H, want_hit=True)
+                    assert np.array_equal(rgb_t, rgb) and np.array_equal(hit_t, hit), (seed, "tree", tree)
+                eng.set_option("tree", 1)
     finally:
         eng.close()
