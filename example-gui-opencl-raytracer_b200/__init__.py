@@ -53,7 +53,7 @@ class MapArchive(C.Structure):
 
 class LaunchInfo(C.Structure):
     _fields_ = [("grid", C.c_uint32), ("block", C.c_uint32), ("smem_bytes", C.c_uint32), ("tiles", C.c_uint32),
-                ("resident_scene", C.c_uint32)]
+                ("resident_scene", C.c_uint32), ("tree_grid", C.c_uint32)]
 
 
 _lib = None

@@ -77,7 +77,10 @@ struct rtb_engine {
     DevBuf tree_slab;         /* per-warp node storage of the level-wise pixel-tree trace (rt_trace_tree.cuh) */
     DevBuf jump;              /* [15][32] xorshift32 jump-ahead matrices for this scene's light count */
     uint32_t jump_L = 0xffffffffu;
-    int opt_tree = 1, opt_tree_cap = 2048;
+    int opt_tree = 1, opt_tree_cap = 8192, opt_tree_min_cost = 0 /* 0 = automatic */, opt_tree_group_max_cost = 0;
+    bool cost_hist_valid = false; /* tile_cost holds measured-time costs of a frame with this geometry */
+    cudaStream_t aux = nullptr;   /* render_tree runs here, beside render_frame */
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
     int time_cur = 0;
     bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
@@ -110,6 +113,9 @@ void rtb_destroy(rtb_engine* e) {
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
     e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
     e->tree_slab.release(); e->wait_word.release(); e->jump.release();
+    if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+    if (e->ev_join) cudaEventDestroy(e->ev_join);
+    if (e->aux) { cudaStreamSynchronize(e->aux); cudaStreamDestroy(e->aux); }
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->evk) cudaEventDestroy(e->evk);
@@ -122,6 +128,13 @@ static int create_impl(rtb_engine* e) {
     CU(cudaEventCreate(&e->ev0), "cudaEventCreate");
     CU(cudaEventCreate(&e->ev1), "cudaEventCreate");
     CU(cudaEventCreate(&e->evk), "cudaEventCreate");
+    {
+        int lo = 0, hi = 0; /* numerically lower = higher priority */
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi), "cudaDeviceGetStreamPriorityRange");
+        CU(cudaStreamCreateWithPriority(&e->aux, cudaStreamNonBlocking, hi), "cudaStreamCreateWithPriority");
+        CU(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming), "cudaEventCreate");
+        CU(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming), "cudaEventCreate");
+    }
     if (e->sched.ensure(256)) return -2;
     CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "cudaMemsetAsync");
     CU(cudaStreamSynchronize(e->stream), "cudaStreamSynchronize");
@@ -351,6 +364,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     e->mirror_global = false;
     if ((uintptr_t)fp.mirror & 15) return fail(-1, "rtb_render: mirror buffer must be 16-byte aligned");
     fp.tile_counter = (unsigned int*)e->sched.p;
+    fp.tree_counter = (unsigned int*)((char*)e->sched.p + 4);
     fp.done_counter = (unsigned int*)((char*)e->sched.p + 32);
     fp.done_flag = e->done_flag;
     fp.done_value = e->done_value;
@@ -371,6 +385,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.wide_max_live = e->opt_wide_max_live;
     fp.split_min_cost = 64u;
     fp.split32_min_cost = 64u;
+    fp.tree_min_cost = 64u;
     /* queue entries carry the tile index in 24 bits (rt_kernels.cu): beyond 2^24 tiles (> 536 Mpixel) the queue stays row-major */
     if (e->opt_tile_order && e->last.tiles >= 4096 && e->last.tiles < (1u << 24)) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
@@ -398,16 +413,33 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                         double c = 24.0 + 4.0 * log2(alpha * per_warp) + 0.5;
                         return (uint32_t)(c < floor_cost ? floor_cost : (c > 64.0 ? 64.0 : c));
                     };
-                    fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(0.75, 40.0);
-                    fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : thr(3.0, 48.0);
+                    const bool tree = e->opt_tree > 0 && e->L <= 16u;
+                    if (tree) {
+                        /* with the CTA-wide pixel-tree kernel beside render_frame (tools/exp/sweep_tree.py): tiles longer than
+                         * 0.75 T go to it whole (4 warps on the tile's pooled segment trees), tiles longer than 3 T as four
+                         * row entries (16 warps); single-pixel entries no longer pay */
+                        fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(3.0, 44.0);
+                        fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : 64u;
+                        uint32_t t = e->opt_tree_min_cost > 0 ? (uint32_t)e->opt_tree_min_cost : thr(0.75, 32.0);
+                        if (fp.split_min_cost < t) t = fp.split_min_cost;
+                        if (fp.split32_min_cost < t) t = fp.split32_min_cost;
+                        fp.tree_min_cost = t;
+                        fp.tree_group_max_cost = e->opt_tree_group_max_cost > 0 ? (uint32_t)e->opt_tree_group_max_cost : t + 8u;
+                        fp.cost_is_history = e->cost_hist_valid ? 1u : 0u;
+                    } else {
+                        fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(0.75, 40.0);
+                        fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : thr(3.0, 48.0);
+                    }
                 }
             }
+            e->cost_hist_valid = same; /* this frame's costs come from measured times: the next one may lean on them */
             e->time_cur = 1 - e->time_cur;
             e->time_valid = true;
             e->tk_W = W; e->tk_H = H; e->tk_total = total; e->tk_band = pp.band_rows; e->tk_parts = pp.parts; e->tk_part = pp.part;
             e->tk_scene_gen = e->scene_gen + e->T;
         } else if (mode == 0) {
             e->time_valid = false;
+            e->cost_hist_valid = false;
         } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
         CU((e->T ? rt_launch_tile_order_tri : rt_launch_tile_order)(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),
@@ -415,13 +447,14 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
         fp.order = (const uint32_t*)e->tile_order.p;
         fp.cost = (const uint32_t*)e->tile_cost.p;
         fp.queue_len = (const uint32_t*)e->tile_hist.p + 128;
+        fp.n_split = (const uint32_t*)e->tile_hist.p + 129;
     }
-    /* level-wise pixel trees for the split entries of heavy tiles (rt_trace_tree.cuh): production trace only, and only
-     * while a node's 1 + 2L addition slots stay small */
+    /* level-wise pixel trees for the heavy queue entries (rt_trace_tree.cuh): production trace only, and only while a
+     * node's 1 + 2L addition slots stay small.  One slab per CTA of the persistent grid. */
     fp.tree_mode = 0;
-    if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && (fp.order || e->opt_tree >= 2)) {
+    if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && ((fp.order && fp.tree_min_cost < 64u) || e->opt_tree >= 2)) {
         const uint32_t cap = (uint32_t)e->opt_tree_cap;
-        const uint32_t slots = (uint32_t)e->sm_count * 6u * 4u; /* >= resident warps: <= 5 CTAs of 4 warps per SM at 96 registers */
+        const uint32_t slots = (uint32_t)e->sm_count * 3u; /* = the render_tree grid: one slab per CTA */
         const size_t records = rt_tree_slab_records(cap, e->L);
         if (e->tree_slab.ensure(records * 16 * slots) == 0) {
             fp.tree_slab = (float4*)e->tree_slab.p;
@@ -436,11 +469,13 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
-    CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
+    const RtTreeLaunch tree = {e->aux, e->ev_fork, e->ev_join};
+    CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, mode, e->sm_count, e->stream, &shape, fp.tree_mode ? &tree : nullptr), "render_frame launch");
     CU(cudaEventRecord(e->ev1, e->stream), "event record");
     e->timed = true;
     e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;
     e->last.resident_scene = shape.resident;
+    e->last.tree_grid = shape.tree_grid;
     if (counters) {
         unsigned long long host[RTB_NCOUNTERS];
         CU(cudaMemcpyAsync(host, fp.counters, sizeof host, cudaMemcpyDeviceToHost, e->stream), "D2H counters");
@@ -483,6 +518,8 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!strcmp(name, "wide_max_live")) { e->opt_wide_max_live = value > 32 ? 32 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     if (!strcmp(name, "tree")) { e->opt_tree = value < 0 ? 0 : (value > 3 ? 3 : value); return 0; }
+    if (!strcmp(name, "tree_group_max_cost")) { e->opt_tree_group_max_cost = value < 0 ? 0 : value; return 0; }
+    if (!strcmp(name, "tree_min_cost")) { e->opt_tree_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tree_cap")) { e->opt_tree_cap = value < 64 ? 64 : (value > 32768 ? 32768 : value); e->tree_slab.release(); return 0; }
     return fail(-1, "rtb_set_option: unknown option");
 }

@@ -34,6 +34,197 @@ namespace RT_NS {
 #endif
 extern __shared__ __align__(128) unsigned char rt_smem[];
 
+#ifndef RT_TREE
+#define RT_TREE 1 /* 0: compile the level-wise pixel-tree phase out (A/B builds) */
+#endif
+
+/* Frame (and hit-id, and mirror) stores of one tree entry by warp 0: lanes 0 and 4 of each tile row store 4 pixels =
+ * 16 bytes after a shuffle transpose; single-pixel entries and frames whose rows are not 16-byte aligned store scalars.
+ * (The main loop of render_frame has the same code inline.) */
+template <bool AOV>
+__device__ __forceinline__ void store_tile(const RtFrameParams& fp, const TileLanes& tq, uint32_t sub, uint32_t lane, uint32_t word,
+                                           uint32_t hid) {
+    const bool vec_store = (fp.W % 4u) == 0u; /* rows are 16-byte aligned */
+    const bool live = tq.live;
+    const uint32_t id = tq.id;
+    const size_t at = tq.at;
+    const size_t mat = fp.mirror_global ? (size_t)id : at; /* mirror in full-frame (row-major) or compact layout */
+    if (vec_store && sub <= 4u) {
+        uint32_t w1 = __shfl_down_sync(0xffffffffu, word, 1);
+        uint32_t w2 = __shfl_down_sync(0xffffffffu, word, 2);
+        uint32_t w3 = __shfl_down_sync(0xffffffffu, word, 3);
+        uint32_t live3 = __shfl_down_sync(0xffffffffu, (uint32_t)live, 3);
+        if ((lane & 3u) == 0u && live) {
+            if (live3) {
+                *reinterpret_cast<uint4*>(fp.out + at) = make_uint4(word, w1, w2, w3);
+                if (fp.mirror) __stcs(reinterpret_cast<uint4*>(fp.mirror + mat), make_uint4(word, w1, w2, w3));
+            } else { /* id >= total inside this quad: scalar tail */
+                fp.out[at] = word;
+                if (id + 1 < fp.total) fp.out[at + 1] = w1;
+                if (id + 2 < fp.total) fp.out[at + 2] = w2;
+                if (fp.mirror) {
+                    fp.mirror[mat] = word;
+                    if (id + 1 < fp.total) fp.mirror[mat + 1] = w1;
+                    if (id + 2 < fp.total) fp.mirror[mat + 2] = w2;
+                }
+            }
+        }
+        if (AOV && fp.hit) {
+            uint32_t h1 = __shfl_down_sync(0xffffffffu, hid, 1);
+            uint32_t h2 = __shfl_down_sync(0xffffffffu, hid, 2);
+            uint32_t h3 = __shfl_down_sync(0xffffffffu, hid, 3);
+            if ((lane & 3u) == 0u && live) {
+                if (live3) *reinterpret_cast<uint4*>(fp.hit + at) = make_uint4(hid, h1, h2, h3);
+                else {
+                    fp.hit[at] = hid;
+                    if (id + 1 < fp.total) fp.hit[at + 1] = h1;
+                    if (id + 2 < fp.total) fp.hit[at + 2] = h2;
+                }
+            }
+        }
+    } else if (live) {
+        fp.out[at] = word;
+        if (fp.mirror) fp.mirror[mat] = word;
+        if (AOV && fp.hit) fp.hit[at] = hid;
+    }
+}
+
+/* Completion signal: every thread fences its frame stores (they may target a peer GPU or host memory), the CTA joins,
+ * and the last CTA of the frame's kernels (render_frame and, beside it, render_tree: fp.done_expected CTAs in all)
+ * publishes the frame number. */
+__device__ __forceinline__ void signal_done(const RtFrameParams& fp) {
+    if (fp.done_flag) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int prev = atomicAdd(fp.done_counter, 1u);
+            if (prev + 1u == fp.done_expected) {
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(fp.done_flag), "r"(fp.done_value) : "memory");
+            }
+        }
+    }
+}
+
+/* Per CTA: TMA-stage the record blob into shared memory (when resident), fill the /255 table, bind the geometry. */
+template <bool RESIDENT>
+__device__ __forceinline__ void stage_geometry(const RtFrameParams& fp, uint64_t* bar, float* lut255, Geo& g) {
+    if (RESIDENT) {
+        const uint32_t bytes = fp.lay.total * 16u;
+        if (threadIdx.x == 0) mbar_init(bar, 1);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(bar, bytes);
+            const uint32_t kChunk = 32768u; /* the object array travels in chunks of <= 32 KiB */
+            for (uint32_t off = 0; off < bytes; off += kChunk) {
+                uint32_t nb = bytes - off < kChunk ? bytes - off : kChunk;
+                tma_bulk_g2s(rt_smem + off, reinterpret_cast<const unsigned char*>(fp.blob) + off, nb, bar);
+            }
+        }
+    }
+    for (uint32_t i = threadIdx.x; i < 256u; i += kBlock) lut255[i] = (float)i / 255.0f; /* overlaps the copy */
+    if (RESIDENT) {
+        mbar_wait(bar, 0);
+        geo_bind(g, reinterpret_cast<const float4*>(rt_smem), fp, lut255);
+    } else {
+        geo_bind(g, fp.blob, fp, lut255);
+    }
+    __syncthreads();
+}
+
+/* ---- render_tree: the heavy entries of the queue as level-wise pixel trees, one CTA per entry at a time
+ * (rt_trace_tree.cuh).  A kernel of its own, launched on a second stream just before render_frame: sharing a kernel
+ * cost render_frame's main loop 8 % (2.65 -> 2.87 ms per 4K frame) even with the phase switched off.  An entry whose
+ * tree outgrows the slab is walked by warp 0 with the cooperative trace -- same words. ---- */
+template <bool RESIDENT, bool AOV>
+__global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__ RtFrameParams fp) {
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ float lut255[256];
+    __shared__ TreeShared tsh;
+    Geo g;
+    stage_geometry<RESIDENT>(fp, &bar, lut255, g);
+    const uint32_t lane = threadIdx.x & 31u;
+    CoopSmem cs; /* scratch of the fallback walk (warp 0 only) */
+    {
+        unsigned char* base = rt_smem + (RESIDENT ? fp.lay.total * 16u : 0u);
+        cs.owner = reinterpret_cast<float4*>(base);
+        cs.task = cs.owner + 32;
+        cs.light = cs.task + kCoopTasks;
+        cs.pre = cs.light + 32 * kCoopLights;
+    }
+    const uint32_t ntiles = fp.order ? __ldg(fp.queue_len) : fp.tiles_x * fp.tiles_y;
+    const uint32_t n_tree = fp.tree_mode >= 2u ? ntiles : (fp.order ? __ldg(fp.n_split) : 0u);
+    const TreeSlab sl = {fp.tree_slab + (size_t)blockIdx.x * fp.tree_records, fp.tree_cap};
+    unsigned long long warp_time = 0;
+    const uint32_t warp = threadIdx.x >> 5;
+    for (;;) {
+        /* the heaviest entries one at a time (their chains bound the frame); the lighter ones four to a pass: a lone
+         * tile of a few hundred segments leaves most of the 128 lanes idle at every level of its tree */
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t slot = atomicAdd(fp.tree_counter, 1u), n = 0;
+            if (slot < n_tree) {
+                tsh.entry[n++] = fp.order ? __ldg(fp.order + slot) : slot;
+                const uint32_t e0 = tsh.entry[0];
+                const bool alone = fp.tree_mode == 3u || (fp.cost && __ldg(fp.cost + (e0 & 0x00ffffffu)) >= fp.tree_group_max_cost);
+                if (!alone) {
+                    slot = atomicAdd(fp.tree_counter, kTreeGroup - 1u);
+                    for (uint32_t k = 0; k < kTreeGroup - 1u && slot + k < n_tree; k++) tsh.entry[n++] = fp.order ? __ldg(fp.order + slot + k) : slot + k;
+                }
+            }
+            tsh.count = n;
+        }
+        __syncthreads();
+        const uint32_t ne = tsh.count;
+        if (ne == 0u) break;
+        /* one pooled pass; should it outgrow the slab, entry by entry; and an entry that does not fit alone is walked
+         * by warp 0 with the cooperative trace */
+        uint32_t first = 0, span = ne;
+        while (first < ne) {
+            const long long clk0 = clock64();
+            /* "tree" = 3 (tests): every pixel of the entry on its own, as single-pixel queue entries are; else one pass */
+            bool traced = true;
+            const uint32_t rounds = fp.tree_mode == 3u ? 32u : 1u;
+#pragma unroll 1
+            for (uint32_t p = 0; p < rounds && traced; p++) {
+                if (rounds > 1u && !tile_lanes(fp, tsh.entry[first], p).live) continue;
+                traced = trace_entry_tree<AOV>(fp, g, sl, tsh, first, span, rounds > 1u ? p : 32u);
+            }
+            if (!traced && span > 1u) { span = 1u; __syncthreads(); continue; } /* CTA-uniform; the barrier keeps the retry off the scratch the failed pass is still reading */
+            if (warp < span) { /* warp w stores entry first + w, lane p = tile pixel p */
+                const uint32_t entry = tsh.entry[first + warp];
+                const TileLanes tq = tile_lanes(fp, entry, lane);
+                uint32_t word = 0, hid = 0;
+                if (traced) {
+                    if (tq.live) { word = tsh.word[threadIdx.x]; hid = tsh.hid[threadIdx.x]; }
+                } else { /* span == 1, warp 0: the tree did not fit the slab */
+                    Tally<false> tl;
+                    uint32_t nseg = 0;
+                    word = trace_tile_coop<false, AOV, false>(fp, g, cs, tq.id, tq.live, lane, hid, nseg, tl);
+                    __syncwarp();
+                }
+                if (fp.tile_time && lane == 0) {
+                    /* warp-time units, like render_frame; a pooled pass is shared out by shaded segments */
+                    uint32_t dt = (uint32_t)((clock64() - clk0) >> 10) * (traced ? kBlock / 32 : 1u);
+                    if (traced && span > 1u) {
+                        uint32_t tot = 0;
+                        for (uint32_t k = 0; k < span; k++) tot += tsh.shaded_of[k] + 1u;
+                        dt = (uint32_t)(((unsigned long long)dt * (tsh.shaded_of[warp] + 1u)) / tot);
+                    }
+                    dt += 1u;
+                    atomicAdd(fp.tile_time + (entry & 0x00ffffffu), dt);
+                    warp_time += dt;
+                }
+                store_tile<AOV>(fp, tq, entry >> 24, lane, word, hid);
+            }
+            first += span;
+            __syncthreads(); /* tsh.word / shaded_of are read above and rewritten by the next pass */
+        }
+    }
+    if (fp.tile_time && lane == 0 && warp_time) atomicAdd(fp.tile_time_sum, warp_time);
+    signal_done(fp);
+}
+
 /* MODE: 0 = cooperative trace (production), 1 = literal + counters (reference accounting), 2 = cooperative +
  * counters (executed work), 3 = per-lane fast trace (the previous production path, kept for A/B),
  * 4 = cooperative trace, WIDE variant (rt_trace_coop.cuh: one ray over 32 lanes; scenes with many spheres) */
@@ -42,31 +233,11 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
     constexpr bool COUNT = MODE == 1 || MODE == 2;
     constexpr bool COOP = MODE == 0 || MODE == 2 || MODE == 4;
     constexpr bool WIDE = MODE == 4;
-    constexpr bool TREE = MODE == 0 || MODE == 4; /* split entries of heavy tiles may run as level-wise pixel trees */
+    constexpr bool TREE = MODE == 0 || MODE == 4; /* heavy entries may run as level-wise pixel trees (phase 1) */
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
     Geo g;
-    if (RESIDENT) {
-        const uint32_t bytes = fp.lay.total * 16u;
-        if (threadIdx.x == 0) mbar_init(&bar, 1);
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            mbar_expect_tx(&bar, bytes);
-            const uint32_t kChunk = 32768u; /* the object array travels in chunks of <= 32 KiB */
-            for (uint32_t off = 0; off < bytes; off += kChunk) {
-                uint32_t nb = bytes - off < kChunk ? bytes - off : kChunk;
-                tma_bulk_g2s(rt_smem + off, reinterpret_cast<const unsigned char*>(fp.blob) + off, nb, &bar);
-            }
-        }
-    }
-    for (uint32_t i = threadIdx.x; i < 256u; i += kBlock) lut255[i] = (float)i / 255.0f; /* overlaps the copy */
-    if (RESIDENT) {
-        mbar_wait(&bar, 0);
-        geo_bind(g, reinterpret_cast<const float4*>(rt_smem), fp, lut255);
-    } else {
-        geo_bind(g, fp.blob, fp, lut255);
-    }
-    __syncthreads();
+    stage_geometry<RESIDENT>(fp, &bar, lut255, g);
 
     const uint32_t lane = threadIdx.x & 31u;
     CoopSmem cs;
@@ -84,12 +255,16 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
     tl.clear();
 
     unsigned long long warp_time = 0; /* sum of this warp's tile times: the frame total gives the mean the next frame's costs are relative to */
+
+    /* The first n_tree entries of the cost-ordered queue (tiles at or above fp.tree_min_cost and the split entries of the
+     * heaviest ones) belong to the render_tree kernel, which runs beside this one on a second stream. */
+    const uint32_t n_tree = (RT_TREE && TREE && fp.tree_mode) ? (fp.tree_mode >= 2u ? ntiles : (fp.order ? __ldg(fp.n_split) : 0u)) : 0u;
     uint32_t next = 0;
-    if (lane == 0) next = atomicAdd(fp.tile_counter, 1u);
+    if (lane == 0) next = atomicAdd(fp.tile_counter, 1u) + n_tree;
     for (;;) {
         const uint32_t slot = __shfl_sync(0xffffffffu, next, 0);
         if (slot >= ntiles) break;
-        if (lane == 0) next = atomicAdd(fp.tile_counter, 1u); /* prefetch: latency hides behind this tile */
+        if (lane == 0) next = atomicAdd(fp.tile_counter, 1u) + n_tree; /* prefetch: latency hides behind this tile */
         const uint32_t entry = fp.order ? __ldg(fp.order + slot) : slot;
         const uint32_t tile = entry & 0x00ffffffu;
         const uint32_t sub = entry >> 24; /* 0: whole 8x4 tile; 1..4: only tile row sub-1; 5..36: only pixel sub-5 (split heavy tiles) */
@@ -111,27 +286,7 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
          * per-lane walk has less lock-step overhead on the cheap majority.  Same words either way. */
         const bool heavy = COOP && (!fp.cost || __ldg(fp.cost + tile) >= fp.coop_min_cost);
         if (heavy) {
-            bool traced = false;
-            if (TREE && fp.tree_mode && (sub != 0u || fp.tree_mode >= 2u)) {
-                const uint32_t warp_slot = blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5);
-                if (warp_slot < fp.tree_slots) {
-                    const TreeSlab sl = {fp.tree_slab + (size_t)warp_slot * fp.tree_records, fp.tree_cap};
-                    uint32_t* lvl = reinterpret_cast<uint32_t*>(cs.owner); /* the cooperative walk's scratch is idle here */
-                    if (fp.tree_mode != 3u) {
-                        traced = trace_tile_tree<AOV>(fp, g, sl, lvl, id, live, lane, word, hid);
-                    } else { /* tests: every pixel of the tile on its own, as single-pixel queue entries are */
-                        traced = true;
-                        const uint32_t lm = __ballot_sync(0xffffffffu, live);
-                        for (uint32_t p = 0; p < 32u && traced; p++) {
-                            if (!((lm >> p) & 1u)) continue;
-                            uint32_t w1 = 0, h1 = 0;
-                            traced = trace_tile_tree<AOV>(fp, g, sl, lvl, id, lane == p, lane, w1, h1);
-                            if (lane == p) { word = w1; hid = h1; }
-                        }
-                    }
-                }
-            }
-            if (!traced) word = trace_tile_coop<COUNT, AOV, WIDE>(fp, g, cs, id, live, lane, hid, nseg, tl);
+            word = trace_tile_coop<COUNT, AOV, WIDE>(fp, g, cs, id, live, lane, hid, nseg, tl);
         } else if (live) {
             if (MODE == 1) word = trace_pixel_literal<COUNT, AOV>(fp, g, id, hid, tl);
             else word = trace_pixel_fast<COUNT, AOV>(fp, g, id, hid, tl);
@@ -207,19 +362,7 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
         }
     }
 
-    /* completion signal: every thread fences its frame stores (they may target a peer GPU or host memory), the CTA
-     * joins, and the last CTA of the grid publishes the frame number */
-    if (fp.done_flag) {
-        __threadfence_system();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            const unsigned int prev = atomicAdd(fp.done_counter, 1u);
-            if (prev + 1u == gridDim.x) {
-                __threadfence_system();
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(fp.done_flag), "r"(fp.done_value) : "memory");
-            }
-        }
-    }
+    signal_done(fp);
 }
 
 /* ---- scene_prep: wire arrays -> compact blob (one thread per record slot) ---- */
@@ -368,7 +511,8 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
  * absolute speed (render.map: mean 29 us; the 1,024-sphere grid: 4.5 ms).  Replaces the skeleton trace whenever a frame of the same geometry has just been rendered. ---- */
 __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsigned long long* __restrict__ prev_sum,
                                   uint32_t* __restrict__ cost_out,
-                                  uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost, uint32_t split32_min_cost) {
+                                  uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost, uint32_t split32_min_cost,
+                                  uint32_t sticky_cost) {
     __shared__ uint32_t shist[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
     __syncthreads();
@@ -378,6 +522,10 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsig
         const float rel = 24.0f + 4.0f * __log2f(fmaxf((float)prev[tile], 0.5f) / mean);
         uint32_t c = rel <= 0.0f ? 0u : (uint32_t)rel;
         c = c < kCostBuckets ? c : kCostBuckets - 1u;
+        /* hysteresis: a tile that the pixel-tree kernel took last frame (cost_out still holds that frame's costs) stays
+         * with it until its measured time has dropped two octaves below the threshold -- a tile whose tree pass is
+         * cheaper than its cooperative walk would otherwise change sides every frame (N = 4: 0.74 / 1.12 ms alternating) */
+        if (sticky_cost < kCostBuckets && c < sticky_cost && c + 8u >= sticky_cost && cost_out[tile] >= sticky_cost) c = sticky_cost;
         cost_out[tile] = c;
         atomicAdd(&shist[c], split_ways(c, split_min_cost, split32_min_cost));
     }
@@ -390,13 +538,17 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsig
  * One global atomic per (block, bucket): ranks inside a block come from shared-memory atomics. */
 __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __restrict__ hist,
                            uint32_t* __restrict__ cursor, uint32_t* __restrict__ order, uint32_t ntiles,
-                           uint32_t split_min_cost, uint32_t split32_min_cost, uint32_t* __restrict__ queue_len) {
+                           uint32_t split_min_cost, uint32_t split32_min_cost, uint32_t first_heavy, uint32_t* __restrict__ queue_len) {
     __shared__ uint32_t base[kCostBuckets], local[kCostBuckets], gbase[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) local[i] = 0;
     if (threadIdx.x == 0) {
-        uint32_t acc = 0;
-        for (int b = (int)kCostBuckets - 1; b >= 0; b--) { base[b] = acc; acc += hist[b]; }
-        if (blockIdx.x == 0) *queue_len = acc;
+        uint32_t acc = 0, nheavy = 0;
+        for (int b = (int)kCostBuckets - 1; b >= 0; b--) {
+            base[b] = acc;
+            acc += hist[b];
+            if ((uint32_t)b >= first_heavy) nheavy = acc; /* the entries of the heavy buckets form a prefix of the queue */
+        }
+        if (blockIdx.x == 0) { queue_len[0] = acc; queue_len[1] = nheavy; }
     }
     __syncthreads();
     const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
@@ -531,8 +683,27 @@ cudaError_t prep_variant(int* blocks_per_sm, uint32_t smem) {
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_frame<R, M, A>, kBlock, smem);
 }
 
+/* The tree kernel beside the main one: forked onto `aux` (created with a higher priority, launched first so that its
+ * CTAs -- the heaviest entries of the frame -- are resident when render_frame's persistent CTAs fill the rest), joined
+ * back into `st`. */
+template <bool R, bool A>
+cudaError_t go_tree(const RtFrameParams& fp, uint32_t grid, uint32_t smem, cudaStream_t st, cudaStream_t aux, cudaEvent_t fork, cudaEvent_t join) {
+    if (smem > 48u * 1024u) {
+        cudaError_t e = cudaFuncSetAttribute(render_tree<R, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    cudaError_t e = cudaEventRecord(fork, st);
+    if (e != cudaSuccess) return e;
+    e = cudaStreamWaitEvent(aux, fork, 0);
+    if (e != cudaSuccess) return e;
+    render_tree<R, A><<<grid, kBlock, smem, aux>>>(fp);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    return cudaEventRecord(join, aux);
+}
+
 template <bool R, int M, bool A>
-cudaError_t go(const RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, RtLaunchShape* shape) {
+cudaError_t go(RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, RtLaunchShape* shape, const RtTreeLaunch* tree) {
     int bps = 0;
     cudaError_t e = prep_variant<R, M, A>(&bps, smem);
     if (e != cudaSuccess) return e;
@@ -543,8 +714,27 @@ cudaError_t go(const RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t 
     const uint32_t need = (ntiles + warps_per_cta - 1) / warps_per_cta;
     if (grid > need) grid = need;
     if (grid == 0) grid = 1;
-    if (shape) { shape->grid = grid; shape->block = kBlock; shape->smem_bytes = smem; shape->resident = R; }
-    return launch_variant<R, M, A>(fp, grid, smem, st);
+    if (shape) { shape->grid = grid; shape->block = kBlock; shape->smem_bytes = smem; shape->resident = R; shape->tree_grid = 0; }
+    const bool with_tree = RT_TREE && (M == 0 || M == 4) && fp.tree_mode && tree && tree->aux;
+    uint32_t tgrid = 0;
+    if (with_tree) {
+        tgrid = fp.tree_slots;
+        if (tgrid > ntiles) tgrid = ntiles;
+        if (tgrid == 0) tgrid = 1;
+    } else {
+        fp.tree_mode = 0;
+    }
+    fp.done_expected = grid + tgrid;
+    if (with_tree) {
+        const uint32_t tsmem = (R ? fp.lay.total * 16u : 0u) + kCoopBytesPerWarp;
+        e = go_tree<R, A>(fp, tgrid, tsmem, st, tree->aux, tree->fork, tree->join);
+        if (e != cudaSuccess) return e;
+        if (shape) shape->tree_grid = tgrid;
+    }
+    e = launch_variant<R, M, A>(fp, grid, smem, st);
+    if (e != cudaSuccess) return e;
+    if (with_tree) e = cudaStreamWaitEvent(st, tree->join, 0);
+    return e;
 }
 
 }  // namespace RT_NS
@@ -582,19 +772,22 @@ cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* 
 cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                  cudaStream_t st) {
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
-    cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, (2 * kCostBuckets + 1) * sizeof(uint32_t), st);
+    cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, (2 * kCostBuckets + 2) * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
     const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
-    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost);
+    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost,
+                                                                                  fp.cost_is_history ? fp.tree_min_cost : kCostBuckets);
     else tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     tile_order<<<(ntiles + 255) / 256, 256, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles,
-                                                    fp.split_min_cost, fp.split32_min_cost, d_hist_cursor + 2 * kCostBuckets);
+                                                    fp.split_min_cost, fp.split32_min_cost, fp.tree_min_cost, d_hist_cursor + 2 * kCostBuckets);
     return cudaGetLastError();
 }
 
-cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape) {
+cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape,
+                                     const RtTreeLaunch* tree) {
+    RtFrameParams fp = fp_in;
     const uint32_t blob_bytes = fp.lay.total * 16u;
     /* keep the geometry resident while it leaves room for >= 2 CTAs per SM */
     const bool resident = blob_bytes <= 96u * 1024u;
@@ -604,7 +797,7 @@ cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp, int mode, int s
     const bool coop = mode == 0 || mode == 2 || mode == 4;
     const uint32_t smem = (resident ? blob_bytes : 0u) + (coop ? (kBlock / 32) * kCoopBytesPerWarp : 0u);
     const bool aov = fp.hit != nullptr;
-#define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape)
+#define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape, tree)
 #define RT_GO_A(R, M) do { if (aov) RT_GO(R, M, true); else RT_GO(R, M, false); } while (0)
 #if RT_TRIANGLES
 #define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else RT_GO_A(R, 3); } while (0)

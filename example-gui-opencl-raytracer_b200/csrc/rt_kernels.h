@@ -82,6 +82,12 @@ struct RtFrameParams {
     const unsigned long long* tile_time_sum_prev; /* the previous frame's */
     const uint32_t* tile_time_prev; /* the previous frame's, used as next cost estimate instead of the skeleton trace, or NULL */
     const uint32_t* queue_len;  /* number of queue entries when `order` is set (tiles + 3 per split tile) */
+    const uint32_t* n_split;    /* ... of which the first *n_split are heavy (cost >= tree_min_cost): the render_tree kernel's share */
+    uint32_t tree_min_cost;     /* 64 = none */
+    uint32_t tree_group_max_cost; /* heavy entries below this cost are pooled four to a CTA pass; from it on they run alone */
+    uint32_t cost_is_history;   /* the cost buffer still holds the previous frame's measured-time costs (hysteresis) */
+    unsigned int* tree_counter; /* zeroed before launch: render_tree's queue cursor */
+
     uint32_t split32_min_cost;  /* ... into 32 single-pixel entries (64 = never) */
     uint32_t split_min_cost;    /* tiles whose estimate reaches this are split into four 8x1 sub-tiles (64 = never) */
     uint32_t wide_min_records;  /* light+sphere records (padded) from which the WIDE kernel variant is launched */
@@ -91,14 +97,15 @@ struct RtFrameParams {
     float4* tree_slab;          /* NULL: never */
     unsigned long long tree_records;
     uint32_t tree_cap;          /* nodes per slab */
-    uint32_t tree_slots;        /* slabs allocated: warp slot = blockIdx.x * warps per CTA + warp */
-    uint32_t tree_mode;         /* 0 off; 1 split queue entries (rows / single pixels of heavy tiles); 2 every tile; 3 every tile, pixel by pixel (tests) */
+    uint32_t tree_slots;        /* slabs allocated, one per CTA */
+    uint32_t tree_mode;         /* 0 off; 1 heavy queue entries (cost >= tree_min_cost); 2 every tile; 3 every tile, pixel by pixel (tests) */
     const uint32_t* jump;       /* [15][32] bit matrices (xorshift32^(4L))^(2^j), see rt_engine.cu */
     unsigned long long* counters; /* RTB_NCOUNTERS, only for the counted variant */
     /* completion signal (multi-GPU, fused into the render): when done_flag is set, the LAST CTA to finish stores
      * done_value there with a system-scope release store -- after every store of the frame (band buffer, mirror / peer
      * frame) has been fenced -- so the gathering rank can wait on a word in its own memory instead of a collective */
     unsigned int* done_counter; /* zeroed before launch */
+    uint32_t done_expected;     /* CTAs of the frame's kernels (render_frame + render_tree); set by the launcher */
     uint32_t* done_flag;        /* may be NULL; device-visible: a peer GPU's memory (CUDA IPC) or mapped host memory */
     uint32_t done_value;
 };
@@ -109,13 +116,20 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
                                  cudaStream_t st);
 
 struct RtLaunchShape {
-    uint32_t grid, block, smem_bytes, resident;
+    uint32_t grid, block, smem_bytes, resident, tree_grid;
+};
+/* Second stream (and the fork / join events) on which the render_tree kernel runs beside render_frame; NULL = no tree phase. */
+struct RtTreeLaunch {
+    cudaStream_t aux;
+    cudaEvent_t fork, join;
 };
 /* Launches the fused raygen+raytracer kernel.  mode: 0 = cooperative trace, 1 = literal trace + reference work
  * counters, 2 = cooperative trace + executed-work counters, 3 = per-lane fast trace.  Geometry is staged in shared memory when it fits. */
-cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
+cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape,
+                             const RtTreeLaunch* tree);
 
-/* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[129] (zeroed here; word 128 receives the queue length),
+/* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[130] (zeroed here; word 128 receives the queue length, word 129
+ * the number of leading heavy entries),
  * d_order[32*ntiles]. */
 cudaError_t rt_launch_tile_order(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                  cudaStream_t st);
@@ -134,7 +148,8 @@ cudaError_t rt_launch_wait_flags(const uint32_t* d_flags, uint32_t stride_words,
                                  uint32_t* d_timeouts, cudaStream_t st);
 
 /* Extension X1 builds of the two launchers above (rt_kernels_tri.cu), used when the scene has triangles. */
-cudaError_t rt_launch_render_tri(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
+cudaError_t rt_launch_render_tri(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape,
+                                 const RtTreeLaunch* tree);
 cudaError_t rt_launch_tile_order_tri(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                      cudaStream_t st);
 /* Extension X1: rtriangle wire array -> {v0, v1-v0, v2-v0} records (3 float4 each). */

@@ -1,32 +1,34 @@
-/* rt_trace_tree.cuh -- level-wise pixel trees: one pixel's segments spread over the lanes of a warp.
+/* rt_trace_tree.cuh -- level-wise pixel trees: the segments of a heavy tile spread over the 128 lanes of a CTA.
  *
  * The stack machine of raytracing.cl:41-190 runs a pixel's segments one after the other; a glass pixel of render.map
- * has up to 166 of them at 3840x2160 and at ~7,500 clocks per step of the walk that chain (0.6 ms) was the floor of
- * every multi-GPU frame and of the single-GPU tail.  But the segments of a pixel form a binary tree -- a shaded
- * segment continues as the reflection of its own stack entry (:150-159) and, through glass, as a new entry for the
- * refracted ray (:161-179) -- whose geometry depends on neither the RNG nor the accumulated colour.  oracle/rt_split.c
- * (rto_tree_render, tree_rank_flat, tree_replay_flat) proves on the CPU that the following evaluation order gives the
- * stack machine's words; this file is that order on a warp:
+ * has up to 166 of them at 3840x2160, a glass tile 2,000-3,000, and a lone warp walks them at ~7,500 clocks per step:
+ * that chain (0.6 ms) was the floor of every multi-GPU frame and of the single-GPU tail.  But the segments of a pixel
+ * form a binary tree -- a shaded segment continues as the reflection of its own stack entry (:150-159) and, through
+ * glass, as a new entry for the refracted ray (:161-179) -- whose geometry depends on neither the RNG nor the
+ * accumulated colour.  oracle/rt_split.c (rto_tree_render, tree_rank_flat, tree_replay_flat) proves on the CPU that the
+ * following evaluation order gives the stack machine's words; this file is that order on one CTA (4 warps), for the
+ * pixels of up to four queue entries at a time (each a whole 8x4 tile, one of its rows, or a single pixel):
  *
  *   1 EXPAND  breadth-first.  The frontier is a queue of ray states {origin, direction, f, n, depth, stack height,
- *             pixel} in the warp's slab; each pass, lane j takes frontier node j: closest hit (one pass over lights,
+ *             pixel} in the CTA's slab; each pass, thread j takes frontier node j: closest hit (one pass over lights,
  *             spheres, planes), classification, material / texel, ambient term, Fresnel, and its <= 2 continuations
- *             appended at ballot-prefix positions.  All nodes of BFS level k have depth k, so there are <= 15 levels.
+ *             appended at prefix-sum positions (ballots per warp, warp totals through shared memory).  All nodes of
+ *             BFS level k have depth k, so there are <= 15 levels.
  *   2 RANK    per node, last level to first: shaded segments and addition-stream slots of its sub-tree; then first
  *             level to last: the pre-order rank among shaded nodes (refraction sub-tree first -- the stack machine's
- *             order) and the position of the node's additions in the pixel's stream.  A shaded segment draws exactly
+ *             order) and the position of the node's additions in its pixel's stream.  A shaded segment draws exactly
  *             4L random numbers (raytracing.cl:96-113 has no early exit), so its RNG state is
  *             xorshift32^(4L*rank)(pixel id): xorshift32 (primitives.cl:111-125) is linear over GF(2) and the state is
  *             a product of <= 15 precomputed 32x32 bit matrices (fp.jump, built per scene by the engine).
- *   3 SHADE   (shaded node, light) pairs dealt over the 32 lanes: shading geometry, the four draws, two shadow rays,
- *             the light's specular and diffuse terms -- written straight into the stream slots.
- *   4 REPLAY  each pixel's lane runs down its stream: ADD v / PUSH / POP on a <= 15-deep stack of partial sums --
- *             additions only, in exactly the order the stack machine performs them.
+ *   3 SHADE   (shaded node, light) pairs dealt over the 128 threads: shading geometry, the four draws, two shadow
+ *             rays, the light's specular and diffuse terms -- written straight into the stream slots.
+ *   4 REPLAY  one thread per pixel runs down the pixel's stream: ADD v / PUSH / POP on a <= 15-deep stack of partial
+ *             sums -- additions only, in exactly the order the stack machine performs them.
  *
  * Terms that the cooperative trace skips because they are exact zeros (R5) are stored as +0 and added: x + 0 == x for
  * every x but -0, and the sign of a zero cannot reach the packed word (clamp, *255, truncation).
- * A tree that outgrows the slab (fp.tree_cap nodes) makes the function return false; the caller then runs the entry
- * through trace_tile_coop -- same words, the old way.
+ * A tree that outgrows the slab (fp.tree_cap nodes) makes the function return false; the caller then hands the entry
+ * to the cooperative walk -- same words, the old way.
  */
 #pragma once
 #include "rt_trace_coop.cuh"
@@ -36,9 +38,31 @@ namespace RT_NS {
 enum : uint32_t { kNdLight = 0u, kNdSky = 1u, kNdShaded = 2u };
 enum : uint32_t { kOpAdd = 0u, kOpPush = 1u, kOpPop = 2u };
 constexpr uint32_t kTreePlanes = RT_TREE_PLANES; /* R0 R1 M S0 S1 S2 T X, 16 bytes per node each (rt_kernels.h) */
+constexpr uint32_t kWarps = kBlock / 32;
 
-/* One warp's slab: kTreePlanes planes of `cap` 16-byte records, cap shaded-list words, then the addition stream of
- * cap * (3 + 2L) 16-byte records.  SoA: lane j touching node base + j reads 512 contiguous bytes per plane. */
+/* One queue entry -> a lane's pixel.  entry = tile | sub << 24; sub 0: whole 8x4 tile; 1..4: only tile row sub-1;
+ * 5..36: only pixel sub-5 (the split entries of heavy tiles). */
+struct TileLanes {
+    uint32_t id;  /* global pixel id y*W + x (RNG seed, raytracing.cl:33) */
+    size_t at;    /* index into the compact band buffer */
+    bool live;    /* this lane owns a pixel of the frame (and of the entry) */
+};
+__device__ __forceinline__ TileLanes tile_lanes(const RtFrameParams& fp, uint32_t entry, uint32_t lane) {
+    const uint32_t tile = entry & 0x00ffffffu, sub = entry >> 24;
+    const uint32_t tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
+    const uint32_t x = tx * kTileW + (lane & 7u);
+    const uint32_t lr = ty * kTileH + (lane >> 3);
+    const uint32_t y = ((lr / fp.band_rows) * fp.parts + fp.part) * fp.band_rows + lr % fp.band_rows;
+    TileLanes t;
+    t.id = y * fp.W + x;
+    t.at = (size_t)lr * fp.W + x;
+    t.live = x < fp.W && lr < fp.local_rows && y < fp.H && t.id < fp.total &&
+             (sub == 0u || (sub <= 4u ? (lane >> 3) + 1u == sub : lane + 5u == sub));
+    return t;
+}
+
+/* One CTA's slab: kTreePlanes planes of `cap` 16-byte records, cap shaded-list words, then the addition stream of
+ * cap * (3 + 2L) 16-byte records.  SoA: thread j touching node base + j reads 512 contiguous bytes per warp and plane. */
 struct TreeSlab {
     float4* base;
     uint32_t cap;
@@ -54,6 +78,20 @@ struct TreeSlab {
     __device__ __forceinline__ uint32_t* shaded() const { return reinterpret_cast<uint32_t*>(plane(kTreePlanes)); }
     __device__ __forceinline__ float4* stream() const { return plane(kTreePlanes) + (cap + 3u) / 4u; }
 };
+
+/* The CTA's shared scratch for one entry. */
+constexpr uint32_t kTreeGroup = kWarps;         /* queue entries one CTA pools into one tree pass: warp w owns entry w */
+constexpr uint32_t kTreePixels = 32u * kTreeGroup;
+struct TreeShared {
+    uint32_t lvl[kMaxDepth + 2];   /* first node of every BFS level, then the node count */
+    uint32_t wcnt[kWarps][4];      /* per warp: refraction children, reflection children, shaded nodes of this pass */
+    uint32_t pix_base[kTreePixels], pix_size[kTreePixels]; /* per pixel (entry slot * 32 + tile pixel): its addition stream */
+    uint32_t word[kTreePixels], hid[kTreePixels];          /* per pixel: the results */
+    uint32_t entry[kTreeGroup];    /* the queue entries of this pass */
+    uint32_t shaded_of[kTreeGroup]; /* shaded segments per entry (cost attribution) */
+    uint32_t slot, count;          /* queue cursor broadcast */
+};
+
 /* xorshift32^(draws*k)(seed): jump[j*32 + i] = image of bit i under (step^draws)^(2^j).  The j loop is warp-uniform
  * (runs to the highest set bit of any lane's k), so every table read is one broadcast load. */
 __device__ __forceinline__ uint32_t rng_jump(const uint32_t* __restrict__ jump, uint32_t seed, uint32_t k, uint32_t kmax) {
@@ -66,39 +104,57 @@ __device__ __forceinline__ uint32_t rng_jump(const uint32_t* __restrict__ jump, 
     return seed;
 }
 
-/* Returns false (warp-uniformly) when the tree does not fit the slab; otherwise `word` (and hit_id) are this lane's. */
+/* All kBlock threads of the CTA call this; the pass covers the queue entries sh.entry[first .. first + ne) (tile | sub << 24;
+ * ne <= kTreeGroup: warp w makes the roots of entry first + w, and the pooled frontier fills the 128 lanes far better than
+ * one tile's would) and, when only_pixel < 32, just that pixel of each (tests).  Returns false (CTA-uniformly) when the
+ * tree does not fit the slab; otherwise sh.word[q] / sh.hid[q], q = w * 32 + tile pixel, hold the results. */
 template <bool AOV>
-__device__ __noinline__ bool trace_tile_tree(const RtFrameParams& fp, const Geo& g, const TreeSlab sl, uint32_t* lvl /* shared: >= 17 words per warp */,
-                                             uint32_t id, bool live, uint32_t lane, uint32_t& word, uint32_t& hit_id) {
+__device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const Geo& g, const TreeSlab sl, TreeShared& sh, uint32_t first,
+                                                 uint32_t ne, uint32_t only_pixel) {
     constexpr uint32_t kFull = 0xffffffffu;
     Tally<false> tl;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     const uint32_t L = g.L, cap = sl.cap;
     const uint32_t own_shaded = 1u + 2u * L;
 
-    /* ---- roots: one node per live pixel ---- */
-    const uint32_t live_mask = __ballot_sync(kFull, live);
-    const uint32_t nroots = (uint32_t)__popc(live_mask);
-    const uint32_t my_root = (uint32_t)__popc(live_mask & lt);
-    if (nroots == 0u) { word = 0; if (AOV) hit_id = 0; return true; }
-    if (live) {
-        V3 o, d;
-        primary_ray(fp, id, o, d);
-        sl.R0()[my_root] = make_float4(o.x, o.y, o.z, 1.0f);
-        sl.R1()[my_root] = make_float4(d.x, d.y, d.z, kAirN);
-        sl.M()[my_root] = make_uint4(0u | (1u << 8) | (lane << 16), 0xffffffffu, 0xffffffffu, 0u);
+    /* ---- roots: one node per live pixel; warp w makes those of entry first + w (lane p = tile pixel p) ---- */
+    uint32_t nroots = 0;
+    {
+        const uint32_t entry = warp < ne ? sh.entry[first + warp] : 0u;
+        const TileLanes tq = tile_lanes(fp, entry, lane);
+        const bool live = warp < ne && tq.live && (only_pixel >= 32u || lane == only_pixel);
+        const uint32_t live_mask = __ballot_sync(kFull, live);
+        if (lane == 0u) sh.wcnt[warp][0] = (uint32_t)__popc(live_mask);
+        __syncthreads();
+        uint32_t before = 0;
+#pragma unroll
+        for (uint32_t w = 0; w < kWarps; w++) {
+            const uint32_t a = sh.wcnt[w][0];
+            if (w < warp) before += a;
+            nroots += a;
+        }
+        if (live) {
+            const uint32_t r = before + (uint32_t)__popc(live_mask & lt);
+            V3 o, d;
+            primary_ray(fp, tq.id, o, d);
+            sl.R0()[r] = make_float4(o.x, o.y, o.z, 1.0f);
+            sl.R1()[r] = make_float4(d.x, d.y, d.z, kAirN);
+            sl.M()[r] = make_uint4(0u | (1u << 8) | ((warp * 32u + lane) << 16), 0xffffffffu, 0xffffffffu, 0u);
+        }
+        __syncthreads();
     }
-    __syncwarp();
+    if (nroots == 0u) return true;
 
     /* ---- 1 EXPAND ---- */
-    uint32_t n_nodes = nroots, n_shaded = 0, head = 0, nlev = 0, root_hid = 0;
+    uint32_t n_nodes = nroots, n_shaded = 0, head = 0, nlev = 0;
     while (head < n_nodes) {
         const uint32_t level_end = n_nodes;
-        if (lane == 0) lvl[nlev] = head;
+        if (tid == 0u) sh.lvl[nlev] = head;
         nlev++;
 #pragma unroll 1
-        for (uint32_t base = head; base < level_end; base += 32u) {
-            const uint32_t i = base + lane;
+        for (uint32_t base = head; base < level_end; base += kBlock) {
+            const uint32_t i = base + tid;
             const bool act = i < level_end;
             bool c_refr = false, c_refl = false, shaded = false;
             V3 ro = mk(0.0f, 0.0f, 0.0f), rd = ro, lo = ro, ld = ro; /* refraction / reflection continuations */
@@ -114,7 +170,7 @@ __device__ __noinline__ bool trace_tile_tree(const RtFrameParams& fp, const Geo&
                 ray_setup_fast(r, o, d);
                 Closest c;
                 closest_pass(r, g, tl, c);
-                uint32_t kind, entry = 0u, hid = 0u;
+                uint32_t kind, entry_child = 0u, hid = 0u;
                 V3 term;
                 if (c.k >= 0 && !c.occluded) { /* a visible light ends the chain, raytracing.cl:48-54 */
                     V3 lp = o + d * c.tL;
@@ -171,7 +227,7 @@ __device__ __noinline__ bool trace_tile_tree(const RtFrameParams& fp, const Geo&
                     const uint32_t depth1 = depth + 1u;
                     if (m.transperent && sz < (uint32_t)kMaxDepth && refl < 1.0f) {
                         if (refract_child(ip, nrm, d, n1, n2, ro, rd)) {
-                            entry = 1u; /* the entry is pushed (and popped) even when it has no segment left to run */
+                            entry_child = 1u; /* the entry is pushed (and popped) even when it has no segment left to run */
                             if (depth1 < (uint32_t)kMaxDepth) { c_refr = true; rf = f * (1.0f - refl); rn = n2; }
                         }
                     }
@@ -184,83 +240,107 @@ __device__ __noinline__ bool trace_tile_tree(const RtFrameParams& fp, const Geo&
                     }
                 }
                 sl.T()[i] = make_float4(term.x, term.y, term.z, 0.0f);
-                meta |= (kind << 24) | (entry << 28);
-                if (AOV && base == 0u) root_hid = hid; /* level 0: lane j expanded root j */
+                meta |= (kind << 24) | (entry_child << 28);
+                if (AOV && base == 0u) sh.hid[(meta >> 16) & 127u] = hid; /* level 0: the roots (nroots <= kBlock: one pass) */
             }
+            /* positions of the continuations: ballots inside the warp, warp totals through shared memory */
             const uint32_t m1 = __ballot_sync(kFull, c_refr), m2 = __ballot_sync(kFull, c_refl), ms = __ballot_sync(kFull, shaded);
-            const uint32_t total = (uint32_t)(__popc(m1) + __popc(m2));
-            if (n_nodes + total > cap) return false; /* warp-uniform */
+            if (lane == 0u) { sh.wcnt[warp][0] = (uint32_t)__popc(m1); sh.wcnt[warp][1] = (uint32_t)__popc(m2); sh.wcnt[warp][2] = (uint32_t)__popc(ms); }
+            __syncthreads();
+            uint32_t b1 = 0, b2 = 0, bs = 0, t1 = 0, t2 = 0, ts = 0;
+#pragma unroll
+            for (uint32_t w = 0; w < kWarps; w++) {
+                const uint32_t a = sh.wcnt[w][0], b = sh.wcnt[w][1], c = sh.wcnt[w][2];
+                if (w < warp) { b1 += a; b2 += b; bs += c; }
+                t1 += a; t2 += b; ts += c;
+            }
+            if (n_nodes + t1 + t2 > cap) return false; /* CTA-uniform */
             if (act) {
                 const uint32_t child_meta = ((meta & 0xffu) + 1u) | (meta & 0x00ffff00u);
                 uint32_t refr = 0xffffffffu, refl_i = 0xffffffffu;
                 if (c_refr) {
-                    refr = n_nodes + (uint32_t)__popc(m1 & lt);
+                    refr = n_nodes + b1 + (uint32_t)__popc(m1 & lt);
                     sl.R0()[refr] = make_float4(ro.x, ro.y, ro.z, rf);
                     sl.R1()[refr] = make_float4(rd.x, rd.y, rd.z, rn);
                     sl.M()[refr] = make_uint4((child_meta & 0xffff00ffu) | ((((meta >> 8) & 0xffu) + 1u) << 8), 0xffffffffu, 0xffffffffu, 0u);
                 }
                 if (c_refl) {
-                    refl_i = n_nodes + (uint32_t)__popc(m1) + (uint32_t)__popc(m2 & lt);
+                    refl_i = n_nodes + t1 + b2 + (uint32_t)__popc(m2 & lt);
                     sl.R0()[refl_i] = make_float4(lo.x, lo.y, lo.z, lf);
                     sl.R1()[refl_i] = make_float4(ld.x, ld.y, ld.z, ln);
                     sl.M()[refl_i] = make_uint4(child_meta, 0xffffffffu, 0xffffffffu, 0u);
                 }
                 sl.M()[i] = make_uint4(meta, refr, refl_i, 0u);
-                if (shaded) sl.shaded()[n_shaded + (uint32_t)__popc(ms & lt)] = i;
+                if (shaded) sl.shaded()[n_shaded + bs + (uint32_t)__popc(ms & lt)] = i;
             }
-            n_nodes += total;
-            n_shaded += (uint32_t)__popc(ms);
-            __syncwarp();
+            n_nodes += t1 + t2;
+            n_shaded += ts;
+            __syncthreads(); /* the children are visible to whoever expands them; wcnt may be rewritten */
         }
         head = level_end;
     }
-    if (lane == 0) lvl[nlev] = n_nodes;
-    __syncwarp();
-    if (AOV) hit_id = __shfl_sync(kFull, root_hid, my_root & 31u);
+    if (tid == 0u) sh.lvl[nlev] = n_nodes;
+    __syncthreads();
 
     /* ---- 2 RANK: sub-tree totals, last level first ---- */
     for (uint32_t lv = nlev; lv-- > 0u;) {
-        const uint32_t b = lvl[lv], e = lvl[lv + 1u];
-        for (uint32_t i = b + lane; i < e; i += 32u) {
+        const uint32_t b = sh.lvl[lv], e = sh.lvl[lv + 1u];
+        for (uint32_t i = b + tid; i < e; i += kBlock) {
             const uint4 mm = sl.M()[i];
-            const bool sh = ((mm.x >> 24) & 0xfu) == kNdShaded;
-            uint32_t cnt = sh ? 1u : 0u;
-            uint32_t size = (sh ? own_shaded : 1u) + (((mm.x >> 28) & 1u) ? 2u : 0u);
+            const bool shd = ((mm.x >> 24) & 0xfu) == kNdShaded;
+            uint32_t cnt = shd ? 1u : 0u;
+            uint32_t size = (shd ? own_shaded : 1u) + (((mm.x >> 28) & 1u) ? 2u : 0u);
             if (mm.y != 0xffffffffu) { const uint4 x = sl.X()[mm.y]; cnt += x.x; size += x.y; }
             if (mm.z != 0xffffffffu) { const uint4 x = sl.X()[mm.z]; cnt += x.x; size += x.y; }
             sl.X()[i] = make_uint4(cnt, size, 0u, 0u);
         }
-        __syncwarp();
+        __syncthreads();
     }
-    /* stream base of every pixel: exclusive scan of the roots' sizes (roots are nodes 0 .. nroots-1) */
-    uint32_t my_size = lane < nroots ? sl.X()[lane].y : 0u;
-    uint32_t scan = my_size;
-    for (int off = 1; off < 32; off <<= 1) {
-        const uint32_t v = __shfl_up_sync(kFull, scan, off);
-        if ((int)lane >= off) scan += v;
+    /* stream base of every pixel: exclusive scan of the roots' sizes (roots are nodes 0 .. nroots-1, nroots <= kBlock);
+     * shaded segments per entry for the cost attribution */
+    {
+        const uint4 rx = tid < nroots ? sl.X()[tid] : make_uint4(0u, 0u, 0u, 0u);
+        const uint32_t my_size = rx.y;
+        uint32_t scan = my_size;
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t v = __shfl_up_sync(kFull, scan, off);
+            if ((int)lane >= off) scan += v;
+        }
+        if (lane == 31u) sh.wcnt[warp][0] = scan;
+        if (tid < kTreeGroup) sh.shaded_of[tid] = 0u;
+        __syncthreads();
+        uint32_t before = 0;
+#pragma unroll
+        for (uint32_t w = 0; w < kWarps; w++) if (w < warp) before += sh.wcnt[w][0];
+        if (tid < nroots) {
+            uint4 x = rx;
+            x.z = 0u; x.w = before + scan - my_size;
+            sl.X()[tid] = x;
+            const uint32_t pix = (sl.M()[tid].x >> 16) & 127u;
+            sh.pix_base[pix] = x.w;
+            sh.pix_size[pix] = my_size;
+            atomicAdd(&sh.shaded_of[pix >> 5], rx.x);
+        }
     }
-    if (lane < nroots) { uint4 x = sl.X()[lane]; x.z = 0u; x.w = scan - my_size; sl.X()[lane] = x; }
-    const uint32_t pix_base = __shfl_sync(kFull, scan - my_size, my_root & 31u);
-    const uint32_t pix_size = __shfl_sync(kFull, my_size, my_root & 31u);
-    __syncwarp();
+    __syncthreads();
     /* ranks and stream positions, first level first; the node's own first addition and the PUSH / POP marks */
     float4* const stream = sl.stream();
     for (uint32_t lv = 0; lv < nlev; lv++) {
-        const uint32_t b = lvl[lv], e = lvl[lv + 1u];
-        for (uint32_t i0 = b; i0 < e; i0 += 32u) {
-            const uint32_t i = i0 + lane;
+        const uint32_t b = sh.lvl[lv], e = sh.lvl[lv + 1u];
+        for (uint32_t i0 = b; i0 < e; i0 += kBlock) { /* whole warps run the loop: rng_jump's table walk is warp-uniform */
+            const uint32_t i = i0 + tid;
             const bool act = i < e;
-            uint32_t rank = 0, pixlane = 0;
-            bool sh = false;
+            uint32_t rank = 0, seed = 0;
+            bool shd = false;
             if (act) {
                 const uint4 mm = sl.M()[i];
                 const uint4 x = sl.X()[i];
                 rank = x.z;
                 const uint32_t pos = x.w;
-                sh = ((mm.x >> 24) & 0xfu) == kNdShaded;
+                shd = ((mm.x >> 24) & 0xfu) == kNdShaded;
                 const float4 t = sl.T()[i];
                 stream[pos] = make_float4(t.x, t.y, t.z, __uint_as_float(kOpAdd));
-                if (sh) {
+                if (shd) {
                     uint32_t p = pos + own_shaded;
                     uint32_t crank = rank + 1u;
                     if ((mm.x >> 28) & 1u) {
@@ -282,23 +362,23 @@ __device__ __noinline__ bool trace_tile_tree(const RtFrameParams& fp, const Geo&
                         cx.z = crank; cx.w = p;
                         sl.X()[mm.z] = cx;
                     }
-                    pixlane = (mm.x >> 16) & 31u;
+                    /* the pixel's global id y*W + x seeds its generator (raytracing.cl:33) */
+                    { const uint32_t pix = (mm.x >> 16) & 127u; seed = tile_lanes(fp, sh.entry[first + (pix >> 5)], pix & 31u).id; }
                 }
             }
-            /* RNG state on entry to the segment: xorshift32^(4L*rank)(pixel id); the pixel id (global: y*W + x,
-             * raytracing.cl:33) lives in the lane that owns that pixel of the tile */
-            const uint32_t seed = __shfl_sync(kFull, id, pixlane);
-            const uint32_t kmax = __reduce_max_sync(kFull, (act && sh) ? rank : 0u);
-            const uint32_t state = rng_jump(fp.jump, seed, (act && sh) ? rank : 0u, kmax);
-            if (act && sh) { uint4 x = sl.X()[i]; x.z = state; sl.X()[i] = x; }
+            /* RNG state on entry to the segment: xorshift32^(4L*rank)(pixel id) */
+            const uint32_t k = (act && shd) ? rank : 0u;
+            const uint32_t kmax = __reduce_max_sync(kFull, k);
+            const uint32_t state = rng_jump(fp.jump, seed, k, kmax);
+            if (act && shd) { uint4 x = sl.X()[i]; x.z = state; sl.X()[i] = x; }
         }
-        __syncwarp();
+        __syncthreads();
     }
 
-    /* ---- 3 SHADE: (shaded node, light) pairs over the lanes ---- */
+    /* ---- 3 SHADE: (shaded node, light) pairs over the threads ---- */
     const uint32_t items = n_shaded * L;
 #pragma unroll 1
-    for (uint32_t it = lane; it < items; it += 32u) {
+    for (uint32_t it = tid; it < items; it += kBlock) {
         const uint32_t k = it / L, li = it - k * L;
         const uint32_t node = sl.shaded()[k];
         const float4 s0 = sl.S0()[node], s1 = sl.S1()[node], s2 = sl.S2()[node];
@@ -345,25 +425,29 @@ __device__ __noinline__ bool trace_tile_tree(const RtFrameParams& fp, const Geo&
         slot[0] = make_float4(spec.x, spec.y, spec.z, __uint_as_float(kOpAdd));
         slot[1] = make_float4(diffv.x, diffv.y, diffv.z, __uint_as_float(kOpAdd));
     }
-    __syncwarp();
+    __syncthreads();
 
-    /* ---- 4 REPLAY: additions in the stack machine's order ---- */
-    V3 acc = mk(0.0f, 0.0f, 0.0f);
-    if (live) {
-        V3 stk[kMaxDepth];
-        uint32_t sp = 0;
-        const float4* ev = stream + pix_base;
+    /* ---- 4 REPLAY: additions in the stack machine's order; thread q replays pixel q = entry slot * 32 + tile pixel ---- */
+    if (warp < ne) {
+        const TileLanes tq = tile_lanes(fp, sh.entry[first + warp], lane);
+        if (tq.live && (only_pixel >= 32u || lane == only_pixel)) {
+            V3 acc = mk(0.0f, 0.0f, 0.0f);
+            V3 stk[kMaxDepth];
+            uint32_t sp = 0;
+            const float4* ev = stream + sh.pix_base[tid];
+            const uint32_t n = sh.pix_size[tid];
 #pragma unroll 4
-        for (uint32_t q = 0; q < pix_size; q++) {
-            const float4 r = ev[q];
-            const uint32_t op = __float_as_uint(r.w);
-            if (op == kOpAdd) acc = acc + xyz(r);
-            else if (op == kOpPush) { stk[sp++] = acc; acc = mk(0.0f, 0.0f, 0.0f); }
-            else { sp--; acc = stk[sp] + acc; }
+            for (uint32_t q = 0; q < n; q++) {
+                const float4 r = ev[q];
+                const uint32_t op = __float_as_uint(r.w);
+                if (op == kOpAdd) acc = acc + xyz(r);
+                else if (op == kOpPush) { stk[sp++] = acc; acc = mk(0.0f, 0.0f, 0.0f); }
+                else { sp--; acc = stk[sp] + acc; }
+            }
+            sh.word[tid] = pack_rgb(acc);
         }
     }
-    word = pack_rgb(acc);
-    __syncwarp();
+    __syncthreads();
     return true;
 }
 

@@ -120,10 +120,11 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * negative = never) run the WIDE variant of the production trace: rounds with few tracing lanes walk the records one
  * ray at a time over all 32 lanes.  "wide_max_live": -1 (default) = those are the rounds below the instruction
  * break-even; 0..32 = fixed limit (32 = every round, used by the tests).  Pixels do not change.
- * "tree": level-wise pixel trees (csrc/rt_trace_tree.cuh: one pixel's segment tree expanded breadth-first over the
- * 32 lanes, RNG jump-ahead, ordered replay).  1 (default) = the split queue entries of heavy tiles (rows of 8 pixels and
- * single pixels); 0 = never; 2 = every tile; 3 = every tile, one pixel at a time (what a single-pixel entry does; tests).
- * "tree_cap": nodes per warp slab (default 2048; a larger tree falls back to the cooperative walk).  Pixels do not
+ * "tree": level-wise pixel trees (csrc/rt_trace_tree.cuh: the segment trees of an entry's pixels expanded breadth-first
+ * over the 128 threads of a CTA, RNG jump-ahead, ordered replay).  1 (default) = the heavy queue entries of
+ * history-scheduled frames: tiles whose cost reaches "tree_min_cost" (0 = automatic) and every split entry; 0 = never;
+ * 2 = every tile; 3 = every tile, one pixel at a time (what a single-pixel entry does; tests).
+ * "tree_cap": nodes per CTA slab (default 8192; a larger tree falls back to the cooperative walk).  Pixels do not
  * change. */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
 /* Brute-force check of the arithmetic routines against IEEE division / sqrt (trials per thread on 592x256
@@ -198,6 +199,7 @@ void rtb_map_free(rtb_map* m);
 /* Launch geometry the renderer chose for the last frame (for bench.py's accounting). */
 typedef struct {
     uint32_t grid, block, smem_bytes, tiles, resident_scene; /* resident_scene: 1 = geometry staged in shared memory */
+    uint32_t tree_grid; /* CTAs of the render_tree kernel launched beside render_frame (0 = none) */
 } rtb_launch_info;
 int rtb_last_launch(rtb_engine* e, rtb_launch_info* info);
 
