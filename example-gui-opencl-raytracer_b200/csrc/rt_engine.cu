@@ -78,6 +78,7 @@ struct rtb_engine {
     DevBuf jump;              /* [15][32] xorshift32 jump-ahead matrices for this scene's light count */
     uint32_t jump_L = 0xffffffffu;
     int opt_tree = 1, opt_tree_cap = 8192, opt_tree_min_cost = 0 /* 0 = automatic */, opt_tree_group_max_cost = 0;
+    bool cost_hist_valid = false; /* tile_cost holds measured-time costs of a frame with this geometry */
     cudaStream_t aux = nullptr;   /* render_tree runs here, beside render_frame */
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
@@ -394,20 +395,14 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
         const bool same = e->time_valid && e->tk_W == W && e->tk_H == H && e->tk_total == total && e->tk_band == pp.band_rows &&
                           e->tk_parts == pp.parts && e->tk_part == pp.part && e->tk_scene_gen == e->scene_gen + e->T;
         if (e->opt_history && mode == 0) {
-            /* each buffer: 8 bytes for the frame's time sum, 8 for its segment sum, one time word per tile, one segment word per tile */
-            if (e->tile_time[0].ensure(nt * 8 + 16) || e->tile_time[1].ensure(nt * 8 + 16)) return -2;
-            char* cur = (char*)e->tile_time[e->time_cur].p;
-            const char* prv = (const char*)e->tile_time[1 - e->time_cur].p;
-            fp.tile_time_sum = (unsigned long long*)cur;
-            fp.tile_seg_sum = (unsigned long long*)(cur + 8);
-            fp.tile_time = (uint32_t*)(cur + 16);
-            fp.tile_seg = (uint32_t*)(cur + 16 + nt * 4);
-            CU(cudaMemsetAsync(cur, 0, nt * 8 + 16, e->stream), "reset tile times");
+            /* each buffer: 16 bytes for the frame's sum, then one word per tile */
+            if (e->tile_time[0].ensure(nt * 4 + 16) || e->tile_time[1].ensure(nt * 4 + 16)) return -2;
+            fp.tile_time_sum = (unsigned long long*)e->tile_time[e->time_cur].p;
+            fp.tile_time = (uint32_t*)((char*)e->tile_time[e->time_cur].p + 16);
+            CU(cudaMemsetAsync(e->tile_time[e->time_cur].p, 0, nt * 4 + 16, e->stream), "reset tile times");
             if (same) {
-                fp.tile_time_sum_prev = (const unsigned long long*)prv;
-                fp.tile_seg_sum_prev = (const unsigned long long*)(prv + 8);
-                fp.tile_time_prev = (const uint32_t*)(prv + 16);
-                fp.tile_seg_prev = (const uint32_t*)(prv + 16 + nt * 4);
+                fp.tile_time_sum_prev = (const unsigned long long*)e->tile_time[1 - e->time_cur].p;
+                fp.tile_time_prev = (const uint32_t*)((const char*)e->tile_time[1 - e->time_cur].p + 16);
                 /* measured costs: a tile is a tail risk when its time is comparable to the time the whole queue needs,
                  * T = mean * tiles / resident warps.  Automatic thresholds (they reproduce the optima of the sweeps in
                  * tools/exp/sweep_split.py at N = 1, 2, 4, 8): four warps from 0.75 T, one pixel per warp from 3 T.
@@ -430,18 +425,21 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                         if (fp.split32_min_cost < t) t = fp.split32_min_cost;
                         fp.tree_min_cost = t;
                         fp.tree_group_max_cost = e->opt_tree_group_max_cost > 0 ? (uint32_t)e->opt_tree_group_max_cost : t + 8u;
+                        fp.cost_is_history = e->cost_hist_valid ? 1u : 0u;
                     } else {
                         fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(0.75, 40.0);
                         fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : thr(3.0, 48.0);
                     }
                 }
             }
+            e->cost_hist_valid = same; /* this frame's costs come from measured times: the next one may lean on them */
             e->time_cur = 1 - e->time_cur;
             e->time_valid = true;
             e->tk_W = W; e->tk_H = H; e->tk_total = total; e->tk_band = pp.band_rows; e->tk_parts = pp.parts; e->tk_part = pp.part;
             e->tk_scene_gen = e->scene_gen + e->T;
         } else if (mode == 0) {
             e->time_valid = false;
+            e->cost_hist_valid = false;
         } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
         CU((e->T ? rt_launch_tile_order_tri : rt_launch_tile_order)(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),

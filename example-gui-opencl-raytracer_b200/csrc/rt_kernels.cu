@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__
     const uint32_t ntiles = fp.order ? __ldg(fp.queue_len) : fp.tiles_x * fp.tiles_y;
     const uint32_t n_tree = fp.tree_mode >= 2u ? ntiles : (fp.order ? __ldg(fp.n_split) : 0u);
     const TreeSlab sl = {fp.tree_slab + (size_t)blockIdx.x * fp.tree_records, fp.tree_cap};
-    unsigned long long warp_time = 0, warp_seg = 0;
+    unsigned long long warp_time = 0;
     const uint32_t warp = threadIdx.x >> 5;
     for (;;) {
         /* the heaviest entries one at a time (their chains bound the frame); the lighter ones four to a pass: a lone
@@ -194,12 +194,13 @@ __global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__
             if (warp < span) { /* warp w stores entry first + w, lane p = tile pixel p */
                 const uint32_t entry = tsh.entry[first + warp];
                 const TileLanes tq = tile_lanes(fp, entry, lane);
-                uint32_t word = 0, hid = 0, nseg_fallback = 0;
+                uint32_t word = 0, hid = 0;
                 if (traced) {
                     if (tq.live) { word = tsh.word[threadIdx.x]; hid = tsh.hid[threadIdx.x]; }
                 } else { /* span == 1, warp 0: the tree did not fit the slab */
                     Tally<false> tl;
-                    word = trace_tile_coop<false, AOV, false>(fp, g, cs, tq.id, tq.live, lane, hid, nseg_fallback, tl);
+                    uint32_t nseg = 0;
+                    word = trace_tile_coop<false, AOV, false>(fp, g, cs, tq.id, tq.live, lane, hid, nseg, tl);
                     __syncwarp();
                 }
                 if (fp.tile_time && lane == 0) {
@@ -213,8 +214,6 @@ __global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__
                     dt += 1u;
                     atomicAdd(fp.tile_time + (entry & 0x00ffffffu), dt);
                     warp_time += dt;
-                    const uint32_t segs = traced ? tsh.shaded_of[warp] : nseg_fallback;
-                    if (segs) { atomicAdd(fp.tile_seg + (entry & 0x00ffffffu), segs); warp_seg += segs; }
                 }
                 store_tile<AOV>(fp, tq, entry >> 24, lane, word, hid);
             }
@@ -222,7 +221,7 @@ __global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__
             __syncthreads(); /* tsh.word / shaded_of are read above and rewritten by the next pass */
         }
     }
-    if (fp.tile_time && lane == 0 && warp_time) { atomicAdd(fp.tile_time_sum, warp_time); atomicAdd(fp.tile_seg_sum, warp_seg); }
+    if (fp.tile_time && lane == 0 && warp_time) atomicAdd(fp.tile_time_sum, warp_time);
     signal_done(fp);
 }
 
@@ -257,7 +256,6 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
 
     unsigned long long warp_time = 0; /* sum of this warp's tile times: the frame total gives the mean the next frame's costs are relative to */
 
-    unsigned long long warp_seg = 0;
     /* The first n_tree entries of the cost-ordered queue (tiles at or above fp.tree_min_cost and the split entries of the
      * heaviest ones) belong to the render_tree kernel, which runs beside this one on a second stream. */
     const uint32_t n_tree = (RT_TREE && TREE && fp.tree_mode) ? (fp.tree_mode >= 2u ? ntiles : (fp.order ? __ldg(fp.n_split) : 0u)) : 0u;
@@ -300,7 +298,6 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
             const uint32_t dt = (uint32_t)((clock64() - tile_clk0) >> 10) + 1u;
             atomicAdd(fp.tile_time + tile, dt);
             warp_time += dt;
-            if (nseg) { atomicAdd(fp.tile_seg + tile, nseg); warp_seg += nseg; }
         }
 #ifdef RT_TILE_TIMING
         {
@@ -354,7 +351,7 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
         }
     }
 
-    if (fp.tile_time && lane == 0 && warp_time) { atomicAdd(fp.tile_time_sum, warp_time); atomicAdd(fp.tile_seg_sum, warp_seg); }
+    if (fp.tile_time && lane == 0 && warp_time) atomicAdd(fp.tile_time_sum, warp_time);
 
     if (COUNT) {
 #pragma unroll
@@ -513,10 +510,9 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
  * cost = 24 + 4*log2(t / mean), so the mean tile sits at 24, 16x the mean at 40, 64x at 48 -- whatever the scene's
  * absolute speed (render.map: mean 29 us; the 1,024-sphere grid: 4.5 ms).  Replaces the skeleton trace whenever a frame of the same geometry has just been rendered. ---- */
 __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsigned long long* __restrict__ prev_sum,
-                                  const uint32_t* __restrict__ prev_seg, const unsigned long long* __restrict__ prev_seg_sum,
                                   uint32_t* __restrict__ cost_out,
                                   uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost, uint32_t split32_min_cost,
-                                  uint32_t tree_min_cost) {
+                                  uint32_t sticky_cost) {
     __shared__ uint32_t shist[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
     __syncthreads();
@@ -526,19 +522,10 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsig
         const float rel = 24.0f + 4.0f * __log2f(fmaxf((float)prev[tile], 0.5f) / mean);
         uint32_t c = rel <= 0.0f ? 0u : (uint32_t)rel;
         c = c < kCostBuckets ? c : kCostBuckets - 1u;
-        /* Which tiles the pixel-tree kernel takes (cost >= tree_min_cost: the head of the queue) is decided by the tile's
-         * SHADED SEGMENTS on the same relative scale, 24 + 4*log2(segments / mean segments): the same number whichever
-         * kernel rendered the tile last frame.  (Deciding by measured time made tiles whose tree pass is cheaper than
-         * their cooperative walk change sides every frame: 0.49 / 0.85 ms alternating at N = 8.)  Heavy tiles are ordered,
-         * pooled or split by that weight; the others keep their time cost, capped below the threshold. */
-        if (tree_min_cost < kCostBuckets) {
-            const float mean_seg = fmaxf((float)(*prev_seg_sum) / (float)ntiles, 1.0f);
-            const float rs = 24.0f + 4.0f * __log2f(fmaxf((float)prev_seg[tile], 0.5f) / mean_seg);
-            uint32_t cs = rs <= 0.0f ? 0u : (uint32_t)rs;
-            cs = cs < kCostBuckets ? cs : kCostBuckets - 1u;
-            if (cs >= tree_min_cost) c = cs;
-            else if (c >= tree_min_cost) c = tree_min_cost - 1u;
-        }
+        /* hysteresis: a tile that the pixel-tree kernel took last frame (cost_out still holds that frame's costs) stays
+         * with it until its measured time has dropped two octaves below the threshold -- a tile whose tree pass is
+         * cheaper than its cooperative walk would otherwise change sides every frame (N = 4: 0.74 / 1.12 ms alternating) */
+        if (sticky_cost < kCostBuckets && c < sticky_cost && c + 8u >= sticky_cost && cost_out[tile] >= sticky_cost) c = sticky_cost;
         cost_out[tile] = c;
         atomicAdd(&shist[c], split_ways(c, split_min_cost, split32_min_cost));
     }
@@ -788,8 +775,8 @@ cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d
     cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, (2 * kCostBuckets + 2) * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
     const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
-    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, fp.tile_seg_prev, fp.tile_seg_sum_prev,
-                                                                                  d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost, fp.tree_min_cost);
+    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost,
+                                                                                  fp.cost_is_history ? fp.tree_min_cost : kCostBuckets);
     else tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;

@@ -81,17 +81,11 @@ struct RtFrameParams {
     unsigned long long* tile_time_sum;            /* sum of tile_time over the frame (zeroed before launch) */
     const unsigned long long* tile_time_sum_prev; /* the previous frame's */
     const uint32_t* tile_time_prev; /* the previous frame's, used as next cost estimate instead of the skeleton trace, or NULL */
-    /* shaded segments per tile, this frame's (zeroed before launch) and the previous frame's, with their frame sums: the
-     * weight that decides which tiles the pixel-tree kernel takes.  Unlike the measured time it does not depend on which
-     * kernel rendered the tile, so a tile cannot change sides from frame to frame. */
-    uint32_t* tile_seg;
-    unsigned long long* tile_seg_sum;
-    const uint32_t* tile_seg_prev;
-    const unsigned long long* tile_seg_sum_prev;
     const uint32_t* queue_len;  /* number of queue entries when `order` is set (tiles + 3 per split tile) */
     const uint32_t* n_split;    /* ... of which the first *n_split are heavy (cost >= tree_min_cost): the render_tree kernel's share */
     uint32_t tree_min_cost;     /* 64 = none */
     uint32_t tree_group_max_cost; /* heavy entries below this cost are pooled four to a CTA pass; from it on they run alone */
+    uint32_t cost_is_history;   /* the cost buffer still holds the previous frame's measured-time costs (hysteresis) */
     unsigned int* tree_counter; /* zeroed before launch: render_tree's queue cursor */
 
     uint32_t split32_min_cost;  /* ... into 32 single-pixel entries (64 = never) */

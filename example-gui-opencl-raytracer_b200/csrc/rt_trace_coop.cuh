@@ -236,6 +236,7 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
         Closest c;
         if (!done) {
             tl.add(RTB_SEGMENTS);
+            nseg++;
             ray_setup_fast(r, o, d);
             if (!WIDE) closest_pass(r, g, tl, c);
         }
@@ -290,9 +291,7 @@ __device__ __forceinline__ uint32_t trace_tile_coop(const RtFrameParams& fp, con
         }
 
         /* ---- direct light, raytracing.cl:87-136, in chunks of kCoopLights lights (L is warp-uniform) ---- */
-        const uint32_t shade_mask = __ballot_sync(kFull, shade);
-        nseg += (uint32_t)__popc(shade_mask); /* shaded segments of the entry: the mode-independent weight of a tile (render_tree counts the same) */
-        if (shade_mask) {
+        if (__any_sync(kFull, shade)) {
             const float shin = (float)m.shininess;
             const float fs = f * m.specular, fd = f * m.diffuse;
             if (shade) {
