@@ -77,10 +77,9 @@ struct rtb_engine {
     DevBuf tree_slab;         /* per-warp node storage of the level-wise pixel-tree trace (rt_trace_tree.cuh) */
     DevBuf jump;              /* [15][32] xorshift32 jump-ahead matrices for this scene's light count */
     uint32_t jump_L = 0xffffffffu;
+    int opt_tree_ctas_per_sm = 3;
     int opt_tree = 1, opt_tree_cap = 8192, opt_tree_min_cost = 0 /* 0 = automatic */, opt_tree_group_max_cost = 0;
     bool cost_hist_valid = false; /* tile_cost holds measured-time costs of a frame with this geometry */
-    cudaStream_t aux = nullptr;   /* render_tree runs here, beside render_frame */
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
     int time_cur = 0;
     bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
@@ -113,9 +112,6 @@ void rtb_destroy(rtb_engine* e) {
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
     e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
     e->tree_slab.release(); e->wait_word.release(); e->jump.release();
-    if (e->ev_fork) cudaEventDestroy(e->ev_fork);
-    if (e->ev_join) cudaEventDestroy(e->ev_join);
-    if (e->aux) { cudaStreamSynchronize(e->aux); cudaStreamDestroy(e->aux); }
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->evk) cudaEventDestroy(e->evk);
@@ -128,13 +124,6 @@ static int create_impl(rtb_engine* e) {
     CU(cudaEventCreate(&e->ev0), "cudaEventCreate");
     CU(cudaEventCreate(&e->ev1), "cudaEventCreate");
     CU(cudaEventCreate(&e->evk), "cudaEventCreate");
-    {
-        int lo = 0, hi = 0; /* numerically lower = higher priority */
-        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi), "cudaDeviceGetStreamPriorityRange");
-        CU(cudaStreamCreateWithPriority(&e->aux, cudaStreamNonBlocking, hi), "cudaStreamCreateWithPriority");
-        CU(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming), "cudaEventCreate");
-        CU(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming), "cudaEventCreate");
-    }
     if (e->sched.ensure(256)) return -2;
     CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "cudaMemsetAsync");
     CU(cudaStreamSynchronize(e->stream), "cudaStreamSynchronize");
@@ -413,7 +402,10 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                         double c = 24.0 + 4.0 * log2(alpha * per_warp) + 0.5;
                         return (uint32_t)(c < floor_cost ? floor_cost : (c > 64.0 ? 64.0 : c));
                     };
-                    const bool tree = e->opt_tree > 0 && e->L <= 16u;
+                    /* the pixel-tree kernel: not for many-sphere scenes (the WIDE variant's territory: a tree node walks all
+                     * records on ONE lane; measured 50 -> 115 ms per N = 8 part on the 1,024-sphere grid) */
+                    const bool wide_scene = e->T == 0u && e->lay.Lpad + e->lay.Spad >= (uint32_t)e->opt_wide_min_records;
+                    const bool tree = e->opt_tree > 0 && e->L <= 16u && (!wide_scene || e->opt_tree >= 2);
                     if (tree) {
                         /* with the CTA-wide pixel-tree kernel beside render_frame (tools/exp/sweep_tree.py): tiles longer than
                          * 0.75 T go to it whole (4 warps on the tile's pooled segment trees), tiles longer than 3 T as four
@@ -424,7 +416,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                         if (fp.split_min_cost < t) t = fp.split_min_cost;
                         if (fp.split32_min_cost < t) t = fp.split32_min_cost;
                         fp.tree_min_cost = t;
-                        fp.tree_group_max_cost = e->opt_tree_group_max_cost > 0 ? (uint32_t)e->opt_tree_group_max_cost : t + 8u;
+                        fp.tree_group_max_cost = e->opt_tree_group_max_cost > 0 ? (uint32_t)e->opt_tree_group_max_cost : 0u; /* pooling four entries per pass lengthens the chains it is there to shorten (tools/exp/sweep_tree.py): off unless asked for */
                         fp.cost_is_history = e->cost_hist_valid ? 1u : 0u;
                     } else {
                         fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(0.75, 40.0);
@@ -454,7 +446,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.tree_mode = 0;
     if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && ((fp.order && fp.tree_min_cost < 64u) || e->opt_tree >= 2)) {
         const uint32_t cap = (uint32_t)e->opt_tree_cap;
-        const uint32_t slots = (uint32_t)e->sm_count * 3u; /* = the render_tree grid: one slab per CTA */
+        const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->opt_tree_ctas_per_sm; /* = the render_tree grid: one slab per CTA */
         const size_t records = rt_tree_slab_records(cap, e->L);
         if (e->tree_slab.ensure(records * 16 * slots) == 0) {
             fp.tree_slab = (float4*)e->tree_slab.p;
@@ -469,8 +461,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
-    const RtTreeLaunch tree = {e->aux, e->ev_fork, e->ev_join};
-    CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, mode, e->sm_count, e->stream, &shape, fp.tree_mode ? &tree : nullptr), "render_frame launch");
+    CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
     CU(cudaEventRecord(e->ev1, e->stream), "event record");
     e->timed = true;
     e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;
@@ -518,6 +509,7 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!strcmp(name, "wide_max_live")) { e->opt_wide_max_live = value > 32 ? 32 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     if (!strcmp(name, "tree")) { e->opt_tree = value < 0 ? 0 : (value > 3 ? 3 : value); return 0; }
+    if (!strcmp(name, "tree_ctas_per_sm")) { e->opt_tree_ctas_per_sm = value < 1 ? 1 : (value > 8 ? 8 : value); e->tree_slab.release(); return 0; }
     if (!strcmp(name, "tree_group_max_cost")) { e->opt_tree_group_max_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tree_min_cost")) { e->opt_tree_min_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tree_cap")) { e->opt_tree_cap = value < 64 ? 64 : (value > 32768 ? 32768 : value); e->tree_slab.release(); return 0; }
@@ -686,6 +678,13 @@ int rtb_host_unregister(void* host) {
     return 0;
 }
 
+int rtb_debug_counters(rtb_engine* e, uint64_t out[RTB_NCOUNTERS]) {
+    if (!e || !out) return fail(-1, "rtb_debug_counters: null argument");
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    CU(cudaMemcpyAsync(out, (char*)e->sched.p + 64, RTB_NCOUNTERS * 8, cudaMemcpyDeviceToHost, e->stream), "D2H counters");
+    CU(cudaStreamSynchronize(e->stream), "rtb_debug_counters");
+    return 0;
+}
 int rtb_last_launch(rtb_engine* e, rtb_launch_info* info) {
     if (!e || !info) return fail(-1, "null argument");
     *info = e->last;

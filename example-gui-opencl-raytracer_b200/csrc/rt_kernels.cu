@@ -133,14 +133,21 @@ __device__ __forceinline__ void stage_geometry(const RtFrameParams& fp, uint64_t
 }
 
 /* ---- render_tree: the heavy entries of the queue as level-wise pixel trees, one CTA per entry at a time
- * (rt_trace_tree.cuh).  A kernel of its own, launched on a second stream just before render_frame: sharing a kernel
- * cost render_frame's main loop 8 % (2.65 -> 2.87 ms per 4K frame) even with the phase switched off.  An entry whose
+ * (rt_trace_tree.cuh).  A kernel of its own, launched just before render_frame in the same stream: sharing a kernel cost
+ * render_frame's main loop 8 % (2.65 -> 2.87 ms per 4K frame) even with the phase switched off, and more than that as
+ * an out-of-line call (1.1 KB of spills).  An entry whose
  * tree outgrows the slab is walked by warp 0 with the cooperative trace -- same words. ---- */
 template <bool RESIDENT, bool AOV>
 __global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__ RtFrameParams fp) {
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
     __shared__ TreeShared tsh;
+    /* Programmatic dependent launch: render_frame follows in the same stream and may start as soon as every CTA of this
+     * grid has got here, i.e. IS RESIDENT -- the heaviest entries of the frame hold their SM slots first, and
+     * render_frame's persistent CTAs fill what is left and, later, what these CTAs vacate.  (On a second stream the two
+     * kernels raced for the slots: when render_frame won, the heavy entries waited for it to drain -- frames alternating
+     * 0.57 / 0.87 ms at N = 8.) */
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     Geo g;
     stage_geometry<RESIDENT>(fp, &bar, lut255, g);
     const uint32_t lane = threadIdx.x & 31u;
@@ -257,7 +264,7 @@ __global__ void __launch_bounds__(kBlock, MODE == 4 ? RT_WIDE_BLOCKS : RT_MIN_BL
     unsigned long long warp_time = 0; /* sum of this warp's tile times: the frame total gives the mean the next frame's costs are relative to */
 
     /* The first n_tree entries of the cost-ordered queue (tiles at or above fp.tree_min_cost and the split entries of the
-     * heaviest ones) belong to the render_tree kernel, which runs beside this one on a second stream. */
+     * heaviest ones) belong to the render_tree kernel, which was launched just before this one and runs beside it. */
     const uint32_t n_tree = (RT_TREE && TREE && fp.tree_mode) ? (fp.tree_mode >= 2u ? ntiles : (fp.order ? __ldg(fp.n_split) : 0u)) : 0u;
     uint32_t next = 0;
     if (lane == 0) next = atomicAdd(fp.tile_counter, 1u) + n_tree;
@@ -522,10 +529,14 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsig
         const float rel = 24.0f + 4.0f * __log2f(fmaxf((float)prev[tile], 0.5f) / mean);
         uint32_t c = rel <= 0.0f ? 0u : (uint32_t)rel;
         c = c < kCostBuckets ? c : kCostBuckets - 1u;
-        /* hysteresis: a tile that the pixel-tree kernel took last frame (cost_out still holds that frame's costs) stays
-         * with it until its measured time has dropped two octaves below the threshold -- a tile whose tree pass is
-         * cheaper than its cooperative walk would otherwise change sides every frame (N = 4: 0.74 / 1.12 ms alternating) */
-        if (sticky_cost < kCostBuckets && c < sticky_cost && c + 8u >= sticky_cost && cost_out[tile] >= sticky_cost) c = sticky_cost;
+        /* hysteresis: a tile that the pixel-tree kernel took last frame (cost_out still holds that frame's costs) keeps the
+         * cost it entered with until its time there has dropped two octaves below the threshold.  A tile whose tree pass
+         * is cheaper than its cooperative walk would otherwise change sides every frame; and the kept cost is what
+         * orders the heavy tiles. */
+        if (sticky_cost < kCostBuckets && c + 8u >= sticky_cost) {
+            const uint32_t old = cost_out[tile];
+            if (old >= sticky_cost && old < kCostBuckets) c = old;
+        }
         cost_out[tile] = c;
         atomicAdd(&shist[c], split_ways(c, split_min_cost, split32_min_cost));
     }
@@ -683,27 +694,34 @@ cudaError_t prep_variant(int* blocks_per_sm, uint32_t smem) {
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_frame<R, M, A>, kBlock, smem);
 }
 
-/* The tree kernel beside the main one: forked onto `aux` (created with a higher priority, launched first so that its
- * CTAs -- the heaviest entries of the frame -- are resident when render_frame's persistent CTAs fill the rest), joined
- * back into `st`. */
+/* The tree kernel first, render_frame right behind it in the same stream with programmatic stream serialization
+ * allowed: it starts once every CTA of render_tree has signalled (griddepcontrol.launch_dependents at its top). */
 template <bool R, bool A>
-cudaError_t go_tree(const RtFrameParams& fp, uint32_t grid, uint32_t smem, cudaStream_t st, cudaStream_t aux, cudaEvent_t fork, cudaEvent_t join) {
+cudaError_t go_tree(const RtFrameParams& fp, uint32_t grid, uint32_t smem, cudaStream_t st) {
     if (smem > 48u * 1024u) {
         cudaError_t e = cudaFuncSetAttribute(render_tree<R, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    cudaError_t e = cudaEventRecord(fork, st);
-    if (e != cudaSuccess) return e;
-    e = cudaStreamWaitEvent(aux, fork, 0);
-    if (e != cudaSuccess) return e;
-    render_tree<R, A><<<grid, kBlock, smem, aux>>>(fp);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    return cudaEventRecord(join, aux);
+    render_tree<R, A><<<grid, kBlock, smem, st>>>(fp);
+    return cudaGetLastError();
+}
+template <bool R, int M, bool A>
+cudaError_t launch_variant_pdl(const RtFrameParams& fp, uint32_t grid, uint32_t smem, cudaStream_t st) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kBlock);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, render_frame<R, M, A>, fp);
 }
 
 template <bool R, int M, bool A>
-cudaError_t go(RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, RtLaunchShape* shape, const RtTreeLaunch* tree) {
+cudaError_t go(RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, RtLaunchShape* shape) {
     int bps = 0;
     cudaError_t e = prep_variant<R, M, A>(&bps, smem);
     if (e != cudaSuccess) return e;
@@ -715,7 +733,7 @@ cudaError_t go(RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, 
     if (grid > need) grid = need;
     if (grid == 0) grid = 1;
     if (shape) { shape->grid = grid; shape->block = kBlock; shape->smem_bytes = smem; shape->resident = R; shape->tree_grid = 0; }
-    const bool with_tree = RT_TREE && (M == 0 || M == 4) && fp.tree_mode && tree && tree->aux;
+    const bool with_tree = RT_TREE && (M == 0 || M == 4) && fp.tree_mode;
     uint32_t tgrid = 0;
     if (with_tree) {
         tgrid = fp.tree_slots;
@@ -727,14 +745,12 @@ cudaError_t go(RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, 
     fp.done_expected = grid + tgrid;
     if (with_tree) {
         const uint32_t tsmem = (R ? fp.lay.total * 16u : 0u) + kCoopBytesPerWarp;
-        e = go_tree<R, A>(fp, tgrid, tsmem, st, tree->aux, tree->fork, tree->join);
+        e = go_tree<R, A>(fp, tgrid, tsmem, st);
         if (e != cudaSuccess) return e;
         if (shape) shape->tree_grid = tgrid;
+        return launch_variant_pdl<R, M, A>(fp, grid, smem, st);
     }
-    e = launch_variant<R, M, A>(fp, grid, smem, st);
-    if (e != cudaSuccess) return e;
-    if (with_tree) e = cudaStreamWaitEvent(st, tree->join, 0);
-    return e;
+    return launch_variant<R, M, A>(fp, grid, smem, st);
 }
 
 }  // namespace RT_NS
@@ -785,8 +801,7 @@ cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d
     return cudaGetLastError();
 }
 
-cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape,
-                                     const RtTreeLaunch* tree) {
+cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape) {
     RtFrameParams fp = fp_in;
     const uint32_t blob_bytes = fp.lay.total * 16u;
     /* keep the geometry resident while it leaves room for >= 2 CTAs per SM */
@@ -797,7 +812,7 @@ cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, in
     const bool coop = mode == 0 || mode == 2 || mode == 4;
     const uint32_t smem = (resident ? blob_bytes : 0u) + (coop ? (kBlock / 32) * kCoopBytesPerWarp : 0u);
     const bool aov = fp.hit != nullptr;
-#define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape, tree)
+#define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape)
 #define RT_GO_A(R, M) do { if (aov) RT_GO(R, M, true); else RT_GO(R, M, false); } while (0)
 #if RT_TRIANGLES
 #define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else RT_GO_A(R, 3); } while (0)

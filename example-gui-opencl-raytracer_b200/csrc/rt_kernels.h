@@ -118,15 +118,10 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
 struct RtLaunchShape {
     uint32_t grid, block, smem_bytes, resident, tree_grid;
 };
-/* Second stream (and the fork / join events) on which the render_tree kernel runs beside render_frame; NULL = no tree phase. */
-struct RtTreeLaunch {
-    cudaStream_t aux;
-    cudaEvent_t fork, join;
-};
+
 /* Launches the fused raygen+raytracer kernel.  mode: 0 = cooperative trace, 1 = literal trace + reference work
  * counters, 2 = cooperative trace + executed-work counters, 3 = per-lane fast trace.  Geometry is staged in shared memory when it fits. */
-cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape,
-                             const RtTreeLaunch* tree);
+cudaError_t rt_launch_render(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
 
 /* Cost-ordered tile queue: d_cost[ntiles], d_hist_cursor[130] (zeroed here; word 128 receives the queue length, word 129
  * the number of leading heavy entries),
@@ -148,8 +143,7 @@ cudaError_t rt_launch_wait_flags(const uint32_t* d_flags, uint32_t stride_words,
                                  uint32_t* d_timeouts, cudaStream_t st);
 
 /* Extension X1 builds of the two launchers above (rt_kernels_tri.cu), used when the scene has triangles. */
-cudaError_t rt_launch_render_tri(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape,
-                                 const RtTreeLaunch* tree);
+cudaError_t rt_launch_render_tri(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
 cudaError_t rt_launch_tile_order_tri(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                      cudaStream_t st);
 /* Extension X1: rtriangle wire array -> {v0, v1-v0, v2-v0} records (3 float4 each). */

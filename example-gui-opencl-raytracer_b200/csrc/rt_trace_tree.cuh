@@ -146,6 +146,12 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
     }
     if (nroots == 0u) return true;
 
+#ifdef RT_TREE_CLOCKS /* diagnostic build (tools/exp/tree_clocks.py): SM clocks per phase, summed over entries, in fp.counters */
+    long long tc0 = clock64();
+#define RT_TREE_TICK(k) do { if (tid == 0u) { const long long t_ = clock64(); atomicAdd(fp.counters + (k), (unsigned long long)(t_ - tc0)); tc0 = t_; } } while (0)
+#else
+#define RT_TREE_TICK(k) do { } while (0)
+#endif
     /* ---- 1 EXPAND ---- */
     uint32_t n_nodes = nroots, n_shaded = 0, head = 0, nlev = 0;
     while (head < n_nodes) {
@@ -281,6 +287,10 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
     }
     if (tid == 0u) sh.lvl[nlev] = n_nodes;
     __syncthreads();
+    RT_TREE_TICK(0);
+#ifdef RT_TREE_CLOCKS
+    if (tid == 0u) { atomicAdd(fp.counters + 5, 1ull); atomicAdd(fp.counters + 6, (unsigned long long)n_nodes); atomicAdd(fp.counters + 7, (unsigned long long)nlev); }
+#endif
 
     /* ---- 2 RANK: sub-tree totals, last level first ---- */
     for (uint32_t lv = nlev; lv-- > 0u;) {
@@ -323,21 +333,18 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
         }
     }
     __syncthreads();
+    RT_TREE_TICK(1);
     /* ranks and stream positions, first level first; the node's own first addition and the PUSH / POP marks */
     float4* const stream = sl.stream();
     for (uint32_t lv = 0; lv < nlev; lv++) {
         const uint32_t b = sh.lvl[lv], e = sh.lvl[lv + 1u];
-        for (uint32_t i0 = b; i0 < e; i0 += kBlock) { /* whole warps run the loop: rng_jump's table walk is warp-uniform */
-            const uint32_t i = i0 + tid;
-            const bool act = i < e;
-            uint32_t rank = 0, seed = 0;
-            bool shd = false;
-            if (act) {
+        for (uint32_t i = b + tid; i < e; i += kBlock) {
+            {
                 const uint4 mm = sl.M()[i];
                 const uint4 x = sl.X()[i];
-                rank = x.z;
+                const uint32_t rank = x.z;
                 const uint32_t pos = x.w;
-                shd = ((mm.x >> 24) & 0xfu) == kNdShaded;
+                const bool shd = ((mm.x >> 24) & 0xfu) == kNdShaded;
                 const float4 t = sl.T()[i];
                 stream[pos] = make_float4(t.x, t.y, t.z, __uint_as_float(kOpAdd));
                 if (shd) {
@@ -362,19 +369,31 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
                         cx.z = crank; cx.w = p;
                         sl.X()[mm.z] = cx;
                     }
-                    /* the pixel's global id y*W + x seeds its generator (raytracing.cl:33) */
-                    { const uint32_t pix = (mm.x >> 16) & 127u; seed = tile_lanes(fp, sh.entry[first + (pix >> 5)], pix & 31u).id; }
                 }
             }
-            /* RNG state on entry to the segment: xorshift32^(4L*rank)(pixel id) */
-            const uint32_t k = (act && shd) ? rank : 0u;
-            const uint32_t kmax = __reduce_max_sync(kFull, k);
-            const uint32_t state = rng_jump(fp.jump, seed, k, kmax);
-            if (act && shd) { uint4 x = sl.X()[i]; x.z = state; sl.X()[i] = x; }
         }
         __syncthreads();
     }
+    /* RNG state on entry to every shaded segment: xorshift32^(4L*rank)(pixel id), the pixel's global id y*W + x being its
+     * seed (raytracing.cl:33).  One pass over the shaded list -- whole warps run it: rng_jump's table walk is
+     * warp-uniform -- instead of a jump per level. */
+    for (uint32_t k0 = 0; k0 < n_shaded; k0 += kBlock) {
+        const uint32_t k = k0 + tid;
+        const bool act = k < n_shaded;
+        uint32_t node = 0, rank = 0, seed = 0;
+        if (act) {
+            node = sl.shaded()[k];
+            const uint32_t pix = (sl.M()[node].x >> 16) & 127u;
+            rank = sl.X()[node].z;
+            seed = tile_lanes(fp, sh.entry[first + (pix >> 5)], pix & 31u).id;
+        }
+        const uint32_t kmax = __reduce_max_sync(kFull, rank);
+        const uint32_t state = rng_jump(fp.jump, seed, rank, kmax);
+        if (act) reinterpret_cast<uint32_t*>(sl.X() + node)[2] = state;
+    }
+    __syncthreads();
 
+    RT_TREE_TICK(2);
     /* ---- 3 SHADE: (shaded node, light) pairs over the threads ---- */
     const uint32_t items = n_shaded * L;
 #pragma unroll 1
@@ -427,27 +446,44 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
     }
     __syncthreads();
 
+    RT_TREE_TICK(3);
     /* ---- 4 REPLAY: additions in the stack machine's order; thread q replays pixel q = entry slot * 32 + tile pixel ---- */
     if (warp < ne) {
         const TileLanes tq = tile_lanes(fp, sh.entry[first + warp], lane);
         if (tq.live && (only_pixel >= 32u || lane == only_pixel)) {
+            /* The additions are one dependent chain per pixel (their order is the result), so the heaviest pixel of the
+             * entry sets the pace: 166 segments = 1,300 records.  Records are fetched eight at a time, one batch ahead of
+             * the one being added (they sit in L2: other threads wrote them), so the chain never waits for memory --
+             * 169k -> clocks per entry measured before (tools/exp/tree_clocks.py), 44 % of the whole pass.  Batches are
+             * padded with ADD +0 records: x + 0 == x (see the header). */
             V3 acc = mk(0.0f, 0.0f, 0.0f);
             V3 stk[kMaxDepth];
             uint32_t sp = 0;
             const float4* ev = stream + sh.pix_base[tid];
             const uint32_t n = sh.pix_size[tid];
-#pragma unroll 4
-            for (uint32_t q = 0; q < n; q++) {
-                const float4 r = ev[q];
-                const uint32_t op = __float_as_uint(r.w);
-                if (op == kOpAdd) acc = acc + xyz(r);
-                else if (op == kOpPush) { stk[sp++] = acc; acc = mk(0.0f, 0.0f, 0.0f); }
-                else { sp--; acc = stk[sp] + acc; }
+            const float4 pad = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kOpAdd));
+            float4 cur[8], nxt[8];
+#pragma unroll
+            for (uint32_t k = 0; k < 8u; k++) cur[k] = k < n ? __ldcg(ev + k) : pad;
+            for (uint32_t q = 0; q < n; q += 8u) {
+#pragma unroll
+                for (uint32_t k = 0; k < 8u; k++) nxt[k] = q + 8u + k < n ? __ldcg(ev + q + 8u + k) : pad;
+#pragma unroll
+                for (uint32_t k = 0; k < 8u; k++) {
+                    const float4 r = cur[k];
+                    const uint32_t op = __float_as_uint(r.w);
+                    if (op == kOpAdd) acc = acc + xyz(r);
+                    else if (op == kOpPush) { stk[sp++] = acc; acc = mk(0.0f, 0.0f, 0.0f); }
+                    else { sp--; acc = stk[sp] + acc; }
+                }
+#pragma unroll
+                for (uint32_t k = 0; k < 8u; k++) cur[k] = nxt[k];
             }
             sh.word[tid] = pack_rgb(acc);
         }
     }
     __syncthreads();
+    RT_TREE_TICK(4);
     return true;
 }
 

@@ -196,6 +196,8 @@ int rtb_map_load(const char* path, rtb_map* out);
 int rtb_map_save(const char* path, const rtb_map* m, int version);
 void rtb_map_free(rtb_map* m);
 
+/* Diagnostic builds only (e.g. -DRT_TREE_CLOCKS): the raw counter words the last launch left behind. */
+int rtb_debug_counters(rtb_engine* e, uint64_t out[RTB_NCOUNTERS]);
 /* Launch geometry the renderer chose for the last frame (for bench.py's accounting). */
 typedef struct {
     uint32_t grid, block, smem_bytes, tiles, resident_scene; /* resident_scene: 1 = geometry staged in shared memory */

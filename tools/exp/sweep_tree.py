@@ -2,7 +2,7 @@
 each rank of a cyclic 8-row band split), per (tree, tree_min_cost, split4, split32) on the relative cost scale
 (24 = mean tile, +4 per octave; 0 = the engine's automatic value).  Six frames per part: the sequence shows whether the
 measured-time schedule is stable.
-    python tools/exp/sweep_tree.py [workload [combo,combo,...]]   combo = tree:tmin:s4:s32"""
+    python tools/exp/sweep_tree.py [workload [combo,combo,...]]   combo = tree:tmin:s4:s32[:group_max_cost]"""
 import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -23,8 +23,11 @@ else:
     combos = [(0, 0, 0, 0), (1, 0, 0, 0)] + [(1, t, s4, s32) for t, s4, s32 in
               ((28, 64, 64), (32, 64, 64), (36, 64, 64), (40, 64, 64), (44, 64, 64), (32, 40, 64), (32, 44, 64), (36, 44, 64), (36, 44, 52), (32, 40, 48), (28, 36, 64), (28, 40, 48))]
 ref_frame = None
-for tree, tmin, s4, s32 in combos:
-    eng.set_option("tree", tree); eng.set_option("tree_min_cost", tmin)
+for combo in combos:
+    tree, tmin, s4, s32 = combo[:4]
+    gmax = combo[4] if len(combo) > 4 else 0
+    eng.set_option("tree_ctas_per_sm", combo[5] if len(combo) > 5 else 3)
+    eng.set_option("tree", tree); eng.set_option("tree_min_cost", tmin); eng.set_option("tree_group_max_cost", gmax)
     eng.set_option("split_min_cost", s4); eng.set_option("split32_min_cost", s32)
     out = []
     for parts in (1, 4, 8):
@@ -39,4 +42,4 @@ for tree, tmin, s4, s32 in combos:
         out.append("N=%d %.3f [%s]" % (parts, worst, " ".join("%.2f" % v for v in seq)))
     rgb, _ = eng.render_to_host(W, H, want_hit=False)
     if ref_frame is None: ref_frame = rgb
-    print("tree=%d tmin=%2d split4>=%2d split32>=%2d same=%s :: %s" % (tree, tmin, s4, s32, bool(np.array_equal(rgb, ref_frame)), " | ".join(out)), flush=True)
+    print("tree=%d tmin=%2d split4>=%2d split32>=%2d gmax=%2d ctas/sm=%d same=%s :: %s" % (tree, tmin, s4, s32, gmax, combo[5] if len(combo) > 5 else 3, bool(np.array_equal(rgb, ref_frame)), " | ".join(out)), flush=True)
