@@ -418,6 +418,12 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                         fp.tree_min_cost = t;
                         fp.tree_group_max_cost = e->opt_tree_group_max_cost > 0 ? (uint32_t)e->opt_tree_group_max_cost : 0u; /* pooling four entries per pass lengthens the chains it is there to shorten (tools/exp/sweep_tree.py): off unless asked for */
                         fp.cost_is_history = e->cost_hist_valid ? 1u : 0u;
+                    } else if (wide_scene) {
+                        /* many-sphere scenes: a split entry's few rays are walked by all 32 lanes (WIDE variant), so
+                         * splitting costs little and the tail of a part is its longest tile: rows from 0.5 T, single
+                         * pixels from T (1,024-sphere grid, slowest of 8 parts 50.8 -> 31-34 ms, of 4 parts 69 -> 54 ms) */
+                        fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(0.5, 32.0);
+                        fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : thr(1.0, 36.0);
                     } else {
                         fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(0.75, 40.0);
                         fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : thr(3.0, 48.0);
