@@ -28,7 +28,7 @@ for arg in sys.argv[1:]:
     for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
         i = head.index(name)
         tot += float(vals[i].replace(",", "")) * UNIT[units[i]]
-    out[workload] = {"dram_bytes": tot, "source_hash": bench.kernel_source_hash(), "capture": os.path.basename(rep),
+    out[workload] = {"dram_bytes": tot, "source_hash": bench.kernel_source_hash(), "capture": "profiles/r02_" + ("render_frame_wide" if "wide" in rep else "render_frame") + "_details.txt (ncu --set full)",
                      "kernel": vals[head.index("Kernel Name")]}
     print(workload, out[workload])
 json.dump(out, open(path, "w"), indent=1)
