@@ -421,8 +421,8 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
         const bool diff_zero = (fd == 0.0f) || (dif == 0.0f);
         V3 spec = mk(0.0f, 0.0f, 0.0f), diffv = spec;
         if (!(spec_zero && diff_zero)) {
-            float soft = 0.0f;
-#pragma unroll 1
+            V3 smp[kShadowSamples];
+#pragma unroll
             for (int j = 0; j < kShadowSamples; j++) {
                 const float theta = (float)(kTwoPi * (double)rng_next(rng));
                 const float phi = (float)(kPi * (double)rng_next(rng));
@@ -430,9 +430,12 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
                 sincos_bounded(phi, sp, cp);
                 sincos_bounded(theta, sth, cth);
                 const float rs = l1.w * sp;
-                const V3 sample = xyz(l0) + mk(rs * cth, rs * sth, l1.w * cp); /* raytracing.cl:101-106 */
-                soft += shadow_path_fast(sample, ip, g, tl);
+                smp[j] = xyz(l0) + mk(rs * cth, rs * sth, l1.w * cp); /* raytracing.cl:101-106 */
             }
+            static_assert(kShadowSamples == 2, "shadow_pair_fast traces the two samples of a light together");
+            float r0, r1;
+            shadow_pair_fast(smp[0], smp[1], ip, g, tl, r0, r1);
+            const float soft = (0.0f + r0) + r1;
             if (!(soft == 0.0f && tame)) { /* else light_rgb *= 0: both terms are exact zeros */
                 const float ssr = soft / (float)kShadowSamples;
                 const V3 lrgb = div3_pos(xyz(l1) * 1.0f, dist * dist) * ssr;
