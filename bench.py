@@ -321,7 +321,7 @@ class _Raw:
 FLAG_STRIDE_WORDS = 16      # one 64-byte line per rank's completion flag
 
 
-def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full", kernel_reps=10):
+def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full", kernel_reps=10, opts=None):
     """One workload on this process group: accounting launch, bit-identity check against one GPU (N>1), device-timed
     steps, kernel-only time for the roofline and (want_e2e) the end-to-end leg.  Returns a dict (complete on rank 0)."""
     torch, dist, eng, pkg = ctx.torch, ctx.dist, ctx.eng, ctx.pkg
@@ -333,6 +333,8 @@ def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full"
     for kv in filter(None, os.environ.get("BENCH_ENGINE_OPTS", "").split(",")):   # A/B hook: name=value,...
         k, v = kv.split("=")
         eng.set_option(k, int(v))
+    for k, v in (opts or {}).items():
+        eng.set_option(k, v)
 
     band = args.band_rows
     part = pkg.Partition(band, world, rank) if world > 1 else None
@@ -553,6 +555,8 @@ def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full"
         frame = None
         if raw_frame is not None:
             eng.dev_free(raw_frame)
+    for k in (opts or {}):
+        eng.set_option(k, 0)
     return res
 
 
@@ -699,6 +703,13 @@ def gpu_body(args, pkg, eng, world, rank, local):
         # takes seconds instead of tens of seconds; the NCCL-gather exchange beside the peer-store default
         others["spheres1024_4k"] = slim(measure(ctx, make_workload("spheres1024_4k", host), 3, 3, exchange=args.exchange,
                                                 want_e2e=False, kernel_reps=3))
+        # SURVEY 8(f) N4 (extension, not the reference's algorithm): the same frame through the cluster walk; counted rays
+        # and algorithmic flop are the brute-force ones, so "roofline" here is an equivalent rate, not executed work
+        others["spheres1024_4k_accel"] = slim(measure(ctx, make_workload("spheres1024_4k", host), 5, 3, exchange=args.exchange,
+                                                      want_e2e=False, kernel_reps=3, opts={"accel": 1}))
+        others["spheres1024_4k_accel"]["note"] = ("EXTENSION N4: cluster acceleration structure (csrc/rt_trace_accel.cuh), frame word-identical "
+                                                  "to the brute-force one (tests/test_accel_gpu.py); Mrays/s and the roofline figure count the "
+                                                  "reference's brute-force rays and tests, which this walk mostly skips")
         if world == 1:
             others["spheres255_8k"] = slim(measure(ctx, make_workload("spheres255_8k", host), 3, 3, want_e2e=False, kernel_reps=3))
             others["orbit_1440p"] = orbit_config(ctx) if rank == 0 else None

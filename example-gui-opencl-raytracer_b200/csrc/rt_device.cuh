@@ -19,6 +19,9 @@
 #ifndef RT_TRIANGLES
 #define RT_TRIANGLES 0
 #endif
+#ifndef RT_ACCEL
+#define RT_ACCEL 0 /* 1: rt_kernels_accel.cu -- sphere walks through the N4 cluster structure (rt_trace_accel.cuh) */
+#endif
 #ifndef RT_NS
 #define RT_NS rt
 #endif
@@ -104,6 +107,10 @@ struct Geo {
     uint32_t S, P, L, Spad, Lpad;
     const float4* tri; /* extension X1: [3T] {v0, e1, e2}, global memory */
     uint32_t T;
+    const float4* acc_cl; /* N4 (rt_trace_accel.cuh), global memory */
+    const float4* acc_rec;
+    const uint32_t* acc_idx;
+    uint32_t acc_nc;
 };
 __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFrameParams& fp, const float* lut) {
     g.S = fp.S; g.P = fp.P; g.L = fp.L;
@@ -116,6 +123,8 @@ __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFra
     g.lut255 = lut;
     g.tri = fp.tri;
     g.T = RT_TRIANGLES ? fp.T : 0u; /* a literal 0 in the plain build: every triangle loop and branch folds away */
+    g.acc_cl = fp.acc_cl; g.acc_rec = fp.acc_rec; g.acc_idx = fp.acc_idx;
+    g.acc_nc = RT_ACCEL ? fp.acc_nc : 0u;
 }
 
 /* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */

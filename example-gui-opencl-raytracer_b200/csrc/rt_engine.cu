@@ -6,6 +6,11 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+#include <cmath>
+#include <utility>
+#include <vector>
+
 #include "../../include/rtb200.h"
 #include "rt_kernels.h"
 
@@ -78,6 +83,9 @@ struct rtb_engine {
     DevBuf jump;              /* [15][32] xorshift32 jump-ahead matrices for this scene's light count */
     uint32_t jump_L = 0xffffffffu;
     int opt_tree_ctas_per_sm = 3;
+    int opt_accel = 0;        /* N4: 1 = many-sphere scenes walk the cluster structure instead of every record */
+    DevBuf accel;             /* clusters, cluster-ordered records, original indices */
+    uint32_t acc_nc = 0;
     int opt_tree = 1, opt_tree_cap = 8192, opt_tree_min_cost = 0 /* 0 = automatic */, opt_tree_group_max_cost = 0;
     bool cost_hist_valid = false; /* tile_cost holds measured-time costs of a frame with this geometry */
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
@@ -111,7 +119,7 @@ void rtb_destroy(rtb_engine* e) {
     e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
     e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
-    e->tree_slab.release(); e->wait_word.release(); e->jump.release();
+    e->tree_slab.release(); e->wait_word.release(); e->jump.release(); e->accel.release();
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->evk) cudaEventDestroy(e->evk);
@@ -180,6 +188,88 @@ static int prep_jump(rtb_engine* e) {
     return 0;
 }
 
+/* N4 (csrc/rt_trace_accel.cuh): spheres in Morton order of their centres, clusters of RT_ACCEL_K, per cluster a bounding
+ * sphere computed in fp64 around the (float) centre and inflated.  `host_spheres` = the wire array (96-byte records). */
+static uint32_t morton10(uint32_t v) { /* spread 10 bits to every third position */
+    v &= 1023u;
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
+    e->acc_nc = 0;
+    const uint32_t S = e->S, K = RT_ACCEL_K;
+    if (S < 2u * K || !host_spheres) return 0;
+    std::vector<double> cx(S), cy(S), cz(S), rr(S);
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (uint32_t i = 0; i < S; i++) {
+        float c[4], r;
+        memcpy(c, host_spheres + (size_t)i * RT_SPHERE_BYTES, 16);
+        memcpy(&r, host_spheres + (size_t)i * RT_SPHERE_BYTES + 16, 4);
+        if (!std::isfinite(c[0]) || !std::isfinite(c[1]) || !std::isfinite(c[2]) || !std::isfinite(r)) return 0; /* brute force */
+        cx[i] = c[0]; cy[i] = c[1]; cz[i] = c[2]; rr[i] = fabs((double)r);
+        const double v[3] = {cx[i], cy[i], cz[i]};
+        for (int k = 0; k < 3; k++) { lo[k] = v[k] < lo[k] ? v[k] : lo[k]; hi[k] = v[k] > hi[k] ? v[k] : hi[k]; }
+    }
+    std::vector<std::pair<uint32_t, uint32_t>> order(S);
+    for (uint32_t i = 0; i < S; i++) {
+        const double v[3] = {cx[i], cy[i], cz[i]};
+        uint32_t code = 0;
+        for (int k = 0; k < 3; k++) {
+            const double span = hi[k] - lo[k];
+            const uint32_t q = span > 0 ? (uint32_t)fmin(1023.0, (v[k] - lo[k]) / span * 1024.0) : 0u;
+            code |= morton10(q) << k;
+        }
+        order[i] = {code, i};
+    }
+    std::sort(order.begin(), order.end());
+    const uint32_t nc = (S + K - 1) / K;
+    std::vector<float> cl(4 * (size_t)nc), rec(4 * (size_t)nc * K);
+    std::vector<uint32_t> idx((size_t)nc * K, 0xffffffffu);
+    for (uint32_t k = 0; k < nc; k++) {
+        const uint32_t b = k * K, n = (b + K <= S ? K : S - b);
+        double mx = 0, my = 0, mz = 0;
+        for (uint32_t j = 0; j < n; j++) { const uint32_t i = order[b + j].second; mx += cx[i]; my += cy[i]; mz += cz[i]; }
+        const float C[3] = {(float)(mx / n), (float)(my / n), (float)(mz / n)};
+        double R = 0;
+        for (uint32_t j = 0; j < n; j++) {
+            const uint32_t i = order[b + j].second;
+            const double dx = cx[i] - C[0], dy = cy[i] - C[1], dz = cz[i] - C[2];
+            const double d = sqrt(dx * dx + dy * dy + dz * dz) + rr[i];
+            R = d > R ? d : R;
+        }
+        R = R * (1.0 + 1e-5) + 1e-30;
+        const double w = 1.125 * R * R * (1.0 + 1e-6);
+        if (!(w < 1e37)) return 0;
+        cl[4 * k + 0] = C[0]; cl[4 * k + 1] = C[1]; cl[4 * k + 2] = C[2]; cl[4 * k + 3] = nextafterf((float)w, INFINITY);
+        for (uint32_t j = 0; j < K; j++) {
+            float* o = &rec[4 * ((size_t)b + j)];
+            if (j < n) {
+                const uint32_t i = order[b + j].second;
+                float c[4], r;
+                uint32_t transp;
+                memcpy(c, host_spheres + (size_t)i * RT_SPHERE_BYTES, 16);
+                memcpy(&r, host_spheres + (size_t)i * RT_SPHERE_BYTES + 16, 4);
+                memcpy(&transp, host_spheres + (size_t)i * RT_SPHERE_BYTES + RT_MATERIAL_OFFSET + 32, 4);
+                o[0] = c[0]; o[1] = c[1]; o[2] = c[2]; o[3] = r * r; /* as scene_prep does: one fp32 product */
+                idx[(size_t)b + j] = i | (transp ? 0x80000000u : 0u);
+            } else {
+                o[0] = o[1] = o[2] = 0.0f; o[3] = -INFINITY; /* never hit */
+            }
+        }
+    }
+    const size_t b0 = (size_t)nc * 16, b1 = (size_t)nc * K * 16, b2 = (size_t)nc * K * 4;
+    if (e->accel.ensure(b0 + b1 + b2)) return -2;
+    CU(cudaMemcpyAsync(e->accel.p, cl.data(), b0, cudaMemcpyHostToDevice, e->stream), "H2D accel");
+    CU(cudaMemcpyAsync((char*)e->accel.p + b0, rec.data(), b1, cudaMemcpyHostToDevice, e->stream), "H2D accel");
+    CU(cudaMemcpyAsync((char*)e->accel.p + b0 + b1, idx.data(), b2, cudaMemcpyHostToDevice, e->stream), "H2D accel");
+    CU(cudaStreamSynchronize(e->stream), "accel upload"); /* the vectors die with this frame */
+    e->acc_nc = nc;
+    return 0;
+}
+
 static int prep_scene(rtb_engine* e) {
     if (int rc = prep_jump(e)) return rc;
     e->lay = rt_blob_layout(e->S, e->P, e->L);
@@ -211,7 +301,7 @@ int rtb_upload_scene(rtb_engine* e, const void* spheres, uint32_t S, const void*
     int rc = prep_scene(e);
     if (rc) return rc;
     CU(cudaStreamSynchronize(e->stream), "scene upload"); /* blocking, like clEnqueueWriteBuffer(CL_TRUE) */
-    return 0;
+    return prep_accel(e, (const unsigned char*)spheres);
 }
 
 int rtb_bind_scene_device(rtb_engine* e, const void* d_spheres, uint32_t S, const void* d_planes, uint32_t P,
@@ -224,7 +314,10 @@ int rtb_bind_scene_device(rtb_engine* e, const void* d_spheres, uint32_t S, cons
     e->d_planes = (const unsigned char*)d_planes;
     e->d_lights = (const unsigned char*)d_lights;
     e->S = S; e->P = P; e->L = L;
-    return prep_scene(e);
+    if (int rc = prep_scene(e)) return rc;
+    std::vector<unsigned char> host((size_t)S * RT_SPHERE_BYTES);
+    if (S) CU(cudaMemcpy(host.data(), d_spheres, host.size(), cudaMemcpyDeviceToHost), "D2H spheres (accel build)");
+    return prep_accel(e, S ? host.data() : nullptr);
 }
 
 static int prep_tris(rtb_engine* e) {
@@ -330,6 +423,15 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.blob = (const float4*)e->blob.p;
     fp.raw_spheres = e->d_spheres; fp.raw_planes = e->d_planes;
     fp.T = e->T; fp.tri = (const float4*)e->tri_rec.p; fp.raw_tris = e->d_tris;
+    /* N4: the cluster walk instead of the record walk -- an extension, off unless asked for ("accel"), production trace only */
+    const bool use_accel = e->opt_accel > 0 && mode == 0 && e->T == 0u && e->acc_nc > 0u;
+    if (use_accel) {
+        const size_t b0 = (size_t)e->acc_nc * 16, b1 = (size_t)e->acc_nc * RT_ACCEL_K * 16;
+        fp.acc_cl = (const float4*)e->accel.p;
+        fp.acc_rec = (const float4*)((const char*)e->accel.p + b0);
+        fp.acc_idx = (const uint32_t*)((const char*)e->accel.p + b0 + b1);
+        fp.acc_nc = e->acc_nc;
+    }
     /* a scene whose planes carry texture ids needs the texture array; without one, ids clamp onto a 1x1 dummy */
     fp.tex = (const uchar4*)(e->d_tex ? e->d_tex : e->d_sky);
     fp.tw = e->d_tex ? (int)e->tw : 1; fp.th = e->d_tex ? (int)e->th : 1; fp.tl = e->d_tex ? (int)e->tl : 1;
@@ -404,7 +506,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                     };
                     /* the pixel-tree kernel: not for many-sphere scenes (the WIDE variant's territory: a tree node walks all
                      * records on ONE lane; measured 50 -> 115 ms per N = 8 part on the 1,024-sphere grid) */
-                    const bool wide_scene = e->T == 0u && e->lay.Lpad + e->lay.Spad >= (uint32_t)e->opt_wide_min_records;
+                    const bool wide_scene = e->T == 0u && !use_accel && e->lay.Lpad + e->lay.Spad >= (uint32_t)e->opt_wide_min_records;
                     const bool tree = e->opt_tree > 0 && e->L <= 16u && (!wide_scene || e->opt_tree >= 2);
                     if (tree) {
                         /* with the CTA-wide pixel-tree kernel beside render_frame (tools/exp/sweep_tree.py): tiles longer than
@@ -441,7 +543,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
             e->time_valid = false;
             e->cost_hist_valid = false;
         } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
-        CU((e->T ? rt_launch_tile_order_tri : rt_launch_tile_order)(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
+        CU((e->T ? rt_launch_tile_order_tri : (use_accel ? rt_launch_tile_order_acc : rt_launch_tile_order))(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),
            "tile_order launch");
         fp.order = (const uint32_t*)e->tile_order.p;
@@ -469,7 +571,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
-    CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
+    CU((e->T ? rt_launch_render_tri : (use_accel ? rt_launch_render_acc : rt_launch_render))(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
     CU(cudaEventRecord(e->ev1, e->stream), "event record");
     e->timed = true;
     e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;
@@ -517,6 +619,7 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!strcmp(name, "wide_max_live")) { e->opt_wide_max_live = value > 32 ? 32 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     if (!strcmp(name, "tree")) { e->opt_tree = value < 0 ? 0 : (value > 3 ? 3 : value); return 0; }
+    if (!strcmp(name, "accel")) { e->opt_accel = value ? 1 : 0; e->time_valid = false; return 0; }
     if (!strcmp(name, "tree_ctas_per_sm")) { e->opt_tree_ctas_per_sm = value < 1 ? 1 : (value > 8 ? 8 : value); e->tree_slab.release(); return 0; }
     if (!strcmp(name, "tree_group_max_cost")) { e->opt_tree_group_max_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tree_min_cost")) { e->opt_tree_min_cost = value < 0 ? 0 : value; return 0; }

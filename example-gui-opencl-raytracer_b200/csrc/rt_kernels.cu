@@ -759,11 +759,13 @@ using namespace RT_NS;
 
 #if RT_TRIANGLES
 #define RT_EXPORT(name) name##_tri
+#elif RT_ACCEL
+#define RT_EXPORT(name) name##_acc
 #else
 #define RT_EXPORT(name) name
 #endif
 
-#if !RT_TRIANGLES
+#if !RT_TRIANGLES && !RT_ACCEL
 cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, const unsigned char* d_planes, uint32_t P,
                                  const unsigned char* d_lights, uint32_t L, float4* d_blob, RtBlobLayout lay,
                                  cudaStream_t st) {
@@ -806,7 +808,7 @@ cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, in
     const uint32_t blob_bytes = fp.lay.total * 16u;
     /* keep the geometry resident while it leaves room for >= 2 CTAs per SM */
     const bool resident = blob_bytes <= 96u * 1024u;
-#if !RT_TRIANGLES
+#if !RT_TRIANGLES && !RT_ACCEL
     if (mode == 0 && fp.T == 0u && fp.lay.Lpad + fp.lay.Spad >= fp.wide_min_records) mode = 4; /* many spheres: WIDE variant */
 #endif
     const bool coop = mode == 0 || mode == 2 || mode == 4;
@@ -814,7 +816,7 @@ cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, in
     const bool aov = fp.hit != nullptr;
 #define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape)
 #define RT_GO_A(R, M) do { if (aov) RT_GO(R, M, true); else RT_GO(R, M, false); } while (0)
-#if RT_TRIANGLES
+#if RT_TRIANGLES || RT_ACCEL
 #define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else RT_GO_A(R, 3); } while (0)
 #else
 #define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else if (mode == 4) RT_GO_A(R, 4); else RT_GO_A(R, 3); } while (0)
@@ -827,7 +829,7 @@ cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, in
     return cudaErrorInvalidValue;
 }
 
-#if !RT_TRIANGLES
+#if !RT_TRIANGLES && !RT_ACCEL
 cudaError_t rt_launch_assemble_bands(const uint32_t* d_compact, size_t stride_words, uint32_t* d_frame, uint32_t W, uint32_t H,
                                      uint32_t band_rows, uint32_t parts, cudaStream_t st) {
     const size_t n = (size_t)((W + 3u) / 4u) * H;

@@ -47,6 +47,9 @@ static inline size_t rt_tree_slab_records(uint32_t cap, uint32_t L) {
     return (size_t)RT_TREE_PLANES * cap + (cap + 3u) / 4u + (size_t)cap * (3u + 2u * L);
 }
 
+/* N4 (rt_trace_accel.cuh): spheres per cluster of the acceleration structure */
+#define RT_ACCEL_K 8
+
 struct RtFrameParams {
     /* raygen.cl:5-8 scalar arguments */
     float corner[3], origin[3], up[3], right[3], wf, hf;
@@ -63,6 +66,11 @@ struct RtFrameParams {
     uint32_t T;
     const float4* tri;
     const unsigned char* raw_tris;
+    /* N4 acceleration structure over the spheres (extension; NULL / 0 = brute force as in the reference) */
+    const float4* acc_cl;    /* [acc_nc] {C.xyz, 1.125 * R'^2}: inflated bounding sphere of a cluster */
+    const float4* acc_rec;   /* [acc_nc * RT_ACCEL_K] {c.xyz, r*r} in cluster order, never-hit padding */
+    const uint32_t* acc_idx; /* [acc_nc * RT_ACCEL_K] original sphere index | transperent << 31, 0xffffffff = padding */
+    uint32_t acc_nc;
     /* image arrays */
     const uchar4* tex; int tw, th, tl;
     const uchar4* sky; int sw, sh;
@@ -144,6 +152,10 @@ cudaError_t rt_launch_wait_flags(const uint32_t* d_flags, uint32_t stride_words,
 
 /* Extension X1 builds of the two launchers above (rt_kernels_tri.cu), used when the scene has triangles. */
 cudaError_t rt_launch_render_tri(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
+/* N4 builds (rt_kernels_accel.cu): the sphere walks go through the cluster structure. */
+cudaError_t rt_launch_render_acc(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
+cudaError_t rt_launch_tile_order_acc(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
+                                     cudaStream_t st);
 cudaError_t rt_launch_tile_order_tri(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                      cudaStream_t st);
 /* Extension X1: rtriangle wire array -> {v0, v1-v0, v2-v0} records (3 float4 each). */

@@ -125,7 +125,10 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * history-scheduled frames: tiles whose cost reaches "tree_min_cost" (0 = automatic) and every split entry; 0 = never;
  * 2 = every tile; 3 = every tile, one pixel at a time (what a single-pixel entry does; tests).
  * "tree_cap": nodes per CTA slab (default 8192; a larger tree falls back to the cooperative walk).  Pixels do not
- * change. */
+ * change.
+ * "accel" (EXTENSION; default 0 = brute force over every record, as the reference does): 1 = scenes
+ * with >= 16 spheres and no triangles walk a cluster structure built at upload (csrc/rt_trace_accel.cuh) that skips only
+ * tests whose outcome is provably "no hit"; the frame is word-identical to the brute-force one. */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
 /* Brute-force check of the arithmetic routines against IEEE division / sqrt (trials per thread on 592x256
  * threads).  out[0] = division mismatches, out[1] = normalize mismatches, out[2] = max |sincos - libdevice|
