@@ -110,6 +110,7 @@ struct Geo {
     const float4* acc_cl; /* N4 (rt_trace_accel.cuh), global memory */
     const float4* acc_rec;
     const uint32_t* acc_idx;
+    const float4* acc_grp;
     uint32_t acc_nc;
 };
 __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFrameParams& fp, const float* lut) {
@@ -123,7 +124,7 @@ __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFra
     g.lut255 = lut;
     g.tri = fp.tri;
     g.T = RT_TRIANGLES ? fp.T : 0u; /* a literal 0 in the plain build: every triangle loop and branch folds away */
-    g.acc_cl = fp.acc_cl; g.acc_rec = fp.acc_rec; g.acc_idx = fp.acc_idx;
+    g.acc_cl = fp.acc_cl; g.acc_rec = fp.acc_rec; g.acc_idx = fp.acc_idx; g.acc_grp = fp.acc_grp;
     g.acc_nc = RT_ACCEL ? fp.acc_nc : 0u;
 }
 

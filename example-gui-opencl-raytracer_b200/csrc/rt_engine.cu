@@ -214,11 +214,12 @@ static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
         for (int k = 0; k < 3; k++) { lo[k] = v[k] < lo[k] ? v[k] : lo[k]; hi[k] = v[k] > hi[k] ? v[k] : hi[k]; }
     }
     std::vector<std::pair<uint32_t, uint32_t>> order(S);
+    double span = 0;
+    for (int k = 0; k < 3; k++) span = hi[k] - lo[k] > span ? hi[k] - lo[k] : span;
     for (uint32_t i = 0; i < S; i++) {
         const double v[3] = {cx[i], cy[i], cz[i]};
         uint32_t code = 0;
-        for (int k = 0; k < 3; k++) {
-            const double span = hi[k] - lo[k];
+        for (int k = 0; k < 3; k++) { /* ONE scale for the three axes: a thin axis (spheres resting on a plane) must not scatter the order */
             const uint32_t q = span > 0 ? (uint32_t)fmin(1023.0, (v[k] - lo[k]) / span * 1024.0) : 0u;
             code |= morton10(q) << k;
         }
@@ -260,11 +261,32 @@ static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
             }
         }
     }
-    const size_t b0 = (size_t)nc * 16, b1 = (size_t)nc * K * 16, b2 = (size_t)nc * K * 4;
-    if (e->accel.ensure(b0 + b1 + b2)) return -2;
+    /* second level: one bounding sphere per RT_ACCEL_G consecutive clusters, around their member spheres */
+    const uint32_t ng = (nc + RT_ACCEL_G - 1) / RT_ACCEL_G;
+    std::vector<float> grp(4 * (size_t)ng);
+    for (uint32_t q = 0; q < ng; q++) {
+        const uint32_t b = q * RT_ACCEL_G * K, end = (b + RT_ACCEL_G * K < S ? b + RT_ACCEL_G * K : S), n = end - b;
+        double mx = 0, my = 0, mz = 0;
+        for (uint32_t j = b; j < end; j++) { const uint32_t i = order[j].second; mx += cx[i]; my += cy[i]; mz += cz[i]; }
+        const float C[3] = {(float)(mx / n), (float)(my / n), (float)(mz / n)};
+        double R = 0;
+        for (uint32_t j = b; j < end; j++) {
+            const uint32_t i = order[j].second;
+            const double dx = cx[i] - C[0], dy = cy[i] - C[1], dz = cz[i] - C[2];
+            const double d = sqrt(dx * dx + dy * dy + dz * dz) + rr[i];
+            R = d > R ? d : R;
+        }
+        R = R * (1.0 + 1e-5) + 1e-30;
+        const double w = 1.125 * R * R * (1.0 + 1e-6);
+        if (!(w < 1e37)) return 0;
+        grp[4 * q + 0] = C[0]; grp[4 * q + 1] = C[1]; grp[4 * q + 2] = C[2]; grp[4 * q + 3] = nextafterf((float)w, INFINITY);
+    }
+    const size_t b0 = (size_t)nc * 16, b1 = (size_t)nc * K * 16, b2 = ((size_t)nc * K * 4 + 15) / 16 * 16, b3 = (size_t)ng * 16;
+    if (e->accel.ensure(b0 + b1 + b2 + b3)) return -2;
+    CU(cudaMemcpyAsync((char*)e->accel.p + b0 + b1 + b2, grp.data(), b3, cudaMemcpyHostToDevice, e->stream), "H2D accel");
     CU(cudaMemcpyAsync(e->accel.p, cl.data(), b0, cudaMemcpyHostToDevice, e->stream), "H2D accel");
     CU(cudaMemcpyAsync((char*)e->accel.p + b0, rec.data(), b1, cudaMemcpyHostToDevice, e->stream), "H2D accel");
-    CU(cudaMemcpyAsync((char*)e->accel.p + b0 + b1, idx.data(), b2, cudaMemcpyHostToDevice, e->stream), "H2D accel");
+    CU(cudaMemcpyAsync((char*)e->accel.p + b0 + b1, idx.data(), (size_t)nc * K * 4, cudaMemcpyHostToDevice, e->stream), "H2D accel");
     CU(cudaStreamSynchronize(e->stream), "accel upload"); /* the vectors die with this frame */
     e->acc_nc = nc;
     return 0;
@@ -430,6 +452,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
         fp.acc_cl = (const float4*)e->accel.p;
         fp.acc_rec = (const float4*)((const char*)e->accel.p + b0);
         fp.acc_idx = (const uint32_t*)((const char*)e->accel.p + b0 + b1);
+        fp.acc_grp = (const float4*)((const char*)e->accel.p + b0 + b1 + ((size_t)e->acc_nc * RT_ACCEL_K * 4 + 15) / 16 * 16);
         fp.acc_nc = e->acc_nc;
     }
     /* a scene whose planes carry texture ids needs the texture array; without one, ids clamp onto a 1x1 dummy */
@@ -512,9 +535,11 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                         /* with the CTA-wide pixel-tree kernel beside render_frame (tools/exp/sweep_tree.py): tiles longer than
                          * 0.75 T go to it whole (4 warps on the tile's pooled segment trees), tiles longer than 3 T as four
                          * row entries (16 warps); single-pixel entries no longer pay */
-                        fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : thr(3.0, 44.0);
-                        fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : 64u;
-                        uint32_t t = e->opt_tree_min_cost > 0 ? (uint32_t)e->opt_tree_min_cost : thr(0.75, 32.0);
+                        /* (N4 scenes: a record walk is cheap there, so what is left of a frame is the segment chains of
+                         * its glass pixels -- up to 2^15 segments each: trees much earlier, rows and single pixels too) */
+                        fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : (use_accel ? thr(0.75, 40.0) : thr(3.0, 44.0));
+                        fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : (use_accel ? thr(3.0, 48.0) : 64u);
+                        uint32_t t = e->opt_tree_min_cost > 0 ? (uint32_t)e->opt_tree_min_cost : (use_accel ? thr(0.2, 32.0) : thr(0.75, 32.0));
                         if (fp.split_min_cost < t) t = fp.split_min_cost;
                         if (fp.split32_min_cost < t) t = fp.split32_min_cost;
                         fp.tree_min_cost = t;
@@ -555,7 +580,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
      * node's 1 + 2L addition slots stay small.  One slab per CTA of the persistent grid. */
     fp.tree_mode = 0;
     if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && ((fp.order && fp.tree_min_cost < 64u) || e->opt_tree >= 2)) {
-        const uint32_t cap = (uint32_t)e->opt_tree_cap;
+        const uint32_t cap = use_accel && e->opt_tree_cap == 8192 ? 32768u : (uint32_t)e->opt_tree_cap; /* N4 scenes: whole glass pixels */
         const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->opt_tree_ctas_per_sm; /* = the render_tree grid: one slab per CTA */
         const size_t records = rt_tree_slab_records(cap, e->L);
         if (e->tree_slab.ensure(records * 16 * slots) == 0) {

@@ -49,6 +49,7 @@ static inline size_t rt_tree_slab_records(uint32_t cap, uint32_t L) {
 
 /* N4 (rt_trace_accel.cuh): spheres per cluster of the acceleration structure */
 #define RT_ACCEL_K 8
+#define RT_ACCEL_G 8 /* clusters per group (second level) */
 
 struct RtFrameParams {
     /* raygen.cl:5-8 scalar arguments */
@@ -71,6 +72,7 @@ struct RtFrameParams {
     const float4* acc_rec;   /* [acc_nc * RT_ACCEL_K] {c.xyz, r*r} in cluster order, never-hit padding */
     const uint32_t* acc_idx; /* [acc_nc * RT_ACCEL_K] original sphere index | transperent << 31, 0xffffffff = padding */
     uint32_t acc_nc;
+    const float4* acc_grp;   /* [ceil(acc_nc / RT_ACCEL_G)] bounding sphere of RT_ACCEL_G consecutive clusters, same encoding */
     /* image arrays */
     const uchar4* tex; int tw, th, tl;
     const uchar4* sky; int sw, sh;

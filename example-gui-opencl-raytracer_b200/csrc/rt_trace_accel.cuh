@@ -30,6 +30,7 @@
 namespace RT_NS {
 
 constexpr uint32_t kAccK = RT_ACCEL_K; /* spheres per cluster (rt_kernels.h) */
+constexpr uint32_t kAccG = RT_ACCEL_G; /* clusters per group: a second level of bounding spheres over consecutive clusters */
 
 /* {C - o, slack-free}: true when no member of the cluster can yield a hit with 0 < t <= tmax (tmax = +inf: any t). */
 __device__ __forceinline__ bool accel_cull(const RayF& r, float a, float4 cl, float tmax) {
@@ -53,6 +54,11 @@ __device__ __forceinline__ bool closest_spheres_accel(const RayF& r, const Geo& 
     bool odd = false;
 #pragma unroll 1
     for (uint32_t k = 0; k < g.acc_nc; k++) {
+        /* what still matters: (computed again per cluster: c.t shrinks as hits come in) */
+        if ((k % kAccG) == 0u) { /* second level: the bounding sphere of the next kAccG clusters */
+            const float tm = (c.k >= 0 && c.tL > c.t) ? c.tL : c.t;
+            if (accel_cull(r, a, __ldg(g.acc_grp + k / kAccG), tm * 1.00001f)) { k += kAccG - 1u; continue; }
+        }
         const float4 cl = __ldg(g.acc_cl + k);
         /* what still matters: hits up to the closest so far (one at exactly c.t with a smaller index must still be seen)
          * and, when the ray has hit a light, every opaque sphere up to that light (its occlusion test) */
@@ -79,6 +85,7 @@ __device__ __forceinline__ bool shadow_spheres_accel(const RayF& r, float len, c
     bool blocked = false;
 #pragma unroll 1
     for (uint32_t k = 0; k < g.acc_nc && !blocked; k++) {
+        if ((k % kAccG) == 0u && accel_cull(r, a, __ldg(g.acc_grp + k / kAccG), len * 1.00001f)) { k += kAccG - 1u; continue; }
         const float4 cl = __ldg(g.acc_cl + k);
         if (accel_cull(r, a, cl, len * 1.00001f)) continue;
         blocked = for_sphere_hits(r, g.acc_rec, k * kAccK, (k + 1u) * kAccK, tl, [&](uint32_t j, float t1) {

@@ -17,6 +17,9 @@ tex, sky = host.default_images(ROOT)
 eng = pkg.Engine(0)
 eng.upload_scene(wl["spheres"], wl["planes"], wl["lights"]); eng.upload_images(0, tex); eng.upload_images(1, sky)
 eng.set_camera(wl["cam"])
+for kv in filter(None, os.environ.get("SWEEP_OPTS", "").split(",")):   # e.g. SWEEP_OPTS=accel=1
+    k, v = kv.split("=")
+    eng.set_option(k, int(v))
 if len(sys.argv) > 2:
     combos = [tuple(int(v) for v in c.split(":")) for c in sys.argv[2].split(",")]
 else:
