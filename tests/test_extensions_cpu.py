@@ -154,3 +154,67 @@ def test_triangle_batch_defers_the_zero_determinant_check():
             assert batch_rejects                          # hit_triangle: det == 0 -> no hit
             if not (a == 0 or np.isnan(a)):
                 assert fires                              # ... and the hot loop alone already says so
+
+
+def numpy_triangle_hit_ids(ref, tris, cam, W, H):
+    """A SECOND, independent pin for extension X1 (the reference has no triangle type, so this is still not reference
+    parity): the primary hit-id frame of a triangles-only scene computed here in vectorised IEEE binary32 numpy --
+    rays from the reference's own raygen.cl text (oracle/_ref), Moeller-Trumbore in the operation order of
+    mt_float32 above, closest hit = first of strictly smaller t in index order (primitives.cl:322-394's rule),
+    id = 1 + S + P + k with S = P = 0."""
+    f = np.float32
+    lib = ref.ref().lib
+    o = np.zeros((W * H, 3), f); d = np.zeros((W * H, 3), f)
+    fp = C.POINTER(C.c_float)
+    camf = np.ascontiguousarray(cam, f)
+    oo, dd = np.zeros(3, f), np.zeros(3, f)
+    for i in range(W * H):
+        lib.ref_raygen(camf.ctypes.data_as(fp), C.c_uint32(W), C.c_uint32(H), C.c_uint32(i), oo.ctypes.data_as(fp), dd.ctypes.data_as(fp))
+        o[i] = oo; d[i] = dd
+    T = len(tris) // 112
+    rec = np.frombuffer(tris, f).reshape(T, 28)
+    v0, v1, v2 = rec[:, 0:3], rec[:, 4:7], rec[:, 8:11]
+    dot = lambda a, b: (a[..., 0] * b[..., 0] + a[..., 1] * b[..., 1]) + a[..., 2] * b[..., 2]
+    cross = lambda a, b: np.stack([a[..., 1] * b[..., 2] - a[..., 2] * b[..., 1], a[..., 2] * b[..., 0] - a[..., 0] * b[..., 2],
+                                   a[..., 0] * b[..., 1] - a[..., 1] * b[..., 0]], axis=-1)
+    best_t = np.full(W * H, np.inf, f)
+    best_k = np.full(W * H, -1, np.int64)
+    with np.errstate(all="ignore"):
+        for k in range(T):                      # index order; strict improvement only
+            e1, e2 = (v1[k] - v0[k]).astype(f), (v2[k] - v0[k]).astype(f)
+            p = cross(d, e2[None, :])
+            det = dot(e1[None, :], p)
+            inv = f(1.0) / det
+            s = o - v0[k][None, :]
+            u = dot(s, p) * inv
+            q = cross(s, e1[None, :])
+            v = dot(d, q) * inv
+            t = dot(e2[None, :], q) * inv
+            hit = (det != 0) & ~((u < 0) | (u > 1)) & ~((v < 0) | (u + v > 1)) & ~(t <= 0)
+            better = hit & ~(t >= best_t)
+            best_t = np.where(better, t, best_t)
+            best_k = np.where(better, k, best_k)
+    assert o.dtype == f and d.dtype == f and best_t.dtype == f
+    return np.where(best_k >= 0, 1 + best_k, 0).astype(np.uint32)
+
+
+def triangle_pin_scene(host):
+    s, p, l, tris, camp = host.heightfield_mesh_scene(n=10)      # 200 triangles, mixed materials
+    return tris, camp
+
+
+def test_triangle_primary_hits_numpy_pin_vs_port(ref, scene, host):
+    """The port's primary hit ids on a triangles-only frame equal the numpy float32 restatement's (ties and all)."""
+    tris, camp = triangle_pin_scene(host)
+    W, H = 80, 45
+    cam = host.camera(W=W, H=H, **camp)
+    want = numpy_triangle_hit_ids(ref, tris, cam, W, H)
+    sc = ref.Scene(b"", b"", b"", scene.tex, scene.sky)          # no spheres, planes or lights: ids are 1 + k
+    port = ref.port()
+    port.set_triangles(tris)
+    try:
+        _, hit = port.render(sc, cam, W, H)
+    finally:
+        port.set_triangles(b"")
+    assert (want > 0).sum() > 500
+    assert np.array_equal(hit, want)

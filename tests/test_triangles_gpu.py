@@ -76,3 +76,22 @@ def test_triangles_only_and_removal(fresh, ref, scene, host):
     rgb, hit = fresh.render_to_host(W, H, want_hit=True)
     want_rgb, want_hit = ref.port().render(ref.Scene(b"", b"", bytes(scene.lights), scene.tex, scene.sky), cam, W, H)
     assert np.array_equal(hit, want_hit) and np.array_equal(rgb, want_rgb)
+
+
+def test_triangle_primary_hits_equal_the_numpy_pin(fresh, ref, scene, host):
+    """Second, independent judge for X1 (still not reference parity -- the reference has no triangles): the CUDA kernel's
+    primary hit ids on a triangles-only frame against vectorised float32 numpy Moeller-Trumbore over rays from the
+    reference's raygen.cl text (tests/test_extensions_cpu.py: numpy_triangle_hit_ids)."""
+    import test_extensions_cpu as ext
+    tris, camp = ext.triangle_pin_scene(host)
+    W, H = 80, 45
+    cam = host.camera(W=W, H=H, **camp)
+    want = ext.numpy_triangle_hit_ids(ref, tris, cam, W, H)
+    fresh.upload_scene(b"", b"", b"")
+    fresh.upload_triangles(tris)
+    fresh.set_camera(cam)
+    for tree in (1, 2):
+        fresh.set_option("tree", tree)
+        _, hit = fresh.render_to_host(W, H, want_hit=True)
+        assert np.array_equal(hit, want), tree
+    fresh.set_option("tree", 1)
