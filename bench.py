@@ -527,7 +527,9 @@ def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full"
     ms_per_step = total_ms / steps
     my_kernel_ms = float(np.mean(kernel_ms))
     achieved_tf = (my_flop if world > 1 else frame_flop) / (my_kernel_ms * 1e-3) / 1e12
-    launches_per_frame = 3 * world + (1 if exchange in ("nccl", "p2p") else 0)
+    # per frame and rank: tile_cost_history + tile_order + render_frame (+ render_tree when the frame has heavy tiles for it);
+    # on rank 0 + wait_flags (p2p) or assemble_bands (nccl)
+    launches_per_frame = (3 + (1 if eng.last_launch().get("tree_grid") else 0)) * world + (1 if exchange in ("nccl", "p2p") else 0)
     res = {
         "workload": wl["name"], "desc": wl["desc"], "width": W, "height": H, "steps": steps, "warmup": warmup,
         "ms_per_step": ms_per_step, "value": frame_rays / (ms_per_step * 1e-3) / 1e6, "unit": "Mrays/s",
@@ -535,7 +537,6 @@ def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full"
         "rays_per_frame": frame_rays, "algorithmic_flop_per_frame": frame_flop,
         "segments": int(totals[2]), "shadow_rays": int(totals[3]),
         "exchange": exchange, "frame_equals_1gpu": verified, "launch": eng.last_launch(), "clocks": clocks,
-        # per frame and rank: tile_cost(_history) + tile_order + render_frame; on rank 0 + wait_flags (p2p) or assemble_bands (nccl)
         "gpu_launches": steps * launches_per_frame,
         "kernel_ms": my_kernel_ms, "kernel_ms_slowest_rank": kern_max_ms,
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": ctx.peak_tf, "unit": "TFLOP/s",

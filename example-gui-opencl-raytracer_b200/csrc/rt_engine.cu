@@ -491,7 +491,8 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     if (rows == 0) { e->timed = false; return 0; }
 
     CU(cudaEventRecord(e->ev0, e->stream), "event record");
-    CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter");
+    const bool ordered = e->opt_tile_order && e->last.tiles >= 4096 && e->last.tiles < (1u << 24);
+    if (!ordered) CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter"); /* else tile_order zeroes it */
     fp.order = nullptr;
     fp.cost = nullptr;
     fp.coop_min_cost = (uint32_t)e->opt_coop_min_cost;
@@ -503,7 +504,9 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     /* queue entries carry the tile index in 24 bits (rt_kernels.cu): beyond 2^24 tiles (> 536 Mpixel) the queue stays row-major */
     if (e->opt_tile_order && e->last.tiles >= 4096 && e->last.tiles < (1u << 24)) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
+        const bool fresh_hist = e->tile_hist.p == nullptr;
         if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 128) || e->tile_hist.ensure(1024)) return -2;
+        if (fresh_hist) CU(cudaMemsetAsync(e->tile_hist.p, 0, 1024, e->stream), "zero tile histogram"); /* once: tile_order leaves it clean */
         /* scheduling hint: the previous frame's measured tile times when it had this geometry and scene (the camera may
          * have moved: frames of an interactive sweep are coherent), else the skeleton trace.  Pixels never depend on it. */
         const bool same = e->time_valid && e->tk_W == W && e->tk_H == H && e->tk_total == total && e->tk_band == pp.band_rows &&
@@ -513,7 +516,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
             if (e->tile_time[0].ensure(nt * 4 + 16) || e->tile_time[1].ensure(nt * 4 + 16)) return -2;
             fp.tile_time_sum = (unsigned long long*)e->tile_time[e->time_cur].p;
             fp.tile_time = (uint32_t*)((char*)e->tile_time[e->time_cur].p + 16);
-            CU(cudaMemsetAsync(e->tile_time[e->time_cur].p, 0, nt * 4 + 16, e->stream), "reset tile times");
+            if (!same) CU(cudaMemsetAsync(e->tile_time[e->time_cur].p, 0, nt * 4 + 16, e->stream), "reset tile times"); /* history frames: tile_cost_history zeroes it */
             if (same) {
                 fp.tile_time_sum_prev = (const unsigned long long*)e->tile_time[1 - e->time_cur].p;
                 fp.tile_time_prev = (const uint32_t*)((const char*)e->tile_time[1 - e->time_cur].p + 16);

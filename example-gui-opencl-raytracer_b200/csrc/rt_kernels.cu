@@ -519,11 +519,15 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
 __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsigned long long* __restrict__ prev_sum,
                                   uint32_t* __restrict__ cost_out,
                                   uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost, uint32_t split32_min_cost,
-                                  uint32_t sticky_cost) {
+                                  uint32_t sticky_cost, uint32_t* __restrict__ time_now /* 4 header words + ntiles: zeroed here instead of by a memset */) {
     __shared__ uint32_t shist[kCostBuckets];
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) shist[i] = 0;
     __syncthreads();
     const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (time_now) {
+        if (tile < 4u) time_now[tile] = 0u;
+        if (tile < ntiles) time_now[4u + tile] = 0u;
+    }
     if (tile < ntiles) {
         const float mean = fmaxf((float)(*prev_sum) / (float)ntiles, 1.0f);
         const float rel = 24.0f + 4.0f * __log2f(fmaxf((float)prev[tile], 0.5f) / mean);
@@ -549,8 +553,11 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsig
  * One global atomic per (block, bucket): ranks inside a block come from shared-memory atomics. */
 __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __restrict__ hist,
                            uint32_t* __restrict__ cursor, uint32_t* __restrict__ order, uint32_t ntiles,
-                           uint32_t split_min_cost, uint32_t split32_min_cost, uint32_t first_heavy, uint32_t* __restrict__ queue_len) {
+                           uint32_t split_min_cost, uint32_t split32_min_cost, uint32_t first_heavy, uint32_t* __restrict__ queue_len,
+                           uint32_t* __restrict__ sched /* 64 words: the render kernels' cursors and counters, zeroed here */) {
     __shared__ uint32_t base[kCostBuckets], local[kCostBuckets], gbase[kCostBuckets];
+    __shared__ bool last_block;
+    if (sched && blockIdx.x == 0 && threadIdx.x < 64u) sched[threadIdx.x] = 0u;
     for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) local[i] = 0;
     if (threadIdx.x == 0) {
         uint32_t acc = 0, nheavy = 0;
@@ -580,6 +587,18 @@ __global__ void tile_order(const uint32_t* __restrict__ cost, const uint32_t* __
         } else if (ways == 4u) { /* a heavy tile is dealt to four warps, one tile row (8 pixels + 24 helper lanes) each */
             o[0] = tile | (1u << 24); o[1] = tile | (2u << 24); o[2] = tile | (3u << 24); o[3] = tile | (4u << 24);
         } else o[0] = tile;
+    }
+    /* leave the histogram and the cursors clean for the next frame (no memset per frame): the last block to get here */
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        last_block = atomicAdd(queue_len + 2, 1u) + 1u == gridDim.x;
+    }
+    __syncthreads();
+    if (last_block) {
+        uint32_t* h = const_cast<uint32_t*>(hist);
+        for (uint32_t i = threadIdx.x; i < kCostBuckets; i += blockDim.x) { h[i] = 0u; cursor[i] = 0u; }
+        if (threadIdx.x == 0) queue_len[2] = 0u;
     }
 }
 
@@ -790,16 +809,19 @@ cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* 
 cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                  cudaStream_t st) {
     const uint32_t ntiles = fp.tiles_x * fp.tiles_y;
-    cudaError_t e = cudaMemsetAsync(d_hist_cursor, 0, (2 * kCostBuckets + 2) * sizeof(uint32_t), st);
-    if (e != cudaSuccess) return e;
+    /* d_hist_cursor: [64 histogram][64 cursors][queue length][heavy prefix][ticket]; zeroed once by the engine, left clean by
+     * every tile_order.  fp.tile_time (history frames) and the 256-byte sched block are zeroed by these kernels too. */
+    cudaError_t e = cudaSuccess;
     const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
     if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost,
-                                                                                  fp.cost_is_history ? fp.tree_min_cost : kCostBuckets);
+                                                                                  fp.cost_is_history ? fp.tree_min_cost : kCostBuckets,
+                                                                                  fp.tile_time ? reinterpret_cast<uint32_t*>(fp.tile_time_sum) : nullptr);
     else tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     tile_order<<<(ntiles + 255) / 256, 256, 0, st>>>(d_cost, d_hist_cursor, d_hist_cursor + kCostBuckets, d_order, ntiles,
-                                                    fp.split_min_cost, fp.split32_min_cost, fp.tree_min_cost, d_hist_cursor + 2 * kCostBuckets);
+                                                    fp.split_min_cost, fp.split32_min_cost, fp.tree_min_cost, d_hist_cursor + 2 * kCostBuckets,
+                                                    reinterpret_cast<uint32_t*>(fp.tile_counter));
     return cudaGetLastError();
 }
 
