@@ -94,9 +94,14 @@ __device__ __forceinline__ void store_tile(const RtFrameParams& fp, const TileLa
  * publishes the frame number. */
 __device__ __forceinline__ void signal_done(const RtFrameParams& fp) {
     if (fp.done_flag) {
-        __threadfence_system();
+        /* The CTA's frame stores are ordered before the barrier; thread 0's fence after it is cumulative (PTX memory
+         * model), so one fence per CTA publishes them all -- at DEVICE scope: the counter is a device-scope atomic, and
+         * the one system-scope fence the peer / host needs is the last CTA's, before its release store (cumulative again
+         * over everything the counter chain made visible to it).  A system-scope fence per CTA cost 0.2 ms per frame once
+         * render_tree's CTAs executed theirs in the middle of render_frame's run (tools/exp/n2_probe.py). */
         __syncthreads();
         if (threadIdx.x == 0) {
+            __threadfence();
             const unsigned int prev = atomicAdd(fp.done_counter, 1u);
             if (prev + 1u == fp.done_expected) {
                 __threadfence_system();
