@@ -28,7 +28,7 @@ ENGINE_SYMBOLS = (
     "rtb_upload_triangles", "rtb_bind_triangles_device", "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
-    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_set_mirror_frame", "rtb_set_completion", "rtb_wait_flags", "rtb_wait_timeouts", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close", "rtb_assemble_bands", "rtb_last_launch", "rtb_debug_counters", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
+    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_set_mirror_frame", "rtb_set_completion", "rtb_wait_flags", "rtb_wait_timeouts", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close", "rtb_assemble_bands", "rtb_last_launch", "rtb_render_noalloc", "rtb_debug_counters", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
 )
 WRAP_SYMBOLS = (
     "cl_wrap_init", "cl_wrap_load_global_data", "cl_wrap_load_single_data", "cl_wrap_load_images", "cl_wrap_output",
@@ -83,6 +83,7 @@ def lib():
             "rtb_partition_rows": (u32, [u32, pp]),
             "rtb_render": (i, [vp, u32, u32, u32, pp, vp, vp, i]),
             "rtb_render_counted": (i, [vp, u32, u32, u32, pp, vp, vp, i, i, C.POINTER(C.c_uint64)]),
+            "rtb_render_noalloc": (i, [vp, C.POINTER(C.c_float), u32, u32, u32, pp, vp, vp]),
             "rtb_set_option": (i, [vp, C.c_char_p, i]),
             "rtb_selftest_arith": (i, [vp, u32, u32, C.POINTER(u32)]),
             "rtb_last_kernel_ms": (C.c_float, [vp]),
@@ -211,6 +212,19 @@ class Engine:
         c["rays"] = c["segments"] + c["shadow_rays"]
         c["flop"] = algorithmic_flop(c)
         return c
+
+    def render_noalloc(self, W, H, d_out, cam=None, total=None, part=None, d_hit=None):
+        """rtb_render_noalloc: one frame into the caller's device buffers without any allocation (static device scratch;
+        at most 262,144 tiles per call).  Asynchronous on the engine's stream."""
+        total = W * H if total is None else total
+        c = None
+        if cam is not None:
+            c = np.ascontiguousarray(cam, np.float32)
+            if c.size != 14:
+                raise ValueError("camera is 14 floats")
+            c = c.ctypes.data_as(C.POINTER(C.c_float))
+        _check(lib().rtb_render_noalloc(self._h, c, W, H, total, C.byref(part) if part is not None else None, d_out, d_hit),
+               "rtb_render_noalloc")
 
     def set_mirror_frame(self, d_frame):
         """The next render also stores every word at d_frame[y*W + x] (a full frame, typically a peer GPU's)."""

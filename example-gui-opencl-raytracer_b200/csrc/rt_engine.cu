@@ -82,6 +82,7 @@ struct rtb_engine {
     DevBuf tree_slab;         /* per-warp node storage of the level-wise pixel-tree trace (rt_trace_tree.cuh) */
     DevBuf jump;              /* [15][32] xorshift32 jump-ahead matrices for this scene's light count */
     uint32_t jump_L = 0xffffffffu;
+    uint32_t* noalloc_scratch = nullptr; /* device address of g_noalloc_scratch on this engine's device (rtb_render_noalloc) */
     int opt_tree_ctas_per_sm = 3;
     int opt_accel = 0;        /* N4: 1 = many-sphere scenes walk the cluster structure instead of every record */
     DevBuf accel;             /* clusters, cluster-ordered records, original indices */
@@ -852,6 +853,107 @@ double rtb_fp32_peak_tflops(rtb_engine* e, int iters) {
     cudaEventDestroy(a);
     cudaEventDestroy(b);
     return best;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * rtb_render_noalloc -- one frame without a single allocation (no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).
+ *
+ * The render kernel's scheduling scratch -- the 256-byte cursor block of render_frame, the histogram / cursors of
+ * tile_order, one cost word and one queue entry per 8x4 tile -- lives in ONE file-scope device array instead of the
+ * engine's cudaMalloc'ed buffers.  Every GPU that loads the library holds its 2.0 MiB until exit.  In host code the
+ * array's NAME is a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress, once per
+ * engine, with the engine's device current.  Every call on a device shares the array: calls that overlap on the GPU
+ * (two engines of one device, two streams) RACE; the header words that must start at zero are cleared by a kernel at the
+ * head of every call (the array keeps the last call's contents).
+ * ------------------------------------------------------------------------------------------------------------------- */
+#define RTB_NOALLOC_MAX_TILES 262144u /* 8x4-pixel tiles: 8,388,608 pixels in whole tiles (3840x2160 = 259,200 tiles fits) */
+#define RTB_NOALLOC_HEADER_WORDS 320u /* 64 words cursor block (tile / tree / done counters, work counters) + 256 words tile_order scratch */
+static __device__ __align__(256) uint32_t g_noalloc_scratch[RTB_NOALLOC_HEADER_WORDS + 2u * RTB_NOALLOC_MAX_TILES];
+
+/* device code may name the array directly: clear what must start at zero */
+static __global__ void noalloc_reset() {
+    for (uint32_t i = threadIdx.x; i < RTB_NOALLOC_HEADER_WORDS; i += blockDim.x) g_noalloc_scratch[i] = 0u;
+}
+
+int rtb_render_noalloc(rtb_engine* e, const float cam[14], uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part,
+                       uint32_t* d_out, uint32_t* d_hit) {
+    if (!e) return fail(-1, "null engine");
+    if (!e->have_scene) return fail(-1, "rtb_render_noalloc: no scene uploaded");
+    if (!cam && !e->have_cam) return fail(-1, "rtb_render_noalloc: no camera given and none set");
+    if (!e->d_sky) return fail(-1, "rtb_render_noalloc: no skybox image uploaded (kernel arg 9)");
+    if (!W || !H) return fail(-1, "rtb_render_noalloc: empty frame");
+    if ((uint64_t)W * H > 0xffffffffull) return fail(-1, "rtb_render_noalloc: W*H exceeds the 32-bit pixel id (raygen.cl:10)");
+    if (!d_out) return fail(-1, "rtb_render_noalloc: the caller passes the output buffer (this call allocates nothing)");
+    if (((uintptr_t)d_out & 15) || ((uintptr_t)d_hit & 15)) return fail(-1, "rtb_render_noalloc: output buffers must be 16-byte aligned");
+    rtb_partition whole = {H, 1, 0};
+    rtb_partition pp = part ? *part : whole;
+    if (pp.parts <= 1) { pp.parts = 1; pp.part = 0; pp.band_rows = H; }
+    if (!pp.band_rows || pp.part >= pp.parts) return fail(-1, "rtb_render_noalloc: bad partition");
+    const uint32_t rows = rtb_partition_rows(H, &pp);
+    const uint64_t tiles = (uint64_t)((W + 7) / 8) * ((rows + 3) / 4);
+    if (tiles > RTB_NOALLOC_MAX_TILES) {
+        snprintf(g_err, sizeof g_err, "rtb_render_noalloc: %llu tiles of 8x4 pixels exceed the static scratch (%u tiles = 8,388,608 pixels; "
+                 "3840x2160 fits): use rtb_render, or split the frame with an rtb_partition", (unsigned long long)tiles, RTB_NOALLOC_MAX_TILES);
+        return -1;
+    }
+    CU(cudaSetDevice(e->device), "cudaSetDevice");
+    if (!e->noalloc_scratch) { /* once per engine (= per device), with that device current */
+        uint32_t* ptr = nullptr;
+        CU(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch), "cudaGetSymbolAddress(g_noalloc_scratch)");
+        if (!ptr) return fail(-2, "rtb_render_noalloc: cudaGetSymbolAddress returned a null address");
+        e->noalloc_scratch = ptr;
+    }
+    if (rows == 0) return 0;
+    const float* cm = cam ? cam : e->cam;
+
+    RtFrameParams fp;
+    memset(&fp, 0, sizeof fp);
+    memcpy(fp.corner, cm + 0, 12); memcpy(fp.origin, cm + 3, 12);
+    memcpy(fp.up, cm + 6, 12); memcpy(fp.right, cm + 9, 12);
+    fp.wf = cm[12]; fp.hf = cm[13];
+    fp.W = W; fp.H = H; fp.total = total;
+    fp.band_rows = pp.band_rows; fp.parts = pp.parts; fp.part = pp.part; fp.local_rows = rows;
+    fp.S = e->S; fp.P = e->P; fp.L = e->L; fp.lay = e->lay;
+    fp.blob = (const float4*)e->blob.p;
+    fp.raw_spheres = e->d_spheres; fp.raw_planes = e->d_planes;
+    fp.T = e->T; fp.tri = (const float4*)e->tri_rec.p; fp.raw_tris = e->d_tris;
+    fp.tex = (const uchar4*)(e->d_tex ? e->d_tex : e->d_sky);
+    fp.tw = e->d_tex ? (int)e->tw : 1; fp.th = e->d_tex ? (int)e->th : 1; fp.tl = e->d_tex ? (int)e->tl : 1;
+    fp.sky = (const uchar4*)e->d_sky; fp.sw = (int)e->sw; fp.sh = (int)e->sh;
+    fp.out = d_out;
+    fp.hit = d_hit;
+    fp.tiles_x = (W + 7) / 8;
+    fp.tiles_y = (rows + 3) / 4;
+    /* scratch: [0, 64) cursor block, [64, 320) tile_order's histogram / cursors / queue length, then costs, then the queue */
+    uint32_t* const base = e->noalloc_scratch;
+    uint32_t* const hist = base + 64;
+    uint32_t* const cost = base + RTB_NOALLOC_HEADER_WORDS;
+    uint32_t* const order = cost + RTB_NOALLOC_MAX_TILES;
+    fp.tile_counter = (unsigned int*)base;
+    fp.tree_counter = (unsigned int*)(base + 1);
+    fp.done_counter = (unsigned int*)(base + 8);
+    fp.counters = (unsigned long long*)(base + 16);
+    fp.coop_min_cost = (uint32_t)e->opt_coop_min_cost;
+    fp.wide_min_records = (uint32_t)e->opt_wide_min_records;
+    fp.wide_max_live = e->opt_wide_max_live;
+    /* the skeleton-trace schedule of a first frame: every tile once, heaviest first; no measured-time history, no split
+     * entries, no pixel-tree kernel (those need per-frame buffers) -- a scheduling difference only, the words are the same */
+    fp.split_min_cost = 64u;
+    fp.split32_min_cost = 64u;
+    fp.tree_min_cost = 64u;
+    fp.tree_mode = 0;
+    noalloc_reset<<<1, 320, 0, e->stream>>>();
+    CU(cudaGetLastError(), "noalloc_reset launch");
+    CU((e->T ? rt_launch_tile_order_tri : rt_launch_tile_order)(fp, cost, hist, order, e->stream), "tile_order launch");
+    fp.order = order;
+    fp.cost = cost;
+    fp.queue_len = hist + 128;
+    fp.n_split = hist + 129;
+    RtLaunchShape shape{};
+    CU((e->T ? rt_launch_render_tri : rt_launch_render)(fp, 0, e->sm_count, e->stream, &shape), "render_frame launch");
+    return 0;
 }
 
 }  // extern "C"

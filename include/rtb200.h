@@ -201,6 +201,23 @@ void rtb_map_free(rtb_map* m);
 
 /* Diagnostic builds only (e.g. -DRT_TREE_CLOCKS): the raw counter words the last launch left behind. */
 int rtb_debug_counters(rtb_engine* e, uint64_t out[RTB_NCOUNTERS]);
+/* rtb_render_noalloc -- NO COUNTERPART IN THE REFERENCE; added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Renders one frame of the
+ * engine's resident scene and image arrays (uploaded / bound earlier) with camera `cam` (the 14 floats of rtb_set_camera;
+ * NULL = the latched camera) into the CALLER's device buffers d_out (rows*W words, required) and d_hit (optional), on
+ * the engine's stream, asynchronously.  The call itself performs no cudaMalloc / cudaFree / allocating library call: the
+ * scheduling scratch of the render kernel (cursor block, tile costs, the cost-ordered tile queue) lives in a file-scope
+ * `static __device__` array of 2.0 MiB that every GPU loading the library holds until exit.
+ * LIMIT: at most 262,144 tiles of 8x4 pixels per call (8,388,608 pixels; 3840x2160 fits) -- larger frames are rejected
+ * (-1, rtb_last_error says so): use rtb_render, or split the frame with a partition.
+ * The frame is scheduled like a first frame (skeleton trace, no measured-time history, no pixel-tree kernel); the words
+ * are those of rtb_render.  One-shot mirror / completion settings are neither used nor consumed.
+ * Every call on a device shares the one array (it keeps the last call's contents; the words that must start at zero
+ * are cleared at the head of each call): calls that OVERLAP on the GPU -- two engines on one device, two streams --
+ * race on it.  Serialise them. */
+int rtb_render_noalloc(rtb_engine* e, const float cam[14], uint32_t W, uint32_t H, uint32_t total, const rtb_partition* part,
+                       uint32_t* d_out, uint32_t* d_hit);
+
 /* Launch geometry the renderer chose for the last frame (for bench.py's accounting). */
 typedef struct {
     uint32_t grid, block, smem_bytes, tiles, resident_scene; /* resident_scene: 1 = geometry staged in shared memory */
