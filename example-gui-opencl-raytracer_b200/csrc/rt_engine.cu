@@ -543,7 +543,11 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                          * its glass pixels -- up to 2^15 segments each: trees much earlier, rows and single pixels too) */
                         fp.split_min_cost = e->opt_split_min_cost > 0 ? (uint32_t)e->opt_split_min_cost : (use_accel ? thr(0.75, 40.0) : thr(3.0, 44.0));
                         fp.split32_min_cost = e->opt_split32_min_cost > 0 ? (uint32_t)e->opt_split32_min_cost : (use_accel ? thr(3.0, 48.0) : 64u);
-                        uint32_t t = e->opt_tree_min_cost > 0 ? (uint32_t)e->opt_tree_min_cost : (use_accel ? thr(0.2, 32.0) : thr(0.75, 32.0));
+                        /* (tools/exp/sweep_tree_fine.py, slowest part's kernels: N=4 0.785 -> 0.764 ms with trees from 0.55 T
+                         * instead of 0.75 T, never below cost 36; halves and whole frames keep 0.75 T, where the tree
+                         * kernel only costs: N=2 1.36 ms either way from cost 44, N=1 2.66 -> 3.1 ms from cost 44) */
+                        uint32_t t = e->opt_tree_min_cost > 0 ? (uint32_t)e->opt_tree_min_cost
+                                     : (use_accel ? thr(0.2, 32.0) : (pp.parts >= 3 ? thr(0.55, 36.0) : thr(0.75, 36.0)));
                         if (fp.split_min_cost < t) t = fp.split_min_cost;
                         if (fp.split32_min_cost < t) t = fp.split32_min_cost;
                         fp.tree_min_cost = t;
