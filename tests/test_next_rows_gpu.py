@@ -149,3 +149,39 @@ def test_scene_larger_than_shared_memory(pkg, ref, scene, host, fresh, wide):
     rgb, hit = fresh.render_to_host(W, H, want_hit=True)
     assert fresh.last_launch()["resident_scene"] == 0
     judge_frame(ref, rgb, hit, want_rgb, want_hit, W, H, "6,561 spheres, non-resident, wide=%s" % wide)
+
+
+def test_completion_word_and_wait_kernel(pkg, ref, scene, fresh):
+    """the completion signal fused into the render (rtb_set_completion: the last CTA of the frame's
+    kernels release-stores the frame number) and the gathering rank's wait kernel (rtb_wait_flags), on one GPU: the flag
+    word carries the value once the stream has drained, with and without the pixel-tree kernel beside render_frame; a
+    flag that never arrives ends in a counted timeout (~2 s), not a hung GPU."""
+    W, H = 1024, 512
+    fresh.upload_scene(scene.spheres, scene.planes, scene.lights)
+    fresh.set_camera(ref.camera(W=W, H=H, **ref.RAYPNG_CAMERA))
+    want, _ = fresh.render_to_host(W, H, want_hit=False)
+    buf = fresh.dev_alloc(W * H * 4 + 4096)
+    flags = buf.value + W * H * 4
+    fresh.dev_write(buf, np.zeros(W * H + 1024, np.uint32))
+    part = pkg.Partition(8, 8, 3)                      # a part small enough for the tree kernel's automatic threshold
+    rows = fresh.partition_rows(H, part)
+    frame_no = 0
+    for tree in (1, 0):
+        fresh.set_option("tree", tree)
+        for rep in range(3):
+            frame_no += 1
+            fresh.set_mirror_frame(buf.value)          # full-frame mirror, global pixel ids
+            fresh.set_completion(flags + 64 * 2, frame_no)
+            fresh.render(W, H, part=part)
+            fresh.wait_flags(flags + 64 * 2, 16, 1, frame_no)
+            fresh.sync()
+            got = fresh.dev_read(buf, W * H * 4 + 4096).view(np.uint32)
+            assert int(got[W * H + 32]) == frame_no
+            y = np.arange(H)
+            mine = (y // 8) % 8 == 3
+            assert np.array_equal(got[:W * H].reshape(H, W)[mine], want.reshape(H, W)[mine]), (tree, rep)
+    fresh.set_option("tree", 1)
+    assert fresh.wait_timeouts() == 0
+    fresh.wait_flags(flags + 64 * 5, 16, 1, 7)         # nobody ever writes this word
+    assert fresh.wait_timeouts() == 1
+    fresh.dev_free(buf)
