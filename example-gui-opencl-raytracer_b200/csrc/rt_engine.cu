@@ -172,16 +172,19 @@ static uint32_t bm_apply(const uint32_t* col, uint32_t x) {
     for (int i = 0; i < 32; i++) if ((x >> i) & 1u) r ^= col[i];
     return r;
 }
-static int prep_jump(rtb_engine* e) {
-    if (e->jump_L == e->L && e->jump.p) return 0;
-    uint32_t tab[15][32];
+static void build_jump_table(uint32_t L, uint32_t tab[15][32]) {
     for (int i = 0; i < 32; i++) {
         uint32_t x = 1u << i;
-        for (uint32_t d = 0; d < 4u * e->L; d++) x = xs_step(x);
+        for (uint32_t d = 0; d < 4u * L; d++) x = xs_step(x);
         tab[0][i] = x;
     }
     for (int j = 1; j < 15; j++)
         for (int i = 0; i < 32; i++) tab[j][i] = bm_apply(tab[j - 1], tab[j - 1][i]);
+}
+static int prep_jump(rtb_engine* e) {
+    if (e->jump_L == e->L && e->jump.p) return 0;
+    uint32_t tab[15][32];
+    build_jump_table(e->L, tab);
     if (e->jump.ensure(sizeof tab)) return -2;
     CU(cudaMemcpyAsync(e->jump.p, tab, sizeof tab, cudaMemcpyHostToDevice, e->stream), "H2D jump table");
     CU(cudaStreamSynchronize(e->stream), "jump table upload"); /* tab is on this stack frame */
@@ -199,9 +202,15 @@ static uint32_t morton10(uint32_t v) { /* spread 10 bits to every third position
     v = (v | (v << 2)) & 0x09249249u;
     return v;
 }
-static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
-    e->acc_nc = 0;
-    const uint32_t S = e->S, K = RT_ACCEL_K;
+struct AccelHost {
+    std::vector<float> cl, rec, grp;
+    std::vector<uint32_t> idx;
+    uint32_t nc = 0, ng = 0;
+};
+/* host part: 1 = built, 0 = this scene is walked by brute force (too few spheres, a non-finite sphere, huge extents) */
+static int build_accel_host(const unsigned char* host_spheres, uint32_t S, AccelHost& out) {
+    const uint32_t K = RT_ACCEL_K;
+    out.nc = out.ng = 0;
     if (S < 2u * K || !host_spheres) return 0;
     std::vector<double> cx(S), cy(S), cz(S), rr(S);
     double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
@@ -228,8 +237,11 @@ static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
     }
     std::sort(order.begin(), order.end());
     const uint32_t nc = (S + K - 1) / K;
-    std::vector<float> cl(4 * (size_t)nc), rec(4 * (size_t)nc * K);
-    std::vector<uint32_t> idx((size_t)nc * K, 0xffffffffu);
+    std::vector<float>&cl = out.cl, &rec = out.rec, &grp = out.grp;
+    std::vector<uint32_t>& idx = out.idx;
+    cl.assign(4 * (size_t)nc, 0.0f);
+    rec.assign(4 * (size_t)nc * K, 0.0f);
+    idx.assign((size_t)nc * K, 0xffffffffu);
     for (uint32_t k = 0; k < nc; k++) {
         const uint32_t b = k * K, n = (b + K <= S ? K : S - b);
         double mx = 0, my = 0, mz = 0;
@@ -264,7 +276,7 @@ static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
     }
     /* second level: one bounding sphere per RT_ACCEL_G consecutive clusters, around their member spheres */
     const uint32_t ng = (nc + RT_ACCEL_G - 1) / RT_ACCEL_G;
-    std::vector<float> grp(4 * (size_t)ng);
+    grp.assign(4 * (size_t)ng, 0.0f);
     for (uint32_t q = 0; q < ng; q++) {
         const uint32_t b = q * RT_ACCEL_G * K, end = (b + RT_ACCEL_G * K < S ? b + RT_ACCEL_G * K : S), n = end - b;
         double mx = 0, my = 0, mz = 0;
@@ -282,6 +294,17 @@ static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
         if (!(w < 1e37)) return 0;
         grp[4 * q + 0] = C[0]; grp[4 * q + 1] = C[1]; grp[4 * q + 2] = C[2]; grp[4 * q + 3] = nextafterf((float)w, INFINITY);
     }
+    out.nc = nc;
+    out.ng = ng;
+    return 1;
+}
+static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
+    e->acc_nc = 0;
+    AccelHost h;
+    if (build_accel_host(host_spheres, e->S, h) != 1) return 0;
+    const uint32_t K = RT_ACCEL_K, nc = h.nc, ng = h.ng;
+    std::vector<float>&cl = h.cl, &rec = h.rec, &grp = h.grp;
+    std::vector<uint32_t>& idx = h.idx;
     const size_t b0 = (size_t)nc * 16, b1 = (size_t)nc * K * 16, b2 = ((size_t)nc * K * 4 + 15) / 16 * 16, b3 = (size_t)ng * 16;
     if (e->accel.ensure(b0 + b1 + b2 + b3)) return -2;
     CU(cudaMemcpyAsync((char*)e->accel.p + b0 + b1 + b2, grp.data(), b3, cudaMemcpyHostToDevice, e->stream), "H2D accel");
@@ -822,6 +845,29 @@ int rtb_host_unregister(void* host) {
     return 0;
 }
 
+/* Host-only views of what the engine builds at upload time (no GPU needed): for the CPU tests. */
+int rtb_debug_jump_table(uint32_t L, uint32_t out[480]) {
+    if (!out) return fail(-1, "rtb_debug_jump_table: null argument");
+    uint32_t tab[15][32];
+    build_jump_table(L, tab);
+    memcpy(out, tab, sizeof tab);
+    return 0;
+}
+int rtb_debug_accel_build(const void* spheres, uint32_t S, float* clusters, float* records, uint32_t* index, float* groups,
+                          uint32_t* n_clusters, uint32_t* n_groups) {
+    if (!n_clusters || !n_groups) return fail(-1, "rtb_debug_accel_build: null argument");
+    AccelHost h;
+    const int built = build_accel_host((const unsigned char*)spheres, S, h);
+    *n_clusters = h.nc;
+    *n_groups = h.ng;
+    if (built == 1) {
+        if (clusters) memcpy(clusters, h.cl.data(), h.cl.size() * 4);
+        if (records) memcpy(records, h.rec.data(), h.rec.size() * 4);
+        if (index) memcpy(index, h.idx.data(), h.idx.size() * 4);
+        if (groups) memcpy(groups, h.grp.data(), h.grp.size() * 4);
+    }
+    return built;
+}
 int rtb_debug_counters(rtb_engine* e, uint64_t out[RTB_NCOUNTERS]) {
     if (!e || !out) return fail(-1, "rtb_debug_counters: null argument");
     CU(cudaSetDevice(e->device), "cudaSetDevice");

@@ -199,6 +199,15 @@ int rtb_map_load(const char* path, rtb_map* out);
 int rtb_map_save(const char* path, const rtb_map* m, int version);
 void rtb_map_free(rtb_map* m);
 
+/* Host-only views (no GPU needed; CPU tests) of two things the engine builds at upload time:
+ * the xorshift32 jump-ahead table of the pixel-tree kernel -- out[j*32 + i] = image of bit i under (step^(4L))^(2^j), j < 15
+ * (primitives.cl:111-125 is linear over GF(2); raytracing.cl:96-113 draws 4L numbers per shaded segment) --
+ * and the N4 cluster structure over a wire sphere array: clusters[4*nc] {C, 1.125 R'^2}, records[4*8*nc] {c, r*r} in
+ * cluster order, index[8*nc] (original index | transperent << 31, 0xffffffff = padding), groups[4*ng]; nc = ceil(S/8),
+ * ng = ceil(nc/8); array pointers may be NULL.  Returns 1 when built, 0 when the scene stays brute force. */
+int rtb_debug_jump_table(uint32_t L, uint32_t out[480]);
+int rtb_debug_accel_build(const void* spheres, uint32_t S, float* clusters, float* records, uint32_t* index, float* groups,
+                          uint32_t* n_clusters, uint32_t* n_groups);
 /* Diagnostic builds only (e.g. -DRT_TREE_CLOCKS): the raw counter words the last launch left behind. */
 int rtb_debug_counters(rtb_engine* e, uint64_t out[RTB_NCOUNTERS]);
 /* rtb_render_noalloc -- NO COUNTERPART IN THE REFERENCE; added for callers that

@@ -306,3 +306,70 @@ def test_two_rank_band_gather_rebuilds_the_frame():
                         "--master-addr", "127.0.0.1", "--master-port", "29617", path, ROOT],
                        capture_output=True, timeout=300)
     assert r.returncode == 0, r.stderr.decode()[-2000:]
+
+
+def test_engine_jump_table_equals_stepping(pkg):
+    """rt_engine.cu: build_jump_table -- the GF(2) matrices the pixel-tree kernel multiplies to reach the RNG state of the
+    k-th shaded segment, xorshift32^(4L*k)(pixel id) (primitives.cl:111-125; 4L draws per segment, raytracing.cl:96-113):
+    applying the matrices of k's set bits to a seed equals stepping the generator 4L*k times."""
+    L_ = pkg.lib()
+    rng = np.random.default_rng(5)
+
+    def step(x):
+        x ^= (x << 13) & 0xFFFFFFFF
+        x ^= x >> 17
+        x ^= (x << 5) & 0xFFFFFFFF
+        return x
+    for nl in (0, 1, 3, 7, 16):
+        tab = (C.c_uint32 * 480)()
+        assert L_.rtb_debug_jump_table(nl, tab) == 0
+        tab = np.array(tab, np.uint64).reshape(15, 32)
+        for seed in [0, 1, 479999, 0xFFFFFFFF] + [int(v) for v in rng.integers(0, 2**32, 6)]:
+            for k in (0, 1, 2, 5, 166, 1023):
+                want = seed
+                for _ in range(4 * nl * k):
+                    want = step(want)
+                got = seed
+                for j in range(15):
+                    if (k >> j) & 1:
+                        r = 0
+                        for i in range(32):
+                            if (got >> i) & 1:
+                                r ^= int(tab[j][i])
+                        got = r
+                assert got == want, (nl, seed, k)
+
+
+def test_accel_structure_contains_its_spheres(pkg):
+    """rt_engine.cu: build_accel_host -- every sphere appears exactly once, with its r*r as one float32
+    product and its transparency bit; it lies inside its cluster's bounding sphere and its group's (w = 1.125 R'^2, so
+    dist + r <= sqrt(w / 1.125)); padding never hits; a non-finite sphere or a tiny scene is left to brute force."""
+    from example_gui_opencl_raytracer_b200 import host
+    L_ = pkg.lib()
+    for n_side in (4, 9, 32):
+        s, _, _, _ = host.sphere_grid_scene(n_side)
+        S = len(s) // 96
+        nc, ng = C.c_uint32(), C.c_uint32()
+        cap_c = (S + 7) // 8
+        cl = np.zeros(4 * cap_c, np.float32); rec = np.zeros(32 * cap_c, np.float32)
+        idx = np.zeros(8 * cap_c, np.uint32); grp = np.zeros(4 * ((cap_c + 7) // 8), np.float32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        built = L_.rtb_debug_accel_build(s, S, vp(cl), vp(rec), vp(idx), vp(grp), C.byref(nc), C.byref(ng))
+        assert built == 1 and nc.value == cap_c and ng.value == (cap_c + 7) // 8
+        wire = np.frombuffer(s, np.float32).reshape(S, 24)
+        transp = np.frombuffer(s, np.uint32).reshape(S, 24)[:, 16]
+        real = idx != 0xFFFFFFFF
+        assert sorted((idx[real] & 0x7FFFFFFF).tolist()) == list(range(S))
+        rec4 = rec.reshape(-1, 4); cl4 = cl.reshape(-1, 4); grp4 = grp.reshape(-1, 4)
+        for j in np.flatnonzero(real):
+            i = int(idx[j] & 0x7FFFFFFF)
+            assert np.array_equal(rec4[j, :3], wire[i, :3])
+            assert rec4[j, 3] == np.float32(wire[i, 4] * wire[i, 4])
+            assert bool(idx[j] >> 31) == bool(transp[i])
+            for box in (cl4[j // 8], grp4[j // 64]):
+                d = np.linalg.norm(wire[i, :3].astype(np.float64) - box[:3].astype(np.float64)) + abs(float(wire[i, 4]))
+                assert d <= np.sqrt(float(box[3]) / 1.125), (n_side, i)
+        assert np.all(np.isneginf(rec4[~real, 3]))
+    bad = bytearray(s); bad[96 * 5: 96 * 5 + 4] = np.float32(np.inf).tobytes()
+    assert L_.rtb_debug_accel_build(bytes(bad), S, None, None, None, None, C.byref(nc), C.byref(ng)) == 0
+    assert L_.rtb_debug_accel_build(s, 15, None, None, None, None, C.byref(nc), C.byref(ng)) == 0
