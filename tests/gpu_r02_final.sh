@@ -12,6 +12,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file
 ncu --set full --clock-control none --import-source on -k regex:render_frame -s 4 -c 1 -f -o $O/prof $CMD > $O/ncu_full.log 2>&1
 CMDW="python bench.py --steps 1 --warmup 3 --no-cpu --other-configs off --workload spheres1024_4k"
 ncu --set full --clock-control none --import-source on -k regex:render_frame -s 3 -c 1 -f -o $O/prof_wide $CMDW > $O/ncu_full_wide.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:render_tree -s 3 -c 1 -f -o $O/prof_tree python tools/exp/sweep_tree.py render_map_4k 1:0:0:0 > $O/ncu_full_tree.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:render_tree -s 28 -c 1 -f -o $O/prof_tree python tools/exp/sweep_tree.py render_map_4k 1:0:0:0 > $O/ncu_full_tree.log 2>&1   # the 29th launch: an N=8 part
 tail -2 $O/ncu_full.log $O/ncu_full_wide.log $O/ncu_full_tree.log
 ls -la $O
