@@ -201,10 +201,17 @@ __device__ __forceinline__ Material load_material_at(const unsigned char* mat) {
 
 /* EXTENSION X1 (no reference counterpart; oracle/rt_oracle.c:hit_triangle is the definition): Moeller-Trumbore,
  * two-sided, one rounded operation per step in exactly that order. */
-template <bool COUNT>
+/* record loads: through the read-only path from global memory, or plain loads when the records have been staged into
+ * shared memory (rt_trace_tree.cuh: tri_walk_staged) */
+template <bool STAGED>
+__device__ __forceinline__ float4 ld_rec(const float4* p) {
+    if (STAGED) return *p;
+    return __ldg(p);
+}
+template <bool COUNT, bool STAGED = false>
 __device__ __forceinline__ bool hit_triangle(V3 o, V3 d, const float4* rec, float& t, Tally<COUNT>& tl) {
     tl.add(RTB_TRI_TESTS);
-    const V3 v0 = xyz(__ldg(rec)), e1 = xyz(__ldg(rec + 1)), e2 = xyz(__ldg(rec + 2));
+    const V3 v0 = xyz(ld_rec<STAGED>(rec)), e1 = xyz(ld_rec<STAGED>(rec + 1)), e2 = xyz(ld_rec<STAGED>(rec + 2));
     V3 p = cross3(d, e2);
     float det = dot3(e1, p);
     if (det == 0.0f) return false;
@@ -240,8 +247,8 @@ __device__ __forceinline__ bool hit_triangle(V3 o, V3 d, const float4* rec, floa
 #ifndef RT_TRI_BATCH
 #define RT_TRI_BATCH 4
 #endif
-template <bool COUNT, class F>
-__device__ __forceinline__ bool for_triangle_hits(V3 o, V3 d, const float4* __restrict__ tri, uint32_t T, Tally<COUNT>& tl, F&& on_hit) {
+template <bool STAGED, bool COUNT, class F>
+__device__ __forceinline__ bool for_triangle_hits_ld(V3 o, V3 d, const float4* __restrict__ tri, uint32_t T, Tally<COUNT>& tl, F&& on_hit) {
     constexpr uint32_t kB = RT_TRI_BATCH;
     uint32_t k = 0;
 #pragma unroll 1
@@ -250,9 +257,9 @@ __device__ __forceinline__ bool for_triangle_hits(V3 o, V3 d, const float4* __re
         float4 rv0[kB], re1[kB], re2[kB];
 #pragma unroll
         for (uint32_t j = 0; j < kB; j++) {
-            rv0[j] = __ldg(tri + 3u * (k + j));
-            re1[j] = __ldg(tri + 3u * (k + j) + 1u);
-            re2[j] = __ldg(tri + 3u * (k + j) + 2u);
+            rv0[j] = ld_rec<STAGED>(tri + 3u * (k + j));
+            re1[j] = ld_rec<STAGED>(tri + 3u * (k + j) + 1u);
+            re2[j] = ld_rec<STAGED>(tri + 3u * (k + j) + 2u);
         }
         float det[kB], a[kB];
         uint32_t cand = 0;
@@ -289,10 +296,14 @@ __device__ __forceinline__ bool for_triangle_hits(V3 o, V3 d, const float4* __re
     }
     for (; k < T; k++) {
         float t1;
-        if (!hit_triangle(o, d, tri + 3u * k, t1, tl)) continue;
+        if (!hit_triangle<COUNT, STAGED>(o, d, tri + 3u * k, t1, tl)) continue;
         if (on_hit(k, t1)) return true;
     }
     return false;
+}
+template <bool COUNT, class F>
+__device__ __forceinline__ bool for_triangle_hits(V3 o, V3 d, const float4* __restrict__ tri, uint32_t T, Tally<COUNT>& tl, F&& on_hit) {
+    return for_triangle_hits_ld<false>(o, d, tri, T, tl, on_hit);
 }
 __device__ __forceinline__ V3 triangle_normal(const float4* rec) {
     V3 n = cross3(xyz(__ldg(rec + 1)), xyz(__ldg(rec + 2)));

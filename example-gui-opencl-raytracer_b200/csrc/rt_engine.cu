@@ -84,6 +84,7 @@ struct rtb_engine {
     uint32_t jump_L = 0xffffffffu;
     uint32_t* noalloc_scratch = nullptr; /* device address of g_noalloc_scratch on this engine's device (rtb_render_noalloc) */
     int opt_tree_ctas_per_sm = 3;
+    int opt_tri_tree_min = 1024; /* triangle scenes from this many triangles on render every tile in the tree kernel (0 = never) */
     int opt_accel = 0;        /* N4: 1 = many-sphere scenes walk the cluster structure instead of every record */
     DevBuf accel;             /* clusters, cluster-ordered records, original indices */
     uint32_t acc_nc = 0;
@@ -469,6 +470,9 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.blob = (const float4*)e->blob.p;
     fp.raw_spheres = e->d_spheres; fp.raw_planes = e->d_planes;
     fp.T = e->T; fp.tri = (const float4*)e->tri_rec.p; fp.raw_tris = e->d_tris;
+    /* Extension X1, large meshes: EVERY tile goes through the CTA-wide tree kernel, whose lock step lets the triangle records be
+     * staged into shared memory in chunks by TMA and shared by 128 rays (rt_trace_tree.cuh: tri_walk_staged) */
+    const bool tri_all = mode == 0 && e->opt_tree == 1 && e->L <= 16u && e->opt_tri_tree_min > 0 && e->T >= (uint32_t)e->opt_tri_tree_min;
     /* N4: the cluster walk instead of the record walk -- an extension, off unless asked for ("accel"), production trace only */
     const bool use_accel = e->opt_accel > 0 && mode == 0 && e->T == 0u && e->acc_nc > 0u;
     if (use_accel) {
@@ -599,6 +603,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
             e->time_valid = false;
             e->cost_hist_valid = false;
         } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
+        if (tri_all) { fp.split_min_cost = 64u; fp.split32_min_cost = 64u; fp.tree_min_cost = 64u; } /* whole tiles, all of them through render_tree */
         CU((e->T ? rt_launch_tile_order_tri : (use_accel ? rt_launch_tile_order_acc : rt_launch_tile_order))(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),
            "tile_order launch");
@@ -610,7 +615,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     /* level-wise pixel trees for the heavy queue entries (rt_trace_tree.cuh): production trace only, and only while a
      * node's 1 + 2L addition slots stay small.  One slab per CTA of the persistent grid. */
     fp.tree_mode = 0;
-    if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && ((fp.order && fp.tree_min_cost < 64u) || e->opt_tree >= 2)) {
+    if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && ((fp.order && fp.tree_min_cost < 64u) || e->opt_tree >= 2 || tri_all)) {
         const uint32_t cap = use_accel && e->opt_tree_cap == 8192 ? 32768u : (uint32_t)e->opt_tree_cap; /* N4 scenes: whole glass pixels */
         const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->opt_tree_ctas_per_sm; /* = the render_tree grid: one slab per CTA */
         const size_t records = rt_tree_slab_records(cap, e->L);
@@ -619,7 +624,8 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
             fp.tree_records = records;
             fp.tree_cap = cap;
             fp.tree_slots = slots;
-            fp.tree_mode = (uint32_t)e->opt_tree;
+            fp.tree_mode = tri_all ? 2u : (uint32_t)e->opt_tree;
+            if (tri_all) fp.tree_group_max_cost = 64u; /* four tiles per CTA pass: 128 rays per level fill the 128 threads */
             fp.jump = (const uint32_t*)e->jump.p;
         } else {
             (void)cudaGetLastError(); /* no room for the slabs: the cooperative walk handles everything */
@@ -676,6 +682,7 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
     if (!strcmp(name, "tree")) { e->opt_tree = value < 0 ? 0 : (value > 3 ? 3 : value); return 0; }
     if (!strcmp(name, "accel")) { e->opt_accel = value ? 1 : 0; e->time_valid = false; return 0; }
+    if (!strcmp(name, "tri_tree_min")) { e->opt_tri_tree_min = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tree_ctas_per_sm")) { e->opt_tree_ctas_per_sm = value < 1 ? 1 : (value > 8 ? 8 : value); e->tree_slab.release(); return 0; }
     if (!strcmp(name, "tree_group_max_cost")) { e->opt_tree_group_max_cost = value < 0 ? 0 : value; return 0; }
     if (!strcmp(name, "tree_min_cost")) { e->opt_tree_min_cost = value < 0 ? 0 : value; return 0; }

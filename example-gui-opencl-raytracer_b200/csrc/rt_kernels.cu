@@ -164,6 +164,11 @@ __global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__
         cs.light = cs.task + kCoopTasks;
         cs.pre = cs.light + 32 * kCoopLights;
     }
+    TriStage stg; /* extension X1 build: chunked TMA staging of the triangle records (behind the fallback walk's scratch) */
+    stg.buf = nullptr; stg.bar = nullptr; stg.phase = 0;
+#if RT_TRIANGLES
+    tri_stage_init(stg, rt_smem + (((RESIDENT ? fp.lay.total * 16u : 0u) + kCoopBytesPerWarp + 15u) & ~15u));
+#endif
     const uint32_t ntiles = fp.order ? __ldg(fp.queue_len) : fp.tiles_x * fp.tiles_y;
     const uint32_t n_tree = fp.tree_mode >= 2u ? ntiles : (fp.order ? __ldg(fp.n_split) : 0u);
     const TreeSlab sl = {fp.tree_slab + (size_t)blockIdx.x * fp.tree_records, fp.tree_cap};
@@ -200,7 +205,7 @@ __global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__
 #pragma unroll 1
             for (uint32_t p = 0; p < rounds && traced; p++) {
                 if (rounds > 1u && !tile_lanes(fp, tsh.entry[first], p).live) continue;
-                traced = trace_entry_tree<AOV>(fp, g, sl, tsh, first, span, rounds > 1u ? p : 32u);
+                traced = trace_entry_tree<AOV>(fp, g, sl, tsh, first, span, rounds > 1u ? p : 32u, stg);
             }
             if (!traced && span > 1u) { span = 1u; __syncthreads(); continue; } /* CTA-uniform; the barrier keeps the retry off the scratch the failed pass is still reading */
             if (warp < span) { /* warp w stores entry first + w, lane p = tile pixel p */
@@ -768,7 +773,7 @@ cudaError_t go(RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, 
     }
     fp.done_expected = grid + tgrid;
     if (with_tree) {
-        const uint32_t tsmem = (R ? fp.lay.total * 16u : 0u) + kCoopBytesPerWarp;
+        const uint32_t tsmem = (((R ? fp.lay.total * 16u : 0u) + kCoopBytesPerWarp + 15u) & ~15u) + (RT_TRIANGLES ? kTriStageBytes : 0u);
         e = go_tree<R, A>(fp, tgrid, tsmem, st);
         if (e != cudaSuccess) return e;
         if (shape) shape->tree_grid = tgrid;

@@ -92,6 +92,65 @@ struct TreeShared {
     uint32_t slot, count;          /* queue cursor broadcast */
 };
 
+/* ---- triangle records staged into shared memory in chunks (extension X1 build) ----------------------------------------
+ * The tree kernel runs a CTA in lock step -- every thread holds one ray of the current level (expand) or one pair of
+ * shadow rays (shade) -- so a chunk of the triangle array fetched ONCE by a TMA bulk copy serves all 128 threads:
+ * kTriChunk records of {v0, e1, e2} (12 KiB) per buffer, two buffers, two mbarriers; while the threads test chunk c from
+ * one buffer the copy of chunk c+1 is in flight into the other.  Records are visited in index order, with the same test
+ * (for_triangle_hits_ld<true>: plain shared-memory loads instead of the read-only global path): same words. */
+constexpr uint32_t kTriChunk = 256;
+constexpr uint32_t kTriStageBytes = 2u * kTriChunk * 48u + 16u;
+struct TriStage {
+    float4* buf;    /* [2][3 * kTriChunk] */
+    uint64_t* bar;  /* [2] */
+    uint32_t phase; /* bit b: the parity bar[b] completes next (CTA-uniform) */
+};
+__device__ __forceinline__ void tri_stage_init(TriStage& st, unsigned char* smem /* kTriStageBytes, 16-byte aligned */) {
+    st.buf = reinterpret_cast<float4*>(smem);
+    st.bar = reinterpret_cast<uint64_t*>(smem + 2u * kTriChunk * 48u);
+    st.phase = 0;
+    if (threadIdx.x == 0) { mbar_init(&st.bar[0], 1); mbar_init(&st.bar[1], 1); }
+    __syncthreads();
+}
+__device__ __forceinline__ void tri_stage_issue(const TriStage& st, const float4* tri, uint32_t T, uint32_t c, uint32_t b) {
+    const uint32_t first = c * kTriChunk;
+    const uint32_t n = T - first < kTriChunk ? T - first : kTriChunk;
+    mbar_expect_tx(&st.bar[b], n * 48u);
+    tma_bulk_g2s(st.buf + (size_t)b * 3u * kTriChunk, tri + (size_t)3u * first, n * 48u, &st.bar[b]);
+}
+/* Every thread of the CTA calls this (uniformly).  test_chunk(records, first index, count) -> this thread still needs the
+ * rest of the array; `need` = it needs anything at all.  The walk ends early when no thread does. */
+template <class F>
+__device__ __forceinline__ void tri_walk_staged(const float4* tri, uint32_t T, TriStage& st, bool need, F&& test_chunk) {
+    const uint32_t nch = (T + kTriChunk - 1u) / kTriChunk;
+    if (nch == 0u) return;
+    if (!__syncthreads_or(need)) return; /* also: every thread is done with whatever used the buffers last */
+    if (threadIdx.x == 0) {
+        tri_stage_issue(st, tri, T, 0u, 0u);
+        if (nch > 1u) tri_stage_issue(st, tri, T, 1u, 1u);
+    }
+#pragma unroll 1
+    for (uint32_t c = 0; c < nch; c++) {
+        const uint32_t b = c & 1u;
+        mbar_wait(&st.bar[b], (st.phase >> b) & 1u);
+        st.phase ^= 1u << b;
+        if (need) {
+            const uint32_t first = c * kTriChunk;
+            need = test_chunk(st.buf + (size_t)b * 3u * kTriChunk, first, T - first < kTriChunk ? T - first : kTriChunk);
+        }
+        const int any = __syncthreads_or(need); /* everyone has finished reading buffer b */
+        if (!any) {
+            if (c + 1u < nch) { /* drain the copy already in flight so the barrier's parity stays in step */
+                const uint32_t b1 = (c + 1u) & 1u;
+                mbar_wait(&st.bar[b1], (st.phase >> b1) & 1u);
+                st.phase ^= 1u << b1;
+            }
+            return;
+        }
+        if (threadIdx.x == 0 && c + 2u < nch) tri_stage_issue(st, tri, T, c + 2u, b);
+    }
+}
+
 /* xorshift32^(draws*k)(seed): jump[j*32 + i] = image of bit i under (step^draws)^(2^j).  The j loop is warp-uniform
  * (runs to the highest set bit of any lane's k), so every table read is one broadcast load. */
 __device__ __forceinline__ uint32_t rng_jump(const uint32_t* __restrict__ jump, uint32_t seed, uint32_t k, uint32_t kmax) {
@@ -110,7 +169,11 @@ __device__ __forceinline__ uint32_t rng_jump(const uint32_t* __restrict__ jump, 
  * tree does not fit the slab; otherwise sh.word[q] / sh.hid[q], q = w * 32 + tile pixel, hold the results. */
 template <bool AOV>
 __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const Geo& g, const TreeSlab sl, TreeShared& sh, uint32_t first,
-                                                 uint32_t ne, uint32_t only_pixel) {
+                                                 uint32_t ne, uint32_t only_pixel, TriStage& stg) {
+    /* extension X1 build with triangles present: their records go through the staged walk, everything else as ever */
+    const bool staged = RT_TRIANGLES && g.T != 0u;
+    Geo gs = g; /* the scene without its triangles */
+    if (staged) gs.T = 0u;
     constexpr uint32_t kFull = 0xffffffffu;
     Tally<false> tl;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -166,16 +229,32 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
             V3 ro = mk(0.0f, 0.0f, 0.0f), rd = ro, lo = ro, ld = ro; /* refraction / reflection continuations */
             float rf = 0.0f, rn = 0.0f, lf = 0.0f, ln = 0.0f;
             uint32_t meta = 0;
+            V3 o = mk(0.0f, 0.0f, 0.0f), d = mk(0.0f, 0.0f, 1.0f);
+            float f = 0.0f, n_cur = kAirN;
+            Closest c;
+            c.t = CUDART_INF_F; c.tL = CUDART_INF_F; c.who = -1; c.whop = -1; c.whot = -1; c.k = -1; c.occluded = false;
             if (act) {
                 const float4 r0 = sl.R0()[i], r1 = sl.R1()[i];
                 meta = sl.M()[i].x;
-                const V3 o = xyz(r0), d = xyz(r1);
-                const float f = r0.w, n_cur = r1.w;
-                const uint32_t depth = meta & 0xffu, sz = (meta >> 8) & 0xffu;
+                o = xyz(r0); d = xyz(r1);
+                f = r0.w; n_cur = r1.w;
                 RayF r;
                 ray_setup_fast(r, o, d);
-                Closest c;
-                closest_pass(r, g, tl, c);
+                closest_pass(r, gs, tl, c);
+            }
+#if RT_TRIANGLES
+            if (staged) /* CTA-uniform: triangles after the planes, same rules (closest_pass), from staged chunks */
+                tri_walk_staged(g.tri, g.T, stg, act, [&](const float4* recs, uint32_t k0, uint32_t n) {
+                    for_triangle_hits_ld<true>(o, d, recs, n, tl, [&](uint32_t k, float t1) {
+                        if (!(t1 >= c.t)) { c.t = t1; c.whot = (int)(k0 + k); }
+                        if (t1 <= c.tL) c.occluded = true;
+                        return false;
+                    });
+                    return true;
+                });
+#endif
+            if (act) {
+                const uint32_t depth = meta & 0xffu, sz = (meta >> 8) & 0xffu;
                 uint32_t kind, entry_child = 0u, hid = 0u;
                 V3 term;
                 if (c.k >= 0 && !c.occluded) { /* a visible light ends the chain, raytracing.cl:48-54 */
@@ -397,55 +476,87 @@ __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const 
     /* ---- 3 SHADE: (shaded node, light) pairs over the threads ---- */
     const uint32_t items = n_shaded * L;
 #pragma unroll 1
-    for (uint32_t it = tid; it < items; it += kBlock) {
-        const uint32_t k = it / L, li = it - k * L;
-        const uint32_t node = sl.shaded()[k];
-        const float4 s0 = sl.S0()[node], s1 = sl.S1()[node], s2 = sl.S2()[node];
-        const uint4 x = sl.X()[node];
-        const V3 ip = xyz(s0), nrm = xyz(s1), vv = xyz(s2);
-        const float fs = s0.w, fd = s1.w, shin = s2.w;
-        uint32_t rng = x.z;
-        for (uint32_t q = 0; q < 4u * li; q++) rng = xorshift_step(rng); /* the lights before this one drew 4 numbers each */
-        const float4 l0 = g.lgeo[li], l1 = g.laux[li];
-        float dist;
-        const V3 sdir = normalize_len(xyz(l0) - ip, dist);
-        float hlen;
-        const V3 hh = normalize_len(vv + sdir, hlen);
-        const float ndh = dot3(nrm, hh);
-        const float sx = 0.0f < ndh ? ndh : 0.0f;
-        const float ndl = dot3(nrm, sdir);
-        const float dif = 0.0f < ndl ? ndl : 0.0f;
-        /* R5: exact zeros -- only while pow(sx, shin) is finite (see rt_trace_fast.cuh) */
-        const bool tame = sx <= 1.0f && shin >= 0.0f;
-        const bool spec_zero = tame && ((fs == 0.0f) || (sx == 0.0f && shin > 0.0f));
-        const bool diff_zero = (fd == 0.0f) || (dif == 0.0f);
-        V3 spec = mk(0.0f, 0.0f, 0.0f), diffv = spec;
-        if (!(spec_zero && diff_zero)) {
-            V3 smp[kShadowSamples];
+    for (uint32_t it0 = 0; it0 < items; it0 += kBlock) { /* uniform trip count: the staged triangle walk is a CTA-wide step */
+        const uint32_t it = it0 + tid;
+        const bool act = it < items;
+        if (!staged && !act) continue;
+        V3 ip = mk(0.0f, 0.0f, 0.0f);
+        float fs = 0.0f, fd = 0.0f, shin = 0.0f, sx = 0.0f, dif = 0.0f, dist = 1.0f;
+        bool tame = true, spec_zero = true, diff_zero = true;
+        float4 l1 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float4* slot = nullptr;
+        V3 smp[kShadowSamples];
+        smp[0] = smp[1] = ip;
+        if (act) {
+            const uint32_t k = it / L, li = it - k * L;
+            const uint32_t node = sl.shaded()[k];
+            const float4 s0 = sl.S0()[node], s1 = sl.S1()[node], s2 = sl.S2()[node];
+            const uint4 x = sl.X()[node];
+            const V3 nrm = xyz(s1), vv = xyz(s2);
+            ip = xyz(s0);
+            fs = s0.w; fd = s1.w; shin = s2.w;
+            uint32_t rng = x.z;
+            for (uint32_t q = 0; q < 4u * li; q++) rng = xorshift_step(rng); /* the lights before this one drew 4 numbers each */
+            const float4 l0 = g.lgeo[li];
+            l1 = g.laux[li];
+            const V3 sdir = normalize_len(xyz(l0) - ip, dist);
+            float hlen;
+            const V3 hh = normalize_len(vv + sdir, hlen);
+            const float ndh = dot3(nrm, hh);
+            sx = 0.0f < ndh ? ndh : 0.0f;
+            const float ndl = dot3(nrm, sdir);
+            dif = 0.0f < ndl ? ndl : 0.0f;
+            /* R5: exact zeros -- only while pow(sx, shin) is finite (see rt_trace_fast.cuh) */
+            tame = sx <= 1.0f && shin >= 0.0f;
+            spec_zero = tame && ((fs == 0.0f) || (sx == 0.0f && shin > 0.0f));
+            diff_zero = (fd == 0.0f) || (dif == 0.0f);
+            slot = stream + x.w + 1u + 2u * li;
+            if (!(spec_zero && diff_zero)) {
 #pragma unroll
-            for (int j = 0; j < kShadowSamples; j++) {
-                const float theta = (float)(kTwoPi * (double)rng_next(rng));
-                const float phi = (float)(kPi * (double)rng_next(rng));
-                float sp, cp, sth, cth;
-                sincos_bounded(phi, sp, cp);
-                sincos_bounded(theta, sth, cth);
-                const float rs = l1.w * sp;
-                smp[j] = xyz(l0) + mk(rs * cth, rs * sth, l1.w * cp); /* raytracing.cl:101-106 */
-            }
-            static_assert(kShadowSamples == 2, "shadow_pair_fast traces the two samples of a light together");
-            float r0, r1;
-            shadow_pair_fast(smp[0], smp[1], ip, g, tl, r0, r1);
-            const float soft = (0.0f + r0) + r1;
-            if (!(soft == 0.0f && tame)) { /* else light_rgb *= 0: both terms are exact zeros */
-                const float ssr = soft / (float)kShadowSamples;
-                const V3 lrgb = div3_pos(xyz(l1) * 1.0f, dist * dist) * ssr;
-                if (!spec_zero) spec = (lrgb * fs) * pow_ieee(sx, shin);
-                if (!diff_zero) diffv = (lrgb * fd) * dif;
+                for (int j = 0; j < kShadowSamples; j++) {
+                    const float theta = (float)(kTwoPi * (double)rng_next(rng));
+                    const float phi = (float)(kPi * (double)rng_next(rng));
+                    float sp, cp, sth, cth;
+                    sincos_bounded(phi, sp, cp);
+                    sincos_bounded(theta, sth, cth);
+                    const float rs = l1.w * sp;
+                    smp[j] = xyz(l0) + mk(rs * cth, rs * sth, l1.w * cp); /* raytracing.cl:101-106 */
+                }
             }
         }
-        float4* slot = stream + x.w + 1u + 2u * li;
-        slot[0] = make_float4(spec.x, spec.y, spec.z, __uint_as_float(kOpAdd));
-        slot[1] = make_float4(diffv.x, diffv.y, diffv.z, __uint_as_float(kOpAdd));
+        static_assert(kShadowSamples == 2, "the two samples of a light are traced together");
+        const bool rays = act && !(spec_zero && diff_zero);
+        float r0 = 0.0f, r1 = 0.0f;
+        if (!staged) {
+            if (rays) shadow_pair_fast(smp[0], smp[1], ip, g, tl, r0, r1);
+        } else {
+#if RT_TRIANGLES
+            ShadowPair sp;
+            sp.dead0 = sp.dead1 = true; sp.o0 = sp.o1 = 1.0f; sp.len0 = sp.len1 = 0.0f;
+            if (rays) shadow_pair_solids(smp[0], smp[1], ip, gs, tl, sp);
+            tri_walk_staged(g.tri, g.T, stg, !(sp.dead0 && sp.dead1), [&](const float4* recs, uint32_t, uint32_t n) {
+                const float len0 = sp.len0, len1 = sp.len1;
+                if (!sp.dead0 && for_triangle_hits_ld<true>(sp.r0.o, sp.r0.d, recs, n, tl, [&](uint32_t, float t1) { return !(t1 >= len0); })) sp.dead0 = true;
+                if (!sp.dead1 && for_triangle_hits_ld<true>(sp.r1.o, sp.r1.d, recs, n, tl, [&](uint32_t, float t1) { return !(t1 >= len1); })) sp.dead1 = true;
+                return !(sp.dead0 && sp.dead1);
+            });
+            if (rays) { r0 = sp.dead0 ? 0.0f : sp.o0; r1 = sp.dead1 ? 0.0f : sp.o1; }
+#endif
+        }
+        if (act) {
+            V3 spec = mk(0.0f, 0.0f, 0.0f), diffv = spec;
+            if (rays) {
+                const float soft = (0.0f + r0) + r1;
+                if (!(soft == 0.0f && tame)) { /* else light_rgb *= 0: both terms are exact zeros */
+                    const float ssr = soft / (float)kShadowSamples;
+                    const V3 lrgb = div3_pos(xyz(l1) * 1.0f, dist * dist) * ssr;
+                    if (!spec_zero) spec = (lrgb * fs) * pow_ieee(sx, shin);
+                    if (!diff_zero) diffv = (lrgb * fd) * dif;
+                }
+            }
+            slot[0] = make_float4(spec.x, spec.y, spec.z, __uint_as_float(kOpAdd));
+            slot[1] = make_float4(diffv.x, diffv.y, diffv.z, __uint_as_float(kOpAdd));
+        }
     }
     __syncthreads();
 

@@ -126,6 +126,9 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * 2 = every tile; 3 = every tile, one pixel at a time (what a single-pixel entry does; tests).
  * "tree_cap": nodes per CTA slab (default 8192; a larger tree falls back to the cooperative walk).  Pixels do not
  * change.
+ * "tri_tree_min" (extension X1; default 1024, 0 = never): scenes with at least this many triangles render EVERY tile in the
+ * tree kernel, where the triangle records are staged into shared memory in 12 KiB chunks by TMA bulk copies and each
+ * chunk serves the 128 rays of a CTA.  Pixels do not change.
  * "accel" (EXTENSION; default 0 = brute force over every record, as the reference does): 1 = scenes
  * with >= 16 spheres and no triangles walk a cluster structure built at upload (csrc/rt_trace_accel.cuh) that skips only
  * tests whose outcome is provably "no hit"; the frame is word-identical to the brute-force one. */

@@ -95,3 +95,40 @@ def test_triangle_primary_hits_equal_the_numpy_pin(fresh, ref, scene, host):
         _, hit = fresh.render_to_host(W, H, want_hit=True)
         assert np.array_equal(hit, want), tree
     fresh.set_option("tree", 1)
+
+
+@pytest.mark.parametrize("n,W,H", [(12, 192, 108), (20, 160, 90), (23, 96, 54)])
+def test_staged_triangle_walk_in_the_tree_kernel(fresh, ref, scene, host, n, W, H):
+    """Large meshes render every tile in the CTA-wide tree kernel with the triangle records staged into shared memory in
+    256-record chunks by TMA (rt_trace_tree.cuh: tri_walk_staged): 288 / 800 / 1,058 triangles = 2 / 4 / 5 chunks, the
+    last one partial.  Forced here with "tri_tree_min" = 1 and with "tree" = 2 / 3; judge = the port (X1: parity unpinned),
+    and the un-staged cooperative walk must give the same words."""
+    s, p, l, tris, camp = host.heightfield_mesh_scene(n=n)
+    cam = host.camera(W=W, H=H, **camp)
+    sc = ref.Scene(s, p, l, scene.tex, scene.sky)
+    port = ref.port()
+    port.set_triangles(tris)
+    try:
+        want_rgb, want_hit = port.render(sc, cam, W, H, wide=True)
+    finally:
+        port.set_triangles(b"")
+    fresh.upload_scene(s, p, l)
+    fresh.upload_triangles(tris)
+    fresh.set_camera(cam)
+    fresh.set_option("tri_tree_min", 0)
+    fresh.set_option("tree", 0)
+    base_rgb, base_hit = fresh.render_to_host(W, H, want_hit=True)
+    assert np.array_equal(base_hit, want_hit)
+    c = ref.compare_frames(base_rgb, want_rgb, W, H)
+    assert c["within1"] >= 0.999 and c["psnr"] >= 50.0
+    for opts in ({"tree": 1, "tri_tree_min": 1}, {"tree": 2, "tri_tree_min": 0}, {"tree": 3, "tri_tree_min": 0}):
+        for k, v in opts.items():
+            fresh.set_option(k, v)
+        for rep in range(2):               # second frame: history-ordered queue
+            rgb, hit = fresh.render_to_host(W, H, want_hit=True)
+            assert np.array_equal(hit, base_hit), (opts, rep)
+            assert np.array_equal(rgb, base_rgb), (opts, rep)
+        if opts["tri_tree_min"]:
+            assert fresh.last_launch()["tree_grid"] > 0
+    fresh.set_option("tree", 1)
+    fresh.set_option("tri_tree_min", 1024)
