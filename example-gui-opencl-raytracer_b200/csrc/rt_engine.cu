@@ -617,7 +617,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.tree_mode = 0;
     if (mode == 0 && e->opt_tree > 0 && e->L <= 16u && ((fp.order && fp.tree_min_cost < 64u) || e->opt_tree >= 2 || tri_all)) {
         const uint32_t cap = use_accel && e->opt_tree_cap == 8192 ? 32768u : (uint32_t)e->opt_tree_cap; /* N4 scenes: whole glass pixels */
-        const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->opt_tree_ctas_per_sm; /* = the render_tree grid: one slab per CTA */
+        const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)(tri_all && e->opt_tree_ctas_per_sm == 3 ? 4 : e->opt_tree_ctas_per_sm); /* = the render_tree grid: one slab per CTA */
         const size_t records = rt_tree_slab_records(cap, e->L);
         if (e->tree_slab.ensure(records * 16 * slots) == 0) {
             fp.tree_slab = (float4*)e->tree_slab.p;

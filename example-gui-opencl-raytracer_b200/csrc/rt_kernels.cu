@@ -34,6 +34,11 @@ namespace RT_NS {
 #endif
 extern __shared__ __align__(128) unsigned char rt_smem[];
 
+#ifndef RT_TREE_BLOCKS
+#define RT_TREE_BLOCKS (RT_TRIANGLES ? 4 : 3) /* CTAs per SM the tree kernel is compiled for: 147 registers; the triangle
+                                                build takes 128 (no spills), where 16 instead of 12 warps per SM pay:
+                                                5k-triangle mesh at 4K 563 -> 531 ms (tools/exp/tri_stage_ab.sh) */
+#endif
 #ifndef RT_TREE
 #define RT_TREE 1 /* 0: compile the level-wise pixel-tree phase out (A/B builds) */
 #endif
@@ -143,7 +148,7 @@ __device__ __forceinline__ void stage_geometry(const RtFrameParams& fp, uint64_t
  * an out-of-line call (1.1 KB of spills).  An entry whose
  * tree outgrows the slab is walked by warp 0 with the cooperative trace -- same words. ---- */
 template <bool RESIDENT, bool AOV>
-__global__ void __launch_bounds__(kBlock, 3) render_tree(const __grid_constant__ RtFrameParams fp) {
+__global__ void __launch_bounds__(kBlock, RT_TREE_BLOCKS) render_tree(const __grid_constant__ RtFrameParams fp) {
     __shared__ __align__(8) uint64_t bar;
     __shared__ float lut255[256];
     __shared__ TreeShared tsh;
