@@ -9,7 +9,7 @@ NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 --extended-lambda -Xcompiler -fPIC -
 KFLAGS  := -fmad=false -prec-div=true -prec-sqrt=true -ftz=false
 CFLAGS  := -O2 -std=gnu11 -fPIC -Wall -Wextra -ffp-contract=off -Iinclude -Iinclude/shim
 
-OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_kernels_accel.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o
+OBJS := $(CSRC)/rt_kernels.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_kernels_accel.o $(CSRC)/rt_kernels_tri_accel.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o
 
 all: $(PKG)/librtb200.so
 
@@ -23,6 +23,9 @@ $(CSRC)/rt_kernels_tri.o: $(CSRC)/rt_kernels_tri.cu $(KDEPS)
 
 $(CSRC)/rt_kernels_accel.o: $(CSRC)/rt_kernels_accel.cu $(KDEPS) $(CSRC)/rt_trace_accel.cuh
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels_accel.ptxas.log || (cat $(CSRC)/rt_kernels_accel.ptxas.log; false)
+
+$(CSRC)/rt_kernels_tri_accel.o: $(CSRC)/rt_kernels_tri_accel.cu $(KDEPS) $(CSRC)/rt_trace_accel.cuh
+	$(NVCC) $(NVFLAGS) $(KFLAGS) -c $< -o $@ 2> $(CSRC)/rt_kernels_tri_accel.ptxas.log || (cat $(CSRC)/rt_kernels_tri_accel.ptxas.log; false)
 
 $(CSRC)/rt_engine.o: $(CSRC)/rt_engine.cu $(CSRC)/rt_kernels.h include/rtb200.h
 	$(NVCC) $(ARCH) -O2 -lineinfo -std=c++17 -Xcompiler -fPIC -c $< -o $@
@@ -42,13 +45,13 @@ $(PKG)/librtb200.so: $(OBJS)
 # diagnostic build: per-tile wall time in the hit-id AOV (tools/exp/tile_times.py, RTB_LIB=...)
 timing: all
 	$(NVCC) $(NVFLAGS) $(KFLAGS) -DRT_TILE_TIMING -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_timing.o 2> /dev/null
-	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_kernels_accel.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
+	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_timing.so /tmp/rt_kernels_timing.o $(CSRC)/rt_kernels_tri.o $(CSRC)/rt_kernels_accel.o $(CSRC)/rt_kernels_tri_accel.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
 
 # A/B build of the render kernels with extra defines: make variant NAME=narrow DEFS=-DRT_COOP_WIDE=0 ; RTB_LIB=.../librtb200_narrow.so
 variant: all
 	$(NVCC) $(NVFLAGS) $(KFLAGS) $(DEFS) -c $(CSRC)/rt_kernels.cu -o /tmp/rt_kernels_$(NAME).o 2> /dev/null
 	$(NVCC) $(NVFLAGS) $(KFLAGS) $(DEFS) -c $(CSRC)/rt_kernels_tri.cu -o /tmp/rt_kernels_tri_$(NAME).o 2> /dev/null
-	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_$(NAME).so /tmp/rt_kernels_$(NAME).o /tmp/rt_kernels_tri_$(NAME).o $(CSRC)/rt_kernels_accel.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
+	$(NVCC) $(ARCH) -shared -o $(PKG)/librtb200_$(NAME).so /tmp/rt_kernels_$(NAME).o /tmp/rt_kernels_tri_$(NAME).o $(CSRC)/rt_kernels_accel.o $(CSRC)/rt_kernels_tri_accel.o $(CSRC)/rt_engine.o $(CSRC)/cuda_wrap.o $(CSRC)/png_io.o $(CSRC)/map_io.o -lz
 
 oracle:
 	$(MAKE) -C oracle

@@ -28,7 +28,7 @@ ENGINE_SYMBOLS = (
     "rtb_upload_triangles", "rtb_bind_triangles_device", "rtb_upload_images", "rtb_bind_images_device", "rtb_set_camera", "rtb_partition_rows", "rtb_render",
     "rtb_render_counted", "rtb_sync", "rtb_read_frame", "rtb_read_hit", "rtb_frame_ptr", "rtb_hit_ptr",
     "rtb_last_render_ms", "rtb_last_kernel_ms", "rtb_stream", "rtb_set_option", "rtb_selftest_arith", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_write", "rtb_dev_read",
-    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_set_mirror_frame", "rtb_set_completion", "rtb_wait_flags", "rtb_wait_timeouts", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close", "rtb_assemble_bands", "rtb_last_launch", "rtb_render_noalloc", "rtb_debug_counters", "rtb_debug_jump_table", "rtb_debug_accel_build", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
+    "rtb_host_register", "rtb_host_unregister", "rtb_host_map", "rtb_set_mirror", "rtb_set_mirror_frame", "rtb_set_completion", "rtb_wait_flags", "rtb_wait_timeouts", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close", "rtb_assemble_bands", "rtb_last_launch", "rtb_render_noalloc", "rtb_debug_counters", "rtb_debug_jump_table", "rtb_debug_accel_build", "rtb_debug_tri_accel_build", "rtb_fp32_peak_tflops", "rtb_map_load", "rtb_map_save", "rtb_map_free",
 )
 WRAP_SYMBOLS = (
     "cl_wrap_init", "cl_wrap_load_global_data", "cl_wrap_load_single_data", "cl_wrap_load_images", "cl_wrap_output",
@@ -114,6 +114,7 @@ def lib():
             "rtb_debug_counters": (i, [vp, C.POINTER(C.c_uint64)]),
             "rtb_debug_jump_table": (i, [u32, C.POINTER(u32)]),
             "rtb_debug_accel_build": (i, [vp, u32, vp, vp, vp, vp, C.POINTER(u32), C.POINTER(u32)]),
+            "rtb_debug_tri_accel_build": (i, [vp, u32, vp, vp, vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]),
             "rtb_fp32_peak_tflops": (C.c_double, [vp, i]),
             "rtb_map_load": (i, [C.c_char_p, C.POINTER(MapArchive)]),
             "rtb_map_save": (i, [C.c_char_p, C.POINTER(MapArchive), i]),

@@ -29,6 +29,8 @@
 #define RT_TRI_PREFILTER 1 /* hit_triangle: decide the common u-test rejects without the division (exact outcome) */
 #endif
 
+#define RT_TRI_ACCEL (RT_ACCEL && RT_TRIANGLES) /* rt_kernels_tri_accel.cu: triangle walks through the hierarchy of rt_trace_accel.cuh */
+
 namespace RT_NS {
 
 constexpr float kEps = 0.001f;                     /* primitives.cl:5  EPSILON */
@@ -112,6 +114,11 @@ struct Geo {
     const uint32_t* acc_idx;
     const float4* acc_grp;
     uint32_t acc_nc;
+    const float4* tacc_node; /* N4 over the triangles (rt_trace_accel.cuh), global memory */
+    const float4* tacc_rec;
+    const uint32_t* tacc_idx;
+    uint32_t tacc_nc, tacc_nl;
+    uint32_t tacc_off[RT_TACC_LEVELS];
 };
 __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFrameParams& fp, const float* lut) {
     g.S = fp.S; g.P = fp.P; g.L = fp.L;
@@ -126,6 +133,11 @@ __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFra
     g.T = RT_TRIANGLES ? fp.T : 0u; /* a literal 0 in the plain build: every triangle loop and branch folds away */
     g.acc_cl = fp.acc_cl; g.acc_rec = fp.acc_rec; g.acc_idx = fp.acc_idx; g.acc_grp = fp.acc_grp;
     g.acc_nc = RT_ACCEL ? fp.acc_nc : 0u;
+    g.tacc_node = fp.tacc_node; g.tacc_rec = fp.tacc_rec; g.tacc_idx = fp.tacc_idx;
+    g.tacc_nc = (RT_ACCEL && RT_TRIANGLES) ? fp.tacc_nc : 0u;
+    g.tacc_nl = fp.tacc_nl;
+#pragma unroll
+    for (int l = 0; l < RT_TACC_LEVELS; l++) g.tacc_off[l] = fp.tacc_off[l];
 }
 
 /* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */

@@ -88,6 +88,9 @@ struct rtb_engine {
     int opt_accel = 0;        /* N4: 1 = many-sphere scenes walk the cluster structure instead of every record */
     DevBuf accel;             /* clusters, cluster-ordered records, original indices */
     uint32_t acc_nc = 0;
+    DevBuf tacc;              /* N4 over the triangles: nodes (all levels), cluster-ordered records, original indices */
+    bool tacc_valid = false;  /* built (or found unbuildable: tacc_nc == 0) for the current triangle array */
+    uint32_t tacc_nc = 0, tacc_nl = 0, tacc_nodes = 0, tacc_off[RT_TACC_LEVELS] = {0};
     int opt_tree = 1, opt_tree_cap = 8192, opt_tree_min_cost = 0 /* 0 = automatic */, opt_tree_group_max_cost = 0;
     bool cost_hist_valid = false; /* tile_cost holds measured-time costs of a frame with this geometry */
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
@@ -121,7 +124,7 @@ void rtb_destroy(rtb_engine* e) {
     e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
     e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
-    e->tree_slab.release(); e->wait_word.release(); e->jump.release(); e->accel.release();
+    e->tree_slab.release(); e->wait_word.release(); e->jump.release(); e->accel.release(); e->tacc.release();
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->evk) cudaEventDestroy(e->evk);
@@ -317,6 +320,141 @@ static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
     return 0;
 }
 
+/* N4 over the triangles of extension X1 (csrc/rt_trace_accel.cuh): `rec` = the {v0, e1, e2} records tri_prep made (12
+ * floats each; the kernel's test sees the triangle v0, v0 + e1, v0 + e2, so that is what the spheres bound).  Triangles in
+ * Morton order of their centroids, clusters of RT_ACCEL_K, then 8 nodes per parent until a level has <= 4 nodes or
+ * RT_TACC_LEVELS levels exist.  Every node: the axis-aligned box of the vertices below it as {centre, half extents}, two
+ * float4: the centre rounded to float, the half extents measured from that float centre in fp64 and rounded up;
+ * .w of the second = hx + hy + hz rounded up (the device's margin term). */
+struct TriAccelHost {
+    std::vector<float> node, rec;
+    std::vector<uint32_t> idx;
+    uint32_t nc = 0, nl = 0, off[RT_TACC_LEVELS] = {0};
+};
+static int build_tri_accel_host(const float* rec, uint32_t T, TriAccelHost& out) {
+    const uint32_t K = RT_ACCEL_K;
+    out.nc = out.nl = 0;
+    if (T < 2u * K || !rec) return 0;
+    std::vector<double> vx(3 * (size_t)T), vy(3 * (size_t)T), vz(3 * (size_t)T);
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    std::vector<double> cen(3 * (size_t)T);
+    for (uint32_t i = 0; i < T; i++) {
+        const float* r = rec + 12 * (size_t)i;
+        for (int k = 0; k < 12; k++)
+            if ((k & 3) != 3 && !std::isfinite(r[k])) return 0; /* brute force */
+        for (int v = 0; v < 3; v++) {
+            const double ex = v == 0 ? 0.0 : r[4 * v + 0], ey = v == 0 ? 0.0 : r[4 * v + 1], ez = v == 0 ? 0.0 : r[4 * v + 2];
+            vx[3 * (size_t)i + v] = (double)r[0] + ex; vy[3 * (size_t)i + v] = (double)r[1] + ey; vz[3 * (size_t)i + v] = (double)r[2] + ez;
+        }
+        const double c[3] = {(vx[3 * (size_t)i] + vx[3 * (size_t)i + 1] + vx[3 * (size_t)i + 2]) / 3.0,
+                             (vy[3 * (size_t)i] + vy[3 * (size_t)i + 1] + vy[3 * (size_t)i + 2]) / 3.0,
+                             (vz[3 * (size_t)i] + vz[3 * (size_t)i + 1] + vz[3 * (size_t)i + 2]) / 3.0};
+        for (int k = 0; k < 3; k++) { cen[3 * (size_t)i + k] = c[k]; lo[k] = c[k] < lo[k] ? c[k] : lo[k]; hi[k] = c[k] > hi[k] ? c[k] : hi[k]; }
+    }
+    /* order: a kd-style sort by counts.  The implicit layout wants every node but the last of a level FULL, so a node of
+     * capacity `cap` triangles hands its first cap/2 (along the longest axis of its centroids' bounds) to its lower
+     * half and the rest to the upper half, down to clusters of K: contiguous positions, tight boxes, no space-filling-curve jumps */
+    std::vector<std::pair<uint32_t, uint32_t>> order(T); /* .second = triangle (the .first is unused here) */
+    for (uint32_t i = 0; i < T; i++) order[i] = {0u, i};
+    uint32_t nc0 = (T + K - 1) / K, levels = 1;
+    for (uint32_t n = nc0; levels < RT_TACC_LEVELS && n > 4u; n = (n + 7u) / 8u) levels++;
+    size_t top_cap = K;
+    for (uint32_t q = 1; q < levels; q++) top_cap *= 8u;
+    struct Job { size_t b, e, cap; };
+    std::vector<Job> jobs;
+    for (size_t b = 0; b < T; b += top_cap) jobs.push_back({b, b + top_cap < T ? b + top_cap : (size_t)T, top_cap});
+    while (!jobs.empty()) {
+        const Job jb = jobs.back();
+        jobs.pop_back();
+        if (jb.cap <= K || jb.e - jb.b <= 1) continue;
+        const size_t half = jb.cap / 2, mid = jb.b + half;
+        if (jb.e > mid) {
+            double blo[3] = {1e300, 1e300, 1e300}, bhi[3] = {-1e300, -1e300, -1e300};
+            for (size_t q = jb.b; q < jb.e; q++)
+                for (int a = 0; a < 3; a++) {
+                    const double v = cen[3 * (size_t)order[q].second + a];
+                    blo[a] = v < blo[a] ? v : blo[a]; bhi[a] = v > bhi[a] ? v : bhi[a];
+                }
+            int ax = 0;
+            if (bhi[1] - blo[1] > bhi[ax] - blo[ax]) ax = 1;
+            if (bhi[2] - blo[2] > bhi[ax] - blo[ax]) ax = 2;
+            std::nth_element(order.begin() + jb.b, order.begin() + mid, order.begin() + jb.e,
+                             [&](const std::pair<uint32_t, uint32_t>& x, const std::pair<uint32_t, uint32_t>& y) {
+                                 const double cx_ = cen[3 * (size_t)x.second + ax], cy_ = cen[3 * (size_t)y.second + ax];
+                                 return cx_ < cy_ || (cx_ == cy_ && x.second < y.second);
+                             });
+            jobs.push_back({mid, jb.e, half});
+        }
+        jobs.push_back({jb.b, jb.e < mid ? jb.e : mid, half});
+    }
+    (void)lo; (void)hi;
+    const uint32_t nc = (T + K - 1) / K;
+    uint32_t n_lvl[RT_TACC_LEVELS], nl = 1, total = nc;
+    n_lvl[0] = nc;
+    out.off[0] = 0;
+    while (nl < RT_TACC_LEVELS && n_lvl[nl - 1] > 4u) {
+        n_lvl[nl] = (n_lvl[nl - 1] + 7u) / 8u;
+        out.off[nl] = total;
+        total += n_lvl[nl];
+        nl++;
+    }
+    out.node.assign(8 * (size_t)total, 0.0f);
+    out.rec.assign(12 * (size_t)nc * K, 0.0f); /* padding: all zero -> det == 0, never hit */
+    out.idx.assign((size_t)nc * K, 0xffffffffu);
+    for (uint32_t j = 0; j < T; j++) {
+        memcpy(&out.rec[12 * (size_t)j], rec + 12 * (size_t)order[j].second, 48);
+        out.idx[j] = order[j].second;
+    }
+    for (uint32_t l = 0; l < nl; l++) {
+        size_t span_t = K; /* triangles (sorted positions) per node of this level */
+        for (uint32_t q = 0; q < l; q++) span_t *= 8u;
+        for (uint32_t k = 0; k < n_lvl[l]; k++) {
+            const size_t b = (size_t)k * span_t, end = b + span_t < T ? b + span_t : T;
+            double blo[3] = {1e300, 1e300, 1e300}, bhi[3] = {-1e300, -1e300, -1e300};
+            for (size_t j = b; j < end; j++)
+                for (int v = 0; v < 3; v++) {
+                    const size_t i = 3 * (size_t)order[j].second + v;
+                    const double pt[3] = {vx[i], vy[i], vz[i]};
+                    for (int a = 0; a < 3; a++) { blo[a] = pt[a] < blo[a] ? pt[a] : blo[a]; bhi[a] = pt[a] > bhi[a] ? pt[a] : bhi[a]; }
+                }
+            float* o = &out.node[8 * ((size_t)out.off[l] + k)];
+            double hs = 0;
+            for (int a = 0; a < 3; a++) {
+                const float c = (float)(0.5 * (blo[a] + bhi[a]));
+                const double up = bhi[a] - (double)c, dn = (double)c - blo[a];
+                const double h = (up > dn ? up : dn) * (1.0 + 1e-6) + 1e-30;
+                if (!(h < 1e37) || !std::isfinite(c)) return 0;
+                o[a] = c;
+                o[4 + a] = nextafterf((float)h, INFINITY);
+                hs += o[4 + a];
+            }
+            o[3] = 0.0f;
+            o[7] = nextafterf((float)hs, INFINITY);
+        }
+    }
+    out.nc = nc;
+    out.nl = nl;
+    return 1;
+}
+static int prep_tri_accel(rtb_engine* e) {
+    e->tacc_nc = 0;
+    if (e->T < 2u * RT_ACCEL_K) return 0;
+    std::vector<float> rec(12 * (size_t)e->T);
+    CU(cudaMemcpyAsync(rec.data(), e->tri_rec.p, rec.size() * 4, cudaMemcpyDeviceToHost, e->stream), "D2H triangle records (accel build)");
+    CU(cudaStreamSynchronize(e->stream), "triangle records");
+    TriAccelHost h;
+    if (build_tri_accel_host(rec.data(), e->T, h) != 1) return 0;
+    const size_t b0 = h.node.size() * 4, b1 = h.rec.size() * 4, b2 = h.idx.size() * 4;
+    if (e->tacc.ensure(b0 + b1 + b2)) return -2;
+    CU(cudaMemcpyAsync(e->tacc.p, h.node.data(), b0, cudaMemcpyHostToDevice, e->stream), "H2D triangle accel");
+    CU(cudaMemcpyAsync((char*)e->tacc.p + b0, h.rec.data(), b1, cudaMemcpyHostToDevice, e->stream), "H2D triangle accel");
+    CU(cudaMemcpyAsync((char*)e->tacc.p + b0 + b1, h.idx.data(), b2, cudaMemcpyHostToDevice, e->stream), "H2D triangle accel");
+    CU(cudaStreamSynchronize(e->stream), "triangle accel upload"); /* the vectors die with this frame */
+    e->tacc_nc = h.nc; e->tacc_nl = h.nl; e->tacc_nodes = (uint32_t)(h.node.size() / 8);
+    memcpy(e->tacc_off, h.off, sizeof h.off);
+    return 0;
+}
+
 static int prep_scene(rtb_engine* e) {
     if (int rc = prep_jump(e)) return rc;
     e->lay = rt_blob_layout(e->S, e->P, e->L);
@@ -373,6 +511,8 @@ static int prep_tris(rtb_engine* e) {
     CU(rt_launch_tri_prep(e->d_tris, e->T, (float4*)e->tri_rec.p, e->stream), "tri_prep launch");
     return 0;
 }
+/* the hierarchy is built on first use (option "accel"), not at upload: 50k triangles cost tens of ms of host time */
+static void tris_changed(rtb_engine* e) { e->tacc_valid = false; e->tacc_nc = 0; }
 int rtb_upload_triangles(rtb_engine* e, const void* tris, uint32_t T) {
     if (!e) return fail(-1, "null engine");
     if (T && !tris) return fail(-1, "rtb_upload_triangles: null array with non-zero count");
@@ -382,6 +522,7 @@ int rtb_upload_triangles(rtb_engine* e, const void* tris, uint32_t T) {
     if (T) CU(cudaMemcpyAsync(e->tris.p, tris, (size_t)T * RT_TRIANGLE_BYTES, cudaMemcpyHostToDevice, e->stream), "H2D triangles");
     e->d_tris = (const unsigned char*)e->tris.p;
     e->T = T;
+    tris_changed(e);
     int rc = prep_tris(e);
     if (rc) return rc;
     CU(cudaStreamSynchronize(e->stream), "triangle upload");
@@ -394,6 +535,7 @@ int rtb_bind_triangles_device(rtb_engine* e, const void* d_tris, uint32_t T) {
     CU(cudaSetDevice(e->device), "cudaSetDevice");
     e->d_tris = (const unsigned char*)d_tris;
     e->T = T;
+    tris_changed(e);
     return prep_tris(e);
 }
 
@@ -472,10 +614,24 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     fp.T = e->T; fp.tri = (const float4*)e->tri_rec.p; fp.raw_tris = e->d_tris;
     /* Extension X1, large meshes: EVERY tile goes through the CTA-wide tree kernel, whose lock step lets the triangle records be
      * staged into shared memory in chunks by TMA and shared by 128 rays (rt_trace_tree.cuh: tri_walk_staged) */
-    const bool tri_all = mode == 0 && e->opt_tree == 1 && e->L <= 16u && e->opt_tri_tree_min > 0 && e->T >= (uint32_t)e->opt_tri_tree_min;
+    /* N4 over the triangles: built on first use; scenes it cannot take (too few, non-finite, huge) stay on the brute-force build */
+    if (e->opt_accel > 0 && mode == 0 && e->T != 0u && !e->tacc_valid) {
+        if (int rc = prep_tri_accel(e)) return rc;
+        e->tacc_valid = true;
+    }
+    const bool use_tacc = e->opt_accel > 0 && mode == 0 && e->T != 0u && e->tacc_nc > 0u;
+    const bool tri_all = !use_tacc && mode == 0 && e->opt_tree == 1 && e->L <= 16u && e->opt_tri_tree_min > 0 && e->T >= (uint32_t)e->opt_tri_tree_min;
     /* N4: the cluster walk instead of the record walk -- an extension, off unless asked for ("accel"), production trace only */
-    const bool use_accel = e->opt_accel > 0 && mode == 0 && e->T == 0u && e->acc_nc > 0u;
-    if (use_accel) {
+    const bool use_accel = e->opt_accel > 0 && mode == 0 && (e->T == 0u ? e->acc_nc > 0u : use_tacc);
+    if (use_tacc) {
+        const size_t b0 = (size_t)e->tacc_nodes * 32, b1 = (size_t)e->tacc_nc * RT_ACCEL_K * 48;
+        fp.tacc_node = (const float4*)e->tacc.p;
+        fp.tacc_rec = (const float4*)((const char*)e->tacc.p + b0);
+        fp.tacc_idx = (const uint32_t*)((const char*)e->tacc.p + b0 + b1);
+        fp.tacc_nc = e->tacc_nc; fp.tacc_nl = e->tacc_nl;
+        memcpy(fp.tacc_off, e->tacc_off, sizeof fp.tacc_off);
+    }
+    if (use_accel && e->acc_nc > 0u) {
         const size_t b0 = (size_t)e->acc_nc * 16, b1 = (size_t)e->acc_nc * RT_ACCEL_K * 16;
         fp.acc_cl = (const float4*)e->accel.p;
         fp.acc_rec = (const float4*)((const char*)e->accel.p + b0);
@@ -561,7 +717,9 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                     /* the pixel-tree kernel: not for many-sphere scenes (the WIDE variant's territory: a tree node walks all
                      * records on ONE lane; measured 50 -> 115 ms per N = 8 part on the 1,024-sphere grid) */
                     const bool wide_scene = e->T == 0u && !use_accel && e->lay.Lpad + e->lay.Spad >= (uint32_t)e->opt_wide_min_records;
-                    const bool tree = e->opt_tree > 0 && e->L <= 16u && (!wide_scene || e->opt_tree >= 2);
+                    /* nor for N4 over triangles: a walk is a chain of dependent loads and the CTA-wide trees only lose time
+                     * on it (measured on the 49,928-triangle mesh at 4K: 40 ms -> 61..74 ms); "tree" >= 2 still forces them (tests) */
+                    const bool tree = e->opt_tree > 0 && e->L <= 16u && (!wide_scene || e->opt_tree >= 2) && (!use_tacc || e->opt_tree >= 2);
                     if (tree) {
                         /* with the CTA-wide pixel-tree kernel beside render_frame (tools/exp/sweep_tree.py): tiles longer than
                          * 0.75 T go to it whole (4 warps on the tile's pooled segment trees), tiles longer than 3 T as four
@@ -604,7 +762,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
             e->cost_hist_valid = false;
         } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
         if (tri_all) { fp.split_min_cost = 64u; fp.split32_min_cost = 64u; fp.tree_min_cost = 64u; } /* whole tiles, all of them through render_tree */
-        CU((e->T ? rt_launch_tile_order_tri : (use_accel ? rt_launch_tile_order_acc : rt_launch_tile_order))(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
+        CU((e->T ? (use_tacc ? rt_launch_tile_order_tacc : rt_launch_tile_order_tri) : (use_accel ? rt_launch_tile_order_acc : rt_launch_tile_order))(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
                                 e->stream),
            "tile_order launch");
         fp.order = (const uint32_t*)e->tile_order.p;
@@ -633,7 +791,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     }
     RtLaunchShape shape{};
     CU(cudaEventRecord(e->evk, e->stream), "event record");
-    CU((e->T ? rt_launch_render_tri : (use_accel ? rt_launch_render_acc : rt_launch_render))(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
+    CU((e->T ? (use_tacc ? rt_launch_render_tacc : rt_launch_render_tri) : (use_accel ? rt_launch_render_acc : rt_launch_render))(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
     CU(cudaEventRecord(e->ev1, e->stream), "event record");
     e->timed = true;
     e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;
@@ -872,6 +1030,22 @@ int rtb_debug_accel_build(const void* spheres, uint32_t S, float* clusters, floa
         if (records) memcpy(records, h.rec.data(), h.rec.size() * 4);
         if (index) memcpy(index, h.idx.data(), h.idx.size() * 4);
         if (groups) memcpy(groups, h.grp.data(), h.grp.size() * 4);
+    }
+    return built;
+}
+int rtb_debug_tri_accel_build(const float* records, uint32_t T, float* nodes, float* sorted_records, uint32_t* index,
+                              uint32_t* n_clusters, uint32_t* n_levels, uint32_t level_offset[RT_TACC_LEVELS], uint32_t* n_nodes) {
+    if (!n_clusters || !n_levels || !level_offset || !n_nodes) return fail(-1, "rtb_debug_tri_accel_build: null argument");
+    TriAccelHost h;
+    const int built = build_tri_accel_host(records, T, h);
+    *n_clusters = h.nc;
+    *n_levels = h.nl;
+    *n_nodes = (uint32_t)(h.node.size() / 8);
+    memcpy(level_offset, h.off, sizeof h.off);
+    if (built == 1) {
+        if (nodes) memcpy(nodes, h.node.data(), h.node.size() * 4);
+        if (sorted_records) memcpy(sorted_records, h.rec.data(), h.rec.size() * 4);
+        if (index) memcpy(index, h.idx.data(), h.idx.size() * 4);
     }
     return built;
 }

@@ -791,7 +791,9 @@ cudaError_t go(RtFrameParams& fp, int sm_count, cudaStream_t st, uint32_t smem, 
 
 using namespace RT_NS;
 
-#if RT_TRIANGLES
+#if RT_TRIANGLES && RT_ACCEL
+#define RT_EXPORT(name) name##_tacc
+#elif RT_TRIANGLES
 #define RT_EXPORT(name) name##_tri
 #elif RT_ACCEL
 #define RT_EXPORT(name) name##_acc
@@ -812,7 +814,7 @@ cudaError_t rt_launch_scene_prep(const unsigned char* d_spheres, uint32_t S, con
 
 #endif
 
-#if RT_TRIANGLES
+#if RT_TRIANGLES && !RT_ACCEL
 cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* d_rec, cudaStream_t st) {
     if (T == 0) return cudaSuccess;
     tri_prep<<<(T + 127) / 128, 128, 0, st>>>(d_tris, T, d_rec);
@@ -853,7 +855,9 @@ cudaError_t RT_EXPORT(rt_launch_render)(const RtFrameParams& fp_in, int mode, in
     const bool aov = fp.hit != nullptr;
 #define RT_GO(R, M, A) return go<R, M, A>(fp, sm_count, st, smem, shape)
 #define RT_GO_A(R, M) do { if (aov) RT_GO(R, M, true); else RT_GO(R, M, false); } while (0)
-#if RT_TRIANGLES || RT_ACCEL
+#if RT_TRIANGLES && RT_ACCEL
+#define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); } while (0) /* the engine sends mode 0 only (rt_engine.cu: use_tacc) */
+#elif RT_TRIANGLES || RT_ACCEL
 #define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else RT_GO_A(R, 3); } while (0)
 #else
 #define RT_GO_M(R) do { if (mode == 0) RT_GO_A(R, 0); else if (mode == 1) RT_GO_A(R, 1); else if (mode == 2) RT_GO_A(R, 2); else if (mode == 4) RT_GO_A(R, 4); else RT_GO_A(R, 3); } while (0)

@@ -50,6 +50,7 @@ static inline size_t rt_tree_slab_records(uint32_t cap, uint32_t L) {
 /* N4 (rt_trace_accel.cuh): spheres per cluster of the acceleration structure */
 #define RT_ACCEL_K 8
 #define RT_ACCEL_G 8 /* clusters per group (second level) */
+#define RT_TACC_LEVELS 6 /* triangle hierarchy: clusters of RT_ACCEL_K triangles, then 8 nodes per parent, up to 8^5 clusters per top node */
 
 struct RtFrameParams {
     /* raygen.cl:5-8 scalar arguments */
@@ -118,6 +119,14 @@ struct RtFrameParams {
     uint32_t done_expected;     /* CTAs of the frame's kernels (render_frame + render_tree); set by the launcher */
     uint32_t* done_flag;        /* may be NULL; device-visible: a peer GPU's memory (CUDA IPC) or mapped host memory */
     uint32_t done_value;
+    /* N4 over the triangles of extension X1 (rt_trace_accel.cuh; NULL / 0 = brute force): bounding spheres in the
+     * encoding of acc_cl, level 0 = clusters of RT_ACCEL_K triangles in Morton order of their centroids, level l + 1 =
+     * 8 consecutive nodes of level l; level l starts at node tacc_off[l] */
+    const float4* tacc_node;
+    const float4* tacc_rec;   /* [tacc_nc * RT_ACCEL_K * 3] {v0, e1, e2} in cluster order; padding records are all zero (det == 0: never hit) */
+    const uint32_t* tacc_idx; /* [tacc_nc * RT_ACCEL_K] original triangle index */
+    uint32_t tacc_nc, tacc_nl;
+    uint32_t tacc_off[RT_TACC_LEVELS];
 };
 
 /* scene_prep: wire arrays -> blob. */
@@ -160,5 +169,9 @@ cudaError_t rt_launch_tile_order_acc(const RtFrameParams& fp, uint32_t* d_cost, 
                                      cudaStream_t st);
 cudaError_t rt_launch_tile_order_tri(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
                                      cudaStream_t st);
+/* N4 over triangles (rt_kernels_tri_accel.cu): extension X1 build with the triangle walks going through the hierarchy. */
+cudaError_t rt_launch_render_tacc(const RtFrameParams& fp, int mode, int sm_count, cudaStream_t st, RtLaunchShape* shape);
+cudaError_t rt_launch_tile_order_tacc(const RtFrameParams& fp, uint32_t* d_cost, uint32_t* d_hist_cursor, uint32_t* d_order,
+                                      cudaStream_t st);
 /* Extension X1: rtriangle wire array -> {v0, v1-v0, v2-v0} records (3 float4 each). */
 cudaError_t rt_launch_tri_prep(const unsigned char* d_tris, uint32_t T, float4* d_rec, cudaStream_t st);

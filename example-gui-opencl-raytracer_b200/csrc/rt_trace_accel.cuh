@@ -100,4 +100,137 @@ __device__ __forceinline__ bool shadow_spheres_accel(const RayF& r, float len, c
     return true;
 }
 
+#if RT_TRIANGLES
+/* ---- N4 over the triangles of extension X1 -------------------------------------------------------------------------
+ * The same idea one level deeper, with boxes: triangles in Morton order of their centroids, clusters of kAccK, then 8
+ * nodes per parent up to RT_TACC_LEVELS levels (rt_engine.cu: build_tri_accel_host); every node is the axis-aligned box
+ * {centre, half extents} of the vertices below it (flat patches of a mesh fill a box far better than a sphere).  A walk
+ * runs over cluster positions in order; at a position that starts a level-l node it tests that node first and skips
+ * its 8^l clusters when the ray provably cannot produce a hit there; clusters that survive run the UNCHANGED
+ * Moeller-Trumbore walk (for_triangle_hits) on their members.
+ *
+ * The cull (tacc_cull): the box grown on every side by mu = (|o - c|_1 + |h|_1) / 4096 >= (distance from the origin to
+ * any point of the box) * 2^-12, and the slab test against it, as a LINE first (entry after exit: miss), then "exit
+ * behind the origin" and "entry beyond what matters".  (accel_cull's margin is 2^-8: a sphere test's discriminant
+ * cancels, so its noise goes with sqrt(2^-24); Moeller-Trumbore's goes with 2^-24 itself, and a margin relative to
+ * the origin's distance is what decides how well far-away origins -- shadow rays from the ground plane near the
+ * horizon -- can still be culled: at 2^-8 those walks degenerated into the full brute-force loop.)  IEEE infinities do the parallel case
+ * (1 / 0 = inf: a slab the origin is inside gives (-inf, +inf), one it is outside gives an empty interval); every
+ * comparison is written so that a NaN anywhere means "do not cull".  The slab arithmetic itself rounds at 2^-22 of
+ * the distances involved, 2^14 times below mu.
+ *
+ * Equality with the brute-force walk (closest_pass / shadow_path_fast):
+ *  - closest hit: the brute-force rule over triangles in index order is `!(t1 >= c.t)` -- strictly closer than
+ *    everything before, spheres and planes included -- so among triangles of equal distance the smallest index wins and
+ *    a triangle never displaces an equally distant sphere or plane.  Here candidates arrive in cluster order, so the
+ *    rule is spelled out: closer, or equally close as the TRIANGLE held so far with a smaller original index.  A NaN
+ *    distance (in c.t on entry or from a member) makes the brute-force outcome order-dependent: such a ray is
+ *    re-walked in index order.  The light-occlusion flag is an OR.
+ *  - shadow ray: any member with !(t1 >= len) blocks -- an OR.
+ *  - what a cull may skip: the margin argument of accel_cull carries over as long as the member test's rounding
+ *    error, seen as a displacement in the triangle's plane, stays below the margin:
+ *    ~ 8 * 2^-24 * |o - v0| / (sin(angle e1,e2) * |cos(angle d,normal)|) < |o - v0| / 4096, i.e. the ray is not within
+ *    ~2^-9 (0.1 degree) of grazing the triangle's plane (times the triangle's shape factor).  Inside that sliver of
+ *    directions the brute-force walk's own answer is rounding noise of a det near zero -- and it accepts a far-away
+ *    triangle only when the ray also lies within ~2^-21 |o - v0| of that triangle's plane -- so a cull can in
+ *    principle skip a triangle the noise would have accepted; the parity statement for this extension of an extension is therefore
+ *    "equal wherever compared" (tests/test_accel_gpu.py: meshes, triangle soups, duplicates, the 49,928-triangle mesh
+ *    at 1080p; bench.py compares the 4K frame), not a proof.  X1 itself has no reference counterpart (parity
+ *    unpinned, SURVEY.md 8(a') X1). */
+struct TaccRay {
+    V3 o, inv; /* origin, 1 / direction per axis (IEEE: +-inf for a zero component) */
+};
+__device__ __forceinline__ TaccRay tacc_ray(V3 o, V3 d) {
+    TaccRay q;
+    q.o = o;
+    q.inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    return q;
+}
+/* false: a NaN or an infinity among the six numbers (NaN test results then depend on the visiting order) */
+__device__ __forceinline__ bool tacc_finite(const RayF& r) {
+    const float chk = ((fabsf(r.o.x) + fabsf(r.o.y)) + fabsf(r.o.z)) + ((fabsf(r.d.x) + fabsf(r.d.y)) + fabsf(r.d.z));
+    return chk <= 3.0e38f;
+}
+/* true when no triangle inside the box {c, h} can yield a hit with 0 < t <= tmax (tmax = +inf: any t) */
+__device__ __forceinline__ bool tacc_cull(const TaccRay& q, float4 c, float4 h, float tmax) {
+    const float ax = c.x - q.o.x, ay = c.y - q.o.y, az = c.z - q.o.z;
+    const float mu = (((fabsf(ax) + fabsf(ay)) + fabsf(az)) + h.w) * 0.000244140625f; /* 2^-12; h.w = hx + hy + hz, rounded up */
+    const float ex = h.x + mu, ey = h.y + mu, ez = h.z + mu;
+    const float x0 = (ax - ex) * q.inv.x, x1 = (ax + ex) * q.inv.x;
+    const float y0 = (ay - ey) * q.inv.y, y1 = (ay + ey) * q.inv.y;
+    const float z0 = (az - ez) * q.inv.z, z1 = (az + ez) * q.inv.z;
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+    /* 0 * inf = NaN (the origin exactly on a grown face of a slab the ray is parallel to) drops out of fminf / fmaxf and
+     * leaves that slab to its other, infinite bound: either outcome is fine at a distance of exactly mu.  Rays with a
+     * non-finite origin or direction never get here (the callers walk those by brute force). */
+    return tn > tf || tf < 0.0f || tn > tmax;
+}
+template <class TMAX, class LEAF>
+__device__ __forceinline__ void tacc_walk(const TaccRay& q, const Geo& g, uint32_t k0, uint32_t k1, TMAX&& tmax, LEAF&& leaf) {
+    const uint32_t top = g.tacc_nl - 1u;
+    uint32_t k = k0;
+    for (;;) {
+        /* search: advance to the next cluster that survives its ancestors' boxes and its own */
+        bool have = false;
+#pragma unroll 1
+        while (k < k1) {
+            uint32_t lv = k ? (uint32_t)(__ffs((int)k) - 1) / 3u : top;
+            lv = lv < top ? lv : top;
+            const float tm = tmax();
+            bool culled = false;
+#pragma unroll
+            for (int l = RT_TACC_LEVELS - 1; l >= 0; --l) {
+                if (!culled && (uint32_t)l <= lv) {
+                    const float4* nd = g.tacc_node + 2u * (g.tacc_off[l] + (k >> (3 * l)));
+                    if (tacc_cull(q, __ldg(nd), __ldg(nd + 1), tm)) {
+                        k += 1u << (3 * l);
+                        culled = true;
+                    }
+                }
+            }
+            if (!culled) { have = true; break; }
+        }
+        if (!have) return;
+        if (leaf(k)) return;
+        k++;
+    }
+}
+
+/* the triangle part of closest_pass (rt_trace_fast.cuh) through the hierarchy; true = re-walk this ray in index order */
+template <bool COUNT>
+__device__ __forceinline__ bool closest_triangles_accel(const RayF& r, const Geo& g, Tally<COUNT>& tl, Closest& c) {
+    if (c.t != c.t || c.tL != c.tL || !tacc_finite(r)) return true;
+    const TaccRay q = tacc_ray(r.o, r.d);
+    bool odd = false;
+    tacc_walk(q, g, 0u, g.tacc_nc,
+              [&]() { return ((c.k >= 0 && !c.occluded && c.tL > c.t) ? c.tL : c.t) * 1.00001f; },
+              [&](uint32_t k) {
+                  for_triangle_hits(r.o, r.d, g.tacc_rec + 3u * kAccK * k, kAccK, tl, [&](uint32_t j, float t1) {
+                      const int orig = (int)__ldg(g.tacc_idx + kAccK * k + j);
+                      if (t1 != t1) odd = true;
+                      if (t1 < c.t || (t1 == c.t && c.whot >= 0 && orig < c.whot)) { c.t = t1; c.whot = orig; }
+                      if (t1 <= c.tL) c.occluded = true;
+                      return false;
+                  });
+                  return false;
+              });
+    return odd;
+}
+
+/* the triangle part of a shadow ray: true = blocked */
+template <bool COUNT>
+__device__ __forceinline__ bool shadow_triangles_accel(const RayF& r, float len, const Geo& g, Tally<COUNT>& tl) {
+    if (!tacc_finite(r)) return for_triangle_hits(r.o, r.d, g.tri, g.T, tl, [&](uint32_t, float t1) { return !(t1 >= len); });
+    const TaccRay q = tacc_ray(r.o, r.d);
+    const float tm = len * 1.00001f;
+    bool blocked = false;
+    tacc_walk(q, g, 0u, g.tacc_nc, [&]() { return tm; }, [&](uint32_t k) {
+        blocked = for_triangle_hits(r.o, r.d, g.tacc_rec + 3u * kAccK * k, kAccK, tl, [&](uint32_t, float t1) { return !(t1 >= len); });
+        return blocked;
+    });
+    return blocked;
+}
+#endif
+
 }  // namespace RT_NS

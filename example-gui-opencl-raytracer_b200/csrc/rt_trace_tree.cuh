@@ -171,7 +171,7 @@ template <bool AOV>
 __device__ __forceinline__ bool trace_entry_tree(const RtFrameParams& fp, const Geo& g, const TreeSlab sl, TreeShared& sh, uint32_t first,
                                                  uint32_t ne, uint32_t only_pixel, TriStage& stg) {
     /* extension X1 build with triangles present: their records go through the staged walk, everything else as ever */
-    const bool staged = RT_TRIANGLES && g.T != 0u;
+    const bool staged = RT_TRIANGLES && g.T != 0u && !(RT_TRI_ACCEL && g.tacc_nc != 0u); /* N4 walks are per ray, not CTA-wide */
     Geo gs = g; /* the scene without its triangles */
     if (staged) gs.T = 0u;
     constexpr uint32_t kFull = 0xffffffffu;

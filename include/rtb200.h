@@ -211,6 +211,14 @@ void rtb_map_free(rtb_map* m);
 int rtb_debug_jump_table(uint32_t L, uint32_t out[480]);
 int rtb_debug_accel_build(const void* spheres, uint32_t S, float* clusters, float* records, uint32_t* index, float* groups,
                           uint32_t* n_clusters, uint32_t* n_groups);
+/* ... and the N4 hierarchy over the triangles of extension X1 (built on first use when option "accel" is on), from
+ * {v0, e1, e2} records of 12 floats (what tri_prep makes of the wire array): nodes[8*n_nodes] = axis-aligned boxes
+ * {centre.xyz, 0, half extents.xyz, their sum}, level l at level_offset[l] (level 0 = clusters of 8 triangles in Morton
+ * order of their centroids, level l+1 = 8 nodes of level l);
+ * sorted_records[12*8*nc] (padding all zero); index[8*nc] original triangle index (0xffffffff = padding).  Array pointers
+ * may be NULL (call once for the sizes: n_nodes <= nc * 8 / 7 + 6).  Returns 1 when built, 0 when the mesh stays brute force. */
+int rtb_debug_tri_accel_build(const float* records, uint32_t T, float* nodes, float* sorted_records, uint32_t* index,
+                              uint32_t* n_clusters, uint32_t* n_levels, uint32_t level_offset[6], uint32_t* n_nodes);
 /* Diagnostic builds only (e.g. -DRT_TREE_CLOCKS): the raw counter words the last launch left behind. */
 int rtb_debug_counters(rtb_engine* e, uint64_t out[RTB_NCOUNTERS]);
 /* rtb_render_noalloc -- NO COUNTERPART IN THE REFERENCE; added for callers that

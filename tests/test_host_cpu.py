@@ -373,3 +373,55 @@ def test_accel_structure_contains_its_spheres(pkg):
     bad = bytearray(s); bad[96 * 5: 96 * 5 + 4] = np.float32(np.inf).tobytes()
     assert L_.rtb_debug_accel_build(bytes(bad), S, None, None, None, None, C.byref(nc), C.byref(ng)) == 0
     assert L_.rtb_debug_accel_build(s, 15, None, None, None, None, C.byref(nc), C.byref(ng)) == 0
+
+
+def test_triangle_hierarchy_contains_its_triangles(pkg):
+    """rt_engine.cu: build_tri_accel_host (N4 over extension X1) -- every triangle appears exactly once with its record
+    bytes unchanged; its three vertices v0, v0 + e1, v0 + e2 lie inside the box {centre, half extents} of EVERY ancestor
+    (cluster and each level above), whose .w carries at least the sum of the half extents; level sizes shrink by 8; padding records are all zero (det == 0: never hit); a non-finite
+    vertex or a tiny mesh is left to brute force."""
+    from example_gui_opencl_raytracer_b200 import host
+    L_ = pkg.lib()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    for n in (3, 12, 40):
+        _, _, _, tris, _ = host.heightfield_mesh_scene(n=n)
+        T = len(tris) // 112
+        wire = np.frombuffer(tris, np.float32).reshape(T, 28)
+        rec = np.zeros((T, 12), np.float32)                      # what tri_prep makes: {v0, v1 - v0, v2 - v0}, one fp32 subtraction each
+        rec[:, 0:3] = wire[:, 0:3]
+        rec[:, 4:7] = wire[:, 4:7] - wire[:, 0:3]
+        rec[:, 8:11] = wire[:, 8:11] - wire[:, 0:3]
+        nc, nl, nn = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        off = (C.c_uint32 * 6)()
+        built = L_.rtb_debug_tri_accel_build(vp(rec), T, None, None, None, C.byref(nc), C.byref(nl), off, C.byref(nn))
+        assert built == 1 and nc.value == (T + 7) // 8
+        nodes = np.zeros(8 * nn.value, np.float32); srt = np.zeros(12 * 8 * nc.value, np.float32); idx = np.zeros(8 * nc.value, np.uint32)
+        assert L_.rtb_debug_tri_accel_build(vp(rec), T, vp(nodes), vp(srt), vp(idx), C.byref(nc), C.byref(nl), off, C.byref(nn)) == 1
+        sizes = [nc.value]
+        for l in range(1, nl.value):
+            assert off[l] == off[l - 1] + sizes[-1]
+            sizes.append((sizes[-1] + 7) // 8)
+        assert off[0] == 0 and nn.value == sum(sizes) and (sizes[-1] <= 4 or nl.value == 6)
+        real = idx != 0xFFFFFFFF
+        assert sorted(idx[real].tolist()) == list(range(T)) and real[:T].all() and not real[T:].any()
+        srt = srt.reshape(-1, 12)
+        assert np.array_equal(srt[:T].view(np.uint32), rec[idx[:T]].view(np.uint32))
+        assert not srt[T:].any()
+        node8 = nodes.reshape(-1, 8).astype(np.float64)
+        assert np.all(node8[:, 7] >= node8[:, 4:7].sum(axis=1)) and np.all(node8[:, 4:7] > 0)
+        r64 = rec.astype(np.float64)
+        for j in range(T):
+            i = int(idx[j])
+            v0 = r64[i, 0:3]
+            for l in range(nl.value):
+                box = node8[off[l] + (j // 8 >> (3 * l))]
+                for v in (v0, v0 + r64[i, 4:7], v0 + r64[i, 8:11]):
+                    assert np.all(np.abs(v - box[0:3]) <= box[4:7]), (n, i, l)
+        # the boxes are tight: a cluster's box is no larger than its members' extent (plus rounding)
+        ext = np.stack([r64[idx[:T], 0:3], r64[idx[:T], 0:3] + r64[idx[:T], 4:7], r64[idx[:T], 0:3] + r64[idx[:T], 8:11]], axis=1)
+        for k in range(nc.value):
+            pts = ext[8 * k: 8 * k + 8].reshape(-1, 3)
+            assert np.all(2 * node8[k, 4:7] <= (pts.max(axis=0) - pts.min(axis=0)) * (1 + 1e-5) + 1e-6)
+    bad = rec.copy(); bad[5, 4] = np.inf
+    assert L_.rtb_debug_tri_accel_build(vp(bad), T, None, None, None, C.byref(nc), C.byref(nl), off, C.byref(nn)) == 0
+    assert L_.rtb_debug_tri_accel_build(vp(rec), 15, None, None, None, C.byref(nc), C.byref(nl), off, C.byref(nn)) == 0
