@@ -117,8 +117,7 @@ struct Geo {
     const float4* tacc_node; /* N4 over the triangles (rt_trace_accel.cuh), global memory */
     const float4* tacc_rec;
     const uint32_t* tacc_idx;
-    uint32_t tacc_nc, tacc_nl;
-    uint32_t tacc_off[RT_TACC_LEVELS];
+    uint32_t tacc_nc, tacc_nl, tacc_ntop;
 };
 __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFrameParams& fp, const float* lut) {
     g.S = fp.S; g.P = fp.P; g.L = fp.L;
@@ -135,9 +134,7 @@ __device__ __forceinline__ void geo_bind(Geo& g, const float4* base, const RtFra
     g.acc_nc = RT_ACCEL ? fp.acc_nc : 0u;
     g.tacc_node = fp.tacc_node; g.tacc_rec = fp.tacc_rec; g.tacc_idx = fp.tacc_idx;
     g.tacc_nc = (RT_ACCEL && RT_TRIANGLES) ? fp.tacc_nc : 0u;
-    g.tacc_nl = fp.tacc_nl;
-#pragma unroll
-    for (int l = 0; l < RT_TACC_LEVELS; l++) g.tacc_off[l] = fp.tacc_off[l];
+    g.tacc_nl = fp.tacc_nl; g.tacc_ntop = fp.tacc_ntop;
 }
 
 /* primitives.cl:111-125: ((float)x)/2^31*2 == (float)x * 2^-30 exactly. */

@@ -90,7 +90,7 @@ struct rtb_engine {
     uint32_t acc_nc = 0;
     DevBuf tacc;              /* N4 over the triangles: nodes (all levels), cluster-ordered records, original indices */
     bool tacc_valid = false;  /* built (or found unbuildable: tacc_nc == 0) for the current triangle array */
-    uint32_t tacc_nc = 0, tacc_nl = 0, tacc_nodes = 0, tacc_off[RT_TACC_LEVELS] = {0};
+    uint32_t tacc_nc = 0, tacc_nl = 0, tacc_nodes = 0, tacc_ntop = 0;
     int opt_tree = 1, opt_tree_cap = 8192, opt_tree_min_cost = 0 /* 0 = automatic */, opt_tree_group_max_cost = 0;
     bool cost_hist_valid = false; /* tile_cost holds measured-time costs of a frame with this geometry */
     DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
@@ -321,16 +321,18 @@ static int prep_accel(rtb_engine* e, const unsigned char* host_spheres) {
 }
 
 /* N4 over the triangles of extension X1 (csrc/rt_trace_accel.cuh): `rec` = the {v0, e1, e2} records tri_prep made (12
- * floats each; the kernel's test sees the triangle v0, v0 + e1, v0 + e2, so that is what the spheres bound).  Triangles in
- * Morton order of their centroids, clusters of RT_ACCEL_K, then 8 nodes per parent until a level has <= 4 nodes or
+ * floats each; the kernel's test sees the triangle v0, v0 + e1, v0 + e2, so that is what the boxes bound).  Triangles in
+ * a kd-style order (below), clusters of RT_ACCEL_K, then 8 nodes per parent until a level has <= 4 nodes or
  * RT_TACC_LEVELS levels exist.  Every node: the axis-aligned box of the vertices below it as {centre, half extents}, two
  * float4: the centre rounded to float, the half extents measured from that float centre in fp64 and rounded up;
- * .w of the second = hx + hy + hz rounded up (the device's margin term). */
+ * .w of the second = 2^-12 (hx + hy + hz) rounded up (the device's margin term).  Levels are stored TOP FIRST, each padded
+ * to ntop * 8^(nl - 1 - l) slots, so that a level's first node is a closed form of its number (tacc_level_base). */
 struct TriAccelHost {
     std::vector<float> node, rec;
     std::vector<uint32_t> idx;
-    uint32_t nc = 0, nl = 0, off[RT_TACC_LEVELS] = {0};
+    uint32_t nc = 0, nl = 0, ntop = 0, off[RT_TACC_LEVELS] = {0};
 };
+static uint32_t tacc_level_base_host(uint32_t ntop, uint32_t m) { return ntop * (0x09249249u & ((1u << (3u * m)) - 1u)); }
 static int build_tri_accel_host(const float* rec, uint32_t T, TriAccelHost& out) {
     const uint32_t K = RT_ACCEL_K;
     out.nc = out.nl = 0;
@@ -389,15 +391,15 @@ static int build_tri_accel_host(const float* rec, uint32_t T, TriAccelHost& out)
     }
     (void)lo; (void)hi;
     const uint32_t nc = (T + K - 1) / K;
-    uint32_t n_lvl[RT_TACC_LEVELS], nl = 1, total = nc;
+    uint32_t n_lvl[RT_TACC_LEVELS], nl = 1;
     n_lvl[0] = nc;
-    out.off[0] = 0;
     while (nl < RT_TACC_LEVELS && n_lvl[nl - 1] > 4u) {
         n_lvl[nl] = (n_lvl[nl - 1] + 7u) / 8u;
-        out.off[nl] = total;
-        total += n_lvl[nl];
         nl++;
     }
+    const uint32_t ntop = n_lvl[nl - 1];
+    for (uint32_t l = 0; l < nl; l++) out.off[l] = tacc_level_base_host(ntop, nl - 1u - l);
+    const uint32_t total = tacc_level_base_host(ntop, nl); /* ntop * (8^nl - 1) / 7 slots; the ones past a level's last node are never read */
     out.node.assign(8 * (size_t)total, 0.0f);
     out.rec.assign(12 * (size_t)nc * K, 0.0f); /* padding: all zero -> det == 0, never hit */
     out.idx.assign((size_t)nc * K, 0xffffffffu);
@@ -429,11 +431,12 @@ static int build_tri_accel_host(const float* rec, uint32_t T, TriAccelHost& out)
                 hs += o[4 + a];
             }
             o[3] = 0.0f;
-            o[7] = nextafterf((float)hs, INFINITY);
+            o[7] = nextafterf((float)(hs * (1.0 / 4096.0)), INFINITY);
         }
     }
     out.nc = nc;
     out.nl = nl;
+    out.ntop = ntop;
     return 1;
 }
 static int prep_tri_accel(rtb_engine* e) {
@@ -451,7 +454,7 @@ static int prep_tri_accel(rtb_engine* e) {
     CU(cudaMemcpyAsync((char*)e->tacc.p + b0 + b1, h.idx.data(), b2, cudaMemcpyHostToDevice, e->stream), "H2D triangle accel");
     CU(cudaStreamSynchronize(e->stream), "triangle accel upload"); /* the vectors die with this frame */
     e->tacc_nc = h.nc; e->tacc_nl = h.nl; e->tacc_nodes = (uint32_t)(h.node.size() / 8);
-    memcpy(e->tacc_off, h.off, sizeof h.off);
+    e->tacc_ntop = h.ntop;
     return 0;
 }
 
@@ -629,7 +632,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
         fp.tacc_rec = (const float4*)((const char*)e->tacc.p + b0);
         fp.tacc_idx = (const uint32_t*)((const char*)e->tacc.p + b0 + b1);
         fp.tacc_nc = e->tacc_nc; fp.tacc_nl = e->tacc_nl;
-        memcpy(fp.tacc_off, e->tacc_off, sizeof fp.tacc_off);
+        fp.tacc_ntop = e->tacc_ntop;
     }
     if (use_accel && e->acc_nc > 0u) {
         const size_t b0 = (size_t)e->acc_nc * 16, b1 = (size_t)e->acc_nc * RT_ACCEL_K * 16;

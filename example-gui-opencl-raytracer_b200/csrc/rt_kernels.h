@@ -119,14 +119,14 @@ struct RtFrameParams {
     uint32_t done_expected;     /* CTAs of the frame's kernels (render_frame + render_tree); set by the launcher */
     uint32_t* done_flag;        /* may be NULL; device-visible: a peer GPU's memory (CUDA IPC) or mapped host memory */
     uint32_t done_value;
-    /* N4 over the triangles of extension X1 (rt_trace_accel.cuh; NULL / 0 = brute force): bounding spheres in the
-     * encoding of acc_cl, level 0 = clusters of RT_ACCEL_K triangles in Morton order of their centroids, level l + 1 =
-     * 8 consecutive nodes of level l; level l starts at node tacc_off[l] */
+    /* N4 over the triangles of extension X1 (rt_trace_accel.cuh; NULL / 0 = brute force): axis-aligned boxes {centre,
+     * half extents} of two float4 each; level 0 = clusters of RT_ACCEL_K triangles in a kd-style order, level l + 1 = 8
+     * consecutive nodes of level l, tacc_nl levels, the top one with tacc_ntop nodes; stored top level first, every
+     * level padded to tacc_ntop * 8^(tacc_nl - 1 - l) slots (rt_trace_accel.cuh: tacc_level_base) */
     const float4* tacc_node;
     const float4* tacc_rec;   /* [tacc_nc * RT_ACCEL_K * 3] {v0, e1, e2} in cluster order; padding records are all zero (det == 0: never hit) */
     const uint32_t* tacc_idx; /* [tacc_nc * RT_ACCEL_K] original triangle index */
-    uint32_t tacc_nc, tacc_nl;
-    uint32_t tacc_off[RT_TACC_LEVELS];
+    uint32_t tacc_nc, tacc_nl, tacc_ntop;
 };
 
 /* scene_prep: wire arrays -> blob. */

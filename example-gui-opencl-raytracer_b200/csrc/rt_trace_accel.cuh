@@ -138,12 +138,13 @@ __device__ __forceinline__ bool shadow_spheres_accel(const RayF& r, float len, c
  *    at 1080p; bench.py compares the 4K frame), not a proof.  X1 itself has no reference counterpart (parity
  *    unpinned, SURVEY.md 8(a') X1). */
 struct TaccRay {
-    V3 o, inv; /* origin, 1 / direction per axis (IEEE: +-inf for a zero component) */
+    V3 o, inv, ainv; /* origin, 1 / direction per axis (IEEE: +-inf for a zero component), |1 / direction| */
 };
 __device__ __forceinline__ TaccRay tacc_ray(V3 o, V3 d) {
     TaccRay q;
     q.o = o;
     q.inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    q.ainv = mk(fabsf(q.inv.x), fabsf(q.inv.y), fabsf(q.inv.z));
     return q;
 }
 /* false: a NaN or an infinity among the six numbers (NaN test results then depend on the visiting order) */
@@ -151,49 +152,51 @@ __device__ __forceinline__ bool tacc_finite(const RayF& r) {
     const float chk = ((fabsf(r.o.x) + fabsf(r.o.y)) + fabsf(r.o.z)) + ((fabsf(r.d.x) + fabsf(r.d.y)) + fabsf(r.d.z));
     return chk <= 3.0e38f;
 }
-/* true when no triangle inside the box {c, h} can yield a hit with 0 < t <= tmax (tmax = +inf: any t) */
+/* true when no triangle inside the box {c, h} can yield a hit with 0 < t <= tmax (tmax = +inf: any t).  Per axis the
+ * grown slab is crossed during [tc - te, tc + te], tc = (c - o) / d, te = (h + mu) / |d|.  The arithmetic here is the
+ * cull's own (explicit FMAs are fine: nothing downstream depends on its bits, only on its margin). */
 __device__ __forceinline__ bool tacc_cull(const TaccRay& q, float4 c, float4 h, float tmax) {
     const float ax = c.x - q.o.x, ay = c.y - q.o.y, az = c.z - q.o.z;
-    const float mu = (((fabsf(ax) + fabsf(ay)) + fabsf(az)) + h.w) * 0.000244140625f; /* 2^-12; h.w = hx + hy + hz, rounded up */
-    const float ex = h.x + mu, ey = h.y + mu, ez = h.z + mu;
-    const float x0 = (ax - ex) * q.inv.x, x1 = (ax + ex) * q.inv.x;
-    const float y0 = (ay - ey) * q.inv.y, y1 = (ay + ey) * q.inv.y;
-    const float z0 = (az - ez) * q.inv.z, z1 = (az + ez) * q.inv.z;
-    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
-    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
-    /* 0 * inf = NaN (the origin exactly on a grown face of a slab the ray is parallel to) drops out of fminf / fmaxf and
-     * leaves that slab to its other, infinite bound: either outcome is fine at a distance of exactly mu.  Rays with a
-     * non-finite origin or direction never get here (the callers walk those by brute force). */
+    const float mu = __fmaf_rn((fabsf(ax) + fabsf(ay)) + fabsf(az), 0.000244140625f, h.w); /* 2^-12 |o - c|_1 + 2^-12 |h|_1 (h.w, rounded up on the host) */
+    const float cx = ax * q.inv.x, cy = ay * q.inv.y, cz = az * q.inv.z;
+    const float ex = (h.x + mu) * q.ainv.x, ey = (h.y + mu) * q.ainv.y, ez = (h.z + mu) * q.ainv.z;
+    const float tn = fmaxf(fmaxf(cx - ex, cy - ey), cz - ez);
+    const float tf = fminf(fminf(cx + ex, cy + ey), cz + ez);
+    /* a direction component of exactly 0: inv = inf, so tc = +-inf (NaN when the origin sits on the centre plane) and
+     * te = inf; inf - inf = NaN drops out of fminf / fmaxf, which leaves that axis unconstrained -- right when the origin
+     * is inside the slab, merely a missed cull when it is outside.  Rays with a non-finite origin or direction never get
+     * here (the callers walk those by brute force); every comparison below is false on NaN: "do not cull". */
     return tn > tf || tf < 0.0f || tn > tmax;
 }
+/* node (level l, i): levels are stored top first, each padded to ntop * 8^(top - l) slots, so level l starts at
+ * ntop * (8^(top - l) - 1) / 7 -- and (8^m - 1) / 7 is the bit pattern 001001...001 of m ones */
+__device__ __forceinline__ uint32_t tacc_level_base(uint32_t ntop, uint32_t m) { return ntop * (0x09249249u & ((1u << (3u * m)) - 1u)); }
 template <class TMAX, class LEAF>
-__device__ __forceinline__ void tacc_walk(const TaccRay& q, const Geo& g, uint32_t k0, uint32_t k1, TMAX&& tmax, LEAF&& leaf) {
-    const uint32_t top = g.tacc_nl - 1u;
-    uint32_t k = k0;
+__device__ __forceinline__ void tacc_walk(const TaccRay& q, const Geo& g, TMAX&& tmax, LEAF&& leaf) {
+    const uint32_t top = g.tacc_nl - 1u, nc = g.tacc_nc, ntop = g.tacc_ntop;
+    uint32_t k = 0, l = top;
     for (;;) {
-        /* search: advance to the next cluster that survives its ancestors' boxes and its own */
+        /* search: one node per step -- the level-l ancestor that starts at cluster position k, then down, or past it */
         bool have = false;
 #pragma unroll 1
-        while (k < k1) {
-            uint32_t lv = k ? (uint32_t)(__ffs((int)k) - 1) / 3u : top;
-            lv = lv < top ? lv : top;
-            const float tm = tmax();
-            bool culled = false;
-#pragma unroll
-            for (int l = RT_TACC_LEVELS - 1; l >= 0; --l) {
-                if (!culled && (uint32_t)l <= lv) {
-                    const float4* nd = g.tacc_node + 2u * (g.tacc_off[l] + (k >> (3 * l)));
-                    if (tacc_cull(q, __ldg(nd), __ldg(nd + 1), tm)) {
-                        k += 1u << (3 * l);
-                        culled = true;
-                    }
-                }
+        while (k < nc) {
+            const float4* nd = g.tacc_node + 2u * (tacc_level_base(ntop, top - l) + (k >> (3u * l)));
+            if (tacc_cull(q, __ldg(nd), __ldg(nd + 1), tmax())) {
+                k += 1u << (3u * l);
+                const uint32_t up = (uint32_t)(__ffs((int)k) - 1) / 3u; /* k != 0 here */
+                l = up < top ? up : top;
+            } else if (l != 0u) {
+                l--;
+            } else {
+                have = true;
+                break;
             }
-            if (!culled) { have = true; break; }
         }
         if (!have) return;
         if (leaf(k)) return;
         k++;
+        const uint32_t up = (uint32_t)(__ffs((int)k) - 1) / 3u;
+        l = up < top ? up : top;
     }
 }
 
@@ -203,8 +206,7 @@ __device__ __forceinline__ bool closest_triangles_accel(const RayF& r, const Geo
     if (c.t != c.t || c.tL != c.tL || !tacc_finite(r)) return true;
     const TaccRay q = tacc_ray(r.o, r.d);
     bool odd = false;
-    tacc_walk(q, g, 0u, g.tacc_nc,
-              [&]() { return ((c.k >= 0 && !c.occluded && c.tL > c.t) ? c.tL : c.t) * 1.00001f; },
+    tacc_walk(q, g, [&]() { return ((c.k >= 0 && !c.occluded && c.tL > c.t) ? c.tL : c.t) * 1.00001f; },
               [&](uint32_t k) {
                   for_triangle_hits(r.o, r.d, g.tacc_rec + 3u * kAccK * k, kAccK, tl, [&](uint32_t j, float t1) {
                       const int orig = (int)__ldg(g.tacc_idx + kAccK * k + j);
@@ -225,7 +227,7 @@ __device__ __forceinline__ bool shadow_triangles_accel(const RayF& r, float len,
     const TaccRay q = tacc_ray(r.o, r.d);
     const float tm = len * 1.00001f;
     bool blocked = false;
-    tacc_walk(q, g, 0u, g.tacc_nc, [&]() { return tm; }, [&](uint32_t k) {
+    tacc_walk(q, g, [&]() { return tm; }, [&](uint32_t k) {
         blocked = for_triangle_hits(r.o, r.d, g.tacc_rec + 3u * kAccK * k, kAccK, tl, [&](uint32_t, float t1) { return !(t1 >= len); });
         return blocked;
     });

@@ -213,10 +213,11 @@ int rtb_debug_accel_build(const void* spheres, uint32_t S, float* clusters, floa
                           uint32_t* n_clusters, uint32_t* n_groups);
 /* ... and the N4 hierarchy over the triangles of extension X1 (built on first use when option "accel" is on), from
  * {v0, e1, e2} records of 12 floats (what tri_prep makes of the wire array): nodes[8*n_nodes] = axis-aligned boxes
- * {centre.xyz, 0, half extents.xyz, their sum}, level l at level_offset[l] (level 0 = clusters of 8 triangles in Morton
- * order of their centroids, level l+1 = 8 nodes of level l);
- * sorted_records[12*8*nc] (padding all zero); index[8*nc] original triangle index (0xffffffff = padding).  Array pointers
- * may be NULL (call once for the sizes: n_nodes <= nc * 8 / 7 + 6).  Returns 1 when built, 0 when the mesh stays brute force. */
+ * {centre.xyz, 0, half extents.xyz, 2^-12 of their sum}, level l at level_offset[l] (level 0 = clusters of 8 triangles in a
+ * kd-style order -- every node hands the lower half of its capacity, along the longest axis of its centroids, to its
+ * lower half --, level l+1 = 8 nodes of level l; stored top level first, each level padded to ntop * 8^(levels-1-l) slots,
+ * n_nodes counts the slots); sorted_records[12*8*nc] (padding all zero); index[8*nc] original triangle index (0xffffffff =
+ * padding).  Array pointers may be NULL (call once for the sizes).  Returns 1 when built, 0 when the mesh stays brute force. */
 int rtb_debug_tri_accel_build(const float* records, uint32_t T, float* nodes, float* sorted_records, uint32_t* index,
                               uint32_t* n_clusters, uint32_t* n_levels, uint32_t level_offset[6], uint32_t* n_nodes);
 /* Diagnostic builds only (e.g. -DRT_TREE_CLOCKS): the raw counter words the last launch left behind. */

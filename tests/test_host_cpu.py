@@ -399,16 +399,20 @@ def test_triangle_hierarchy_contains_its_triangles(pkg):
         assert L_.rtb_debug_tri_accel_build(vp(rec), T, vp(nodes), vp(srt), vp(idx), C.byref(nc), C.byref(nl), off, C.byref(nn)) == 1
         sizes = [nc.value]
         for l in range(1, nl.value):
-            assert off[l] == off[l - 1] + sizes[-1]
             sizes.append((sizes[-1] + 7) // 8)
-        assert off[0] == 0 and nn.value == sum(sizes) and (sizes[-1] <= 4 or nl.value == 6)
+        ntop, top = sizes[-1], nl.value - 1
+        assert ntop <= 4 or nl.value == 6
+        for l in range(nl.value):                                  # top level first, level l padded to ntop * 8^(top-l) slots
+            assert off[l] == ntop * ((8 ** (top - l) - 1) // 7) and sizes[l] <= ntop * 8 ** (top - l)
+        assert nn.value == ntop * ((8 ** nl.value - 1) // 7)
         real = idx != 0xFFFFFFFF
         assert sorted(idx[real].tolist()) == list(range(T)) and real[:T].all() and not real[T:].any()
         srt = srt.reshape(-1, 12)
         assert np.array_equal(srt[:T].view(np.uint32), rec[idx[:T]].view(np.uint32))
         assert not srt[T:].any()
         node8 = nodes.reshape(-1, 8).astype(np.float64)
-        assert np.all(node8[:, 7] >= node8[:, 4:7].sum(axis=1)) and np.all(node8[:, 4:7] > 0)
+        used = np.concatenate([np.arange(off[l], off[l] + sizes[l]) for l in range(nl.value)])
+        assert np.all(node8[used, 7] * 4096 >= node8[used, 4:7].sum(axis=1)) and np.all(node8[used, 4:7] > 0)
         r64 = rec.astype(np.float64)
         for j in range(T):
             i = int(idx[j])
@@ -421,7 +425,7 @@ def test_triangle_hierarchy_contains_its_triangles(pkg):
         ext = np.stack([r64[idx[:T], 0:3], r64[idx[:T], 0:3] + r64[idx[:T], 4:7], r64[idx[:T], 0:3] + r64[idx[:T], 8:11]], axis=1)
         for k in range(nc.value):
             pts = ext[8 * k: 8 * k + 8].reshape(-1, 3)
-            assert np.all(2 * node8[k, 4:7] <= (pts.max(axis=0) - pts.min(axis=0)) * (1 + 1e-5) + 1e-6)
+            assert np.all(2 * node8[off[0] + k, 4:7] <= (pts.max(axis=0) - pts.min(axis=0)) * (1 + 1e-5) + 1e-6)
     bad = rec.copy(); bad[5, 4] = np.inf
     assert L_.rtb_debug_tri_accel_build(vp(bad), T, None, None, None, C.byref(nc), C.byref(nl), off, C.byref(nn)) == 0
     assert L_.rtb_debug_tri_accel_build(vp(rec), 15, None, None, None, C.byref(nc), C.byref(nl), off, C.byref(nn)) == 0
