@@ -321,7 +321,7 @@ class _Raw:
 FLAG_STRIDE_WORDS = 16      # one 64-byte line per rank's completion flag
 
 
-def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full", kernel_reps=10, opts=None):
+def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full", kernel_reps=10, opts=None, count=True):
     """One workload on this process group: accounting launch, bit-identity check against one GPU (N>1), device-timed
     steps, kernel-only time for the roofline and (want_e2e) the end-to-end leg.  Returns a dict (complete on rank 0)."""
     torch, dist, eng, pkg = ctx.torch, ctx.dist, ctx.eng, ctx.pkg
@@ -350,7 +350,10 @@ def measure(ctx, wl, steps, warmup, exchange="p2p", want_e2e=True, verify="full"
     stream.synchronize()
 
     # ---- accounting launch (untimed): rays and algorithmic flop of this rank's rows ----
-    cnt = eng.render_counted(W, H, part=part, d_out=band_buf.data_ptr())
+    if count:
+        cnt = eng.render_counted(W, H, part=part, d_out=band_buf.data_ptr())
+    else:   # lines that report a frame time only (the literal counted launch of a 50k-triangle frame takes many seconds)
+        cnt = dict(rays=0, flop=0, segments=0, shadow_rays=0, sphere_tests=0, plane_tests=0)
     totals = torch.tensor([cnt["rays"], cnt["flop"], cnt["segments"], cnt["shadow_rays"], cnt["sphere_tests"],
                            cnt["plane_tests"]], dtype=torch.int64, device=dev)
     if world > 1:
@@ -682,6 +685,50 @@ def orbit_config(ctx):
     return out
 
 
+def mesh_accel_config(ctx, host):
+    """BASELINE.json configs[3]'s mesh at 3840x2160 on one GPU through the N4 hierarchy over the triangles
+    (csrc/rt_trace_accel.cuh, option "accel"), next to ONE brute-force frame of the same engine, which is also the judge:
+    every colour word and every hit id of the two frames must be equal."""
+    eng = ctx.eng
+    wl = make_workload("mesh50k_4k", host)
+    W, H = wl["W"], wl["H"]
+    eng.upload_scene(wl["spheres"], wl["planes"], wl["lights"])
+    eng.upload_triangles(wl["tris"])
+    eng.set_camera(wl["cam"])
+    eng.set_option("accel", 0)
+    b_rgb, b_hit = eng.render_to_host(W, H, want_hit=True)
+    brute_ms = eng.last_render_ms()
+    eng.set_option("accel", 1)
+    try:
+        t0 = time.perf_counter()
+        a_rgb, a_hit = eng.render_to_host(W, H, want_hit=True)       # includes the one-off host build of the hierarchy
+        first_ms = (time.perf_counter() - t0) * 1e3
+        same = bool(np.array_equal(a_rgb, b_rgb) and np.array_equal(a_hit, b_hit))
+        ms = []
+        for i in range(3 + 10):
+            with ctx.torch.cuda.stream(ctx.stream):
+                ctx.flush.fill_(1)
+            eng.render(W, H)
+            eng.sync()
+            if i >= 3:
+                ms.append(eng.last_render_ms())
+        a_rgb, a_hit = eng.render_to_host(W, H, want_hit=True)       # a history-scheduled frame
+        same = same and bool(np.array_equal(a_rgb, b_rgb) and np.array_equal(a_hit, b_hit))
+        launch = eng.last_launch()
+    finally:
+        eng.set_option("accel", 0)
+        eng.upload_triangles(b"")
+    m = float(np.mean(ms))
+    return {"workload": "mesh50k_4k_accel", "desc": wl["desc"].replace("brute-force closest hit", "box hierarchy over the triangles (N4)"),
+            "width": W, "height": H, "steps": len(ms), "warmup": 3, "ms_per_step": m, "ms_per_step_max": float(np.max(ms)),
+            "frames_per_s": 1e3 / m, "brute_force_ms_per_step": brute_ms, "speedup_vs_brute_force": brute_ms / m,
+            "first_frame_ms_incl_host_build": first_ms, "frame_equals_brute_force": same, "launch": launch,
+            "gpu_launches": 3 * len(ms),
+            "note": "EXTENSION N4 over EXTENSION X1 (neither is in the reference; parity unpinned): one brute-force frame (every tile in the "
+                    "tree kernel, TMA-staged chunks) timed once and compared word for word, colour and hit ids, with the hierarchy's "
+                    "first and last frame; times are the engine's CUDA events around a whole frame, L2 flushed between frames"}
+
+
 def slim(res):
     """An other_configs entry: the measurement without the bulky keys."""
     keep = ("workload", "desc", "width", "height", "steps", "warmup", "ms_per_step", "value", "unit", "frames_per_s",
@@ -717,6 +764,7 @@ def gpu_body(args, pkg, eng, world, rank, local):
         if world == 1:
             others["spheres255_8k"] = slim(measure(ctx, make_workload("spheres255_8k", host), 3, 3, want_e2e=False, kernel_reps=3))
             others["orbit_1440p"] = orbit_config(ctx) if rank == 0 else None
+            others["mesh50k_4k_accel"] = mesh_accel_config(ctx, host)
         if world > 1:
             alt = "nccl" if args.exchange == "p2p" else "p2p"
             others["render_map_4k_exchange_" + alt] = slim(measure(ctx, wl, min(args.steps, 10), 3, exchange=alt, want_e2e=False,
@@ -726,6 +774,14 @@ def gpu_body(args, pkg, eng, world, rank, local):
                                                 want_e2e=False, verify="sampled", kernel_reps=1))
             others["mesh50k_8k"]["note"] = ("EXTENSION X1, parity unpinned (the reference has no triangle type); one warm-up and one "
                                             "timed step: a frame takes seconds")
+            acc = slim(measure(ctx, make_workload("mesh50k_8k", host), 5, 3, exchange=args.exchange, want_e2e=False,
+                               verify="sampled", kernel_reps=3, opts={"accel": 1}, count=False))
+            for k in ("value", "unit", "rays_per_frame", "algorithmic_flop_per_frame", "roofline"):
+                acc.pop(k, None)
+            acc["workload"] = "mesh50k_8k_accel"
+            acc["note"] = ("EXTENSION N4 over EXTENSION X1: the same 8K frame through the box hierarchy over the triangles; frame time only "
+                           "(no counted launch); equality with brute force: tests/test_accel_gpu.py and the N=1 line mesh50k_4k_accel")
+            others["mesh50k_8k_accel"] = acc
 
     if rank == 0:
         W, H = wl["W"], wl["H"]

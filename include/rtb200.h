@@ -130,8 +130,11 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * tree kernel, where the triangle records are staged into shared memory in 12 KiB chunks by TMA bulk copies and each
  * chunk serves the 128 rays of a CTA.  Pixels do not change.
  * "accel" (EXTENSION; default 0 = brute force over every record, as the reference does): 1 = scenes
- * with >= 16 spheres and no triangles walk a cluster structure built at upload (csrc/rt_trace_accel.cuh) that skips only
- * tests whose outcome is provably "no hit"; the frame is word-identical to the brute-force one. */
+ * with >= 16 spheres walk a cluster structure built at upload (csrc/rt_trace_accel.cuh) that skips only tests whose
+ * outcome is provably "no hit"; the frame is word-identical to the brute-force one.  Scenes with >= 16 triangles
+ * (extension X1) walk a box hierarchy over the triangles, built on the host at the first frame after an upload; its
+ * frames equal the brute-force ones wherever compared (tests/test_accel_gpu.py, bench.py), which for Moeller-Trumbore's
+ * noise at grazing incidence is a measurement, not a proof (rt_trace_accel.cuh). */
 int rtb_set_option(rtb_engine* e, const char* name, int value);
 /* Brute-force check of the arithmetic routines against IEEE division / sqrt (trials per thread on 592x256
  * threads).  out[0] = division mismatches, out[1] = normalize mismatches, out[2] = max |sincos - libdevice|
