@@ -78,7 +78,22 @@ struct rtb_engine {
     bool have_cam = false;
 
     DevBuf frame, hit, sched; /* sched: tile counter (4 B) + work counters */
-    DevBuf tile_cost, tile_order, tile_hist;
+    DevBuf tile_cost[2], tile_order[2], tile_hist[2]; /* two sets of queue buffers (and two 256-byte halves of `sched`): the
+                                                         frame being rendered reads one while the next frame's queue is built in the other */
+    int set_cur = 0;          /* the set the most recent ordered frame used */
+    int cost_hist_set = -1;   /* the set whose cost buffer holds measured-time costs of a frame with the tk_* geometry (-1: none) */
+    /* schedule look-ahead: right after frame n's kernels are in the stream, frame n+1's queue is built on a second
+     * stream from frame n-1's tile times, so that the two small scheduling kernels leave the frame's critical path */
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t ev_look = nullptr;
+    bool look_pending = false; /* ev_look has been recorded and the main stream has not waited for it yet */
+    bool look_valid = false;   /* ... and what it describes: */
+    int look_set = 0, look_time = 0, look_launcher = 0;
+    uint32_t look_W = 0, look_H = 0, look_total = 0, look_band = 0, look_parts = 0, look_part = 0;
+    uint32_t look_split = 0, look_split32 = 0, look_tree = 0, look_group = 0, look_cih = 0;
+    unsigned long long look_scene = 0;
+    int opt_lookahead = 1;
+    uint32_t last_sched_off = 0; /* which half of `sched` the last frame used (rtb_debug_counters) */
     DevBuf tree_slab;         /* per-warp node storage of the level-wise pixel-tree trace (rt_trace_tree.cuh) */
     DevBuf jump;              /* [15][32] xorshift32 jump-ahead matrices for this scene's light count */
     uint32_t jump_L = 0xffffffffu;
@@ -92,10 +107,10 @@ struct rtb_engine {
     bool tacc_valid = false;  /* built (or found unbuildable: tacc_nc == 0) for the current triangle array */
     uint32_t tacc_nc = 0, tacc_nl = 0, tacc_nodes = 0, tacc_ntop = 0;
     int opt_tree = 1, opt_tree_cap = 8192, opt_tree_min_cost = 0 /* 0 = automatic */, opt_tree_group_max_cost = 0;
-    bool cost_hist_valid = false; /* tile_cost holds measured-time costs of a frame with this geometry */
-    DevBuf tile_time[2];      /* measured per-tile times: this frame's and the previous frame's (ping-pong) */
-    int time_cur = 0;
-    bool time_valid = false;  /* tile_time[1 - time_cur] describes a frame of the geometry below */
+    DevBuf tile_time[3];      /* measured per-tile times: this frame's, the previous frame's, and the one before (which the
+                                 look-ahead clears for the next frame) */
+    int time_cur = 0;         /* the buffer the next history frame writes */
+    bool time_valid = false;  /* tile_time[(time_cur + 2) % 3] describes a frame of the geometry below */
     uint32_t tk_W = 0, tk_H = 0, tk_total = 0, tk_band = 0, tk_parts = 0, tk_part = 0;
     unsigned long long scene_gen = 0, tk_scene_gen = 0;
     int opt_trace = 0, opt_tile_order = 1, opt_coop_min_cost = 0, opt_split_min_cost = 0 /* 0 = automatic */, opt_split32_min_cost = 0 /* 0 = automatic */, opt_history = 1, opt_wide_min_records = 64, opt_wide_max_live = -1;
@@ -121,13 +136,17 @@ void rtb_destroy(rtb_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->stream2) cudaStreamSynchronize(e->stream2);
     e->tris.release(); e->tri_rec.release(); e->spheres.release(); e->planes.release(); e->lights.release(); e->blob.release();
     e->tex.release(); e->sky.release(); e->frame.release(); e->hit.release(); e->sched.release();
-    e->tile_cost.release(); e->tile_order.release(); e->tile_hist.release(); e->tile_time[0].release(); e->tile_time[1].release();
+    for (int k = 0; k < 2; k++) { e->tile_cost[k].release(); e->tile_order[k].release(); e->tile_hist[k].release(); }
+    for (int k = 0; k < 3; k++) e->tile_time[k].release();
     e->tree_slab.release(); e->wait_word.release(); e->jump.release(); e->accel.release(); e->tacc.release();
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->evk) cudaEventDestroy(e->evk);
+    if (e->ev_look) cudaEventDestroy(e->ev_look);
+    if (e->stream2) cudaStreamDestroy(e->stream2);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -137,8 +156,11 @@ static int create_impl(rtb_engine* e) {
     CU(cudaEventCreate(&e->ev0), "cudaEventCreate");
     CU(cudaEventCreate(&e->ev1), "cudaEventCreate");
     CU(cudaEventCreate(&e->evk), "cudaEventCreate");
-    if (e->sched.ensure(256)) return -2;
-    CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "cudaMemsetAsync");
+    CU(cudaStreamCreateWithFlags(&e->stream2, cudaStreamNonBlocking), "cudaStreamCreate");
+    if (const char* la = getenv("RTB_LOOKAHEAD")) e->opt_lookahead = atoi(la) != 0; /* A/B hook for callers behind cl_wrap_* (option "lookahead") */
+    CU(cudaEventCreateWithFlags(&e->ev_look, cudaEventDisableTiming), "cudaEventCreate");
+    if (e->sched.ensure(512)) return -2;
+    CU(cudaMemsetAsync(e->sched.p, 0, 512, e->stream), "cudaMemsetAsync");
     CU(cudaStreamSynchronize(e->stream), "cudaStreamSynchronize");
     return 0;
 }
@@ -664,22 +686,39 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     e->mirror = nullptr;
     e->mirror_global = false;
     if ((uintptr_t)fp.mirror & 15) return fail(-1, "rtb_render: mirror buffer must be 16-byte aligned");
-    fp.tile_counter = (unsigned int*)e->sched.p;
-    fp.tree_counter = (unsigned int*)((char*)e->sched.p + 4);
-    fp.done_counter = (unsigned int*)((char*)e->sched.p + 32);
+    auto bind_sched = [&](int set) { /* cursors, counters: one 256-byte half of `sched` per set of queue buffers */
+        char* b = (char*)e->sched.p + 256 * set;
+        fp.tile_counter = (unsigned int*)b;
+        fp.tree_counter = (unsigned int*)(b + 4);
+        fp.done_counter = (unsigned int*)(b + 32);
+        fp.counters = (unsigned long long*)(b + 64);
+        e->last_sched_off = 256u * (uint32_t)set;
+    };
+    bind_sched(0);
     fp.done_flag = e->done_flag;
     fp.done_value = e->done_value;
     e->done_flag = nullptr;
-    fp.counters = (unsigned long long*)((char*)e->sched.p + 64);
     fp.tiles_x = (W + 7) / 8;
     fp.tiles_y = (rows + 3) / 4;
 
     e->last.tiles = fp.tiles_x * fp.tiles_y;
     if (rows == 0) { e->timed = false; return 0; }
 
+    if (e->look_pending) { /* whatever this frame does with the queue buffers comes after the look-ahead that may be writing them */
+        CU(cudaStreamWaitEvent(e->stream, e->ev_look, 0), "wait for the schedule look-ahead");
+        e->look_pending = false;
+    }
     CU(cudaEventRecord(e->ev0, e->stream), "event record");
     const bool ordered = e->opt_tile_order && e->last.tiles >= 4096 && e->last.tiles < (1u << 24);
-    if (!ordered) CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter"); /* else tile_order zeroes it */
+    if (!ordered) {
+        CU(cudaMemsetAsync(e->sched.p, 0, 256, e->stream), "reset tile counter"); /* else tile_order zeroes it */
+        e->look_valid = false;
+    }
+    bool history_frame = false, same_frame = false;
+    int set = 0, launcher = e->T ? (use_tacc ? 3 : 2) : (use_accel ? 1 : 0);
+    auto tile_order_launcher = [&](int which) {
+        return which == 3 ? rt_launch_tile_order_tacc : (which == 2 ? rt_launch_tile_order_tri : (which == 1 ? rt_launch_tile_order_acc : rt_launch_tile_order));
+    };
     fp.order = nullptr;
     fp.cost = nullptr;
     fp.coop_min_cost = (uint32_t)e->opt_coop_min_cost;
@@ -691,22 +730,26 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     /* queue entries carry the tile index in 24 bits (rt_kernels.cu): beyond 2^24 tiles (> 536 Mpixel) the queue stays row-major */
     if (e->opt_tile_order && e->last.tiles >= 4096 && e->last.tiles < (1u << 24)) { /* small frames: the queue is short enough as it is */
         const size_t nt = e->last.tiles;
-        const bool fresh_hist = e->tile_hist.p == nullptr;
-        if (e->tile_cost.ensure(nt * 4) || e->tile_order.ensure(nt * 128) || e->tile_hist.ensure(1024)) return -2;
-        if (fresh_hist) CU(cudaMemsetAsync(e->tile_hist.p, 0, 1024, e->stream), "zero tile histogram"); /* once: tile_order leaves it clean */
+        for (int k = 0; k < 2; k++) {
+            const bool fresh_hist = e->tile_hist[k].p == nullptr;
+            if (e->tile_cost[k].ensure(nt * 4) || e->tile_order[k].ensure(nt * 128) || e->tile_hist[k].ensure(1024)) return -2;
+            if (fresh_hist) CU(cudaMemsetAsync(e->tile_hist[k].p, 0, 1024, e->stream), "zero tile histogram"); /* once: tile_order leaves it clean */
+        }
         /* scheduling hint: the previous frame's measured tile times when it had this geometry and scene (the camera may
          * have moved: frames of an interactive sweep are coherent), else the skeleton trace.  Pixels never depend on it. */
         const bool same = e->time_valid && e->tk_W == W && e->tk_H == H && e->tk_total == total && e->tk_band == pp.band_rows &&
                           e->tk_parts == pp.parts && e->tk_part == pp.part && e->tk_scene_gen == e->scene_gen + e->T;
         if (e->opt_history && mode == 0) {
             /* each buffer: 16 bytes for the frame's sum, then one word per tile */
-            if (e->tile_time[0].ensure(nt * 4 + 16) || e->tile_time[1].ensure(nt * 4 + 16)) return -2;
+            if (e->tile_time[0].ensure(nt * 4 + 16) || e->tile_time[1].ensure(nt * 4 + 16) || e->tile_time[2].ensure(nt * 4 + 16)) return -2;
+            history_frame = true;
+            same_frame = same;
             fp.tile_time_sum = (unsigned long long*)e->tile_time[e->time_cur].p;
             fp.tile_time = (uint32_t*)((char*)e->tile_time[e->time_cur].p + 16);
-            if (!same) CU(cudaMemsetAsync(e->tile_time[e->time_cur].p, 0, nt * 4 + 16, e->stream), "reset tile times"); /* history frames: tile_cost_history zeroes it */
             if (same) {
-                fp.tile_time_sum_prev = (const unsigned long long*)e->tile_time[1 - e->time_cur].p;
-                fp.tile_time_prev = (const uint32_t*)((const char*)e->tile_time[1 - e->time_cur].p + 16);
+                const int tp = (e->time_cur + 2) % 3; /* the previous frame's */
+                fp.tile_time_sum_prev = (const unsigned long long*)e->tile_time[tp].p;
+                fp.tile_time_prev = (const uint32_t*)((const char*)e->tile_time[tp].p + 16);
                 /* measured costs: a tile is a tail risk when its time is comparable to the time the whole queue needs,
                  * T = mean * tiles / resident warps.  Automatic thresholds (they reproduce the optima of the sweeps in
                  * tools/exp/sweep_split.py at N = 1, 2, 4, 8): four warps from 0.75 T, one pixel per warp from 3 T.
@@ -740,7 +783,7 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                         if (fp.split32_min_cost < t) t = fp.split32_min_cost;
                         fp.tree_min_cost = t;
                         fp.tree_group_max_cost = e->opt_tree_group_max_cost > 0 ? (uint32_t)e->opt_tree_group_max_cost : 0u; /* pooling four entries per pass lengthens the chains it is there to shorten (tools/exp/sweep_tree.py): off unless asked for */
-                        fp.cost_is_history = e->cost_hist_valid ? 1u : 0u;
+                        fp.cost_is_history = e->cost_hist_set >= 0 ? 1u : 0u;
                     } else if (wide_scene) {
                         /* many-sphere scenes: a split entry's few rays are walked by all 32 lanes (WIDE variant), so
                          * splitting costs little and the tail of a part is its longest tile: rows from 0.5 T, single
@@ -755,23 +798,45 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
                     }
                 }
             }
-            e->cost_hist_valid = same; /* this frame's costs come from measured times: the next one may lean on them */
-            e->time_cur = 1 - e->time_cur;
+        } else if (mode == 0) {
+            e->time_valid = false;
+            e->cost_hist_set = -1;
+        } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
+        if (tri_all) { fp.split_min_cost = 64u; fp.split32_min_cost = 64u; fp.tree_min_cost = 64u; } /* whole tiles, all of them through render_tree */
+        /* the queue: already built by the look-ahead of the previous frame (same geometry, scene, thresholds, kernel
+         * family; it also cleared this frame's time buffer and its half of `sched`), or built here and now */
+        const bool looked = e->look_valid && history_frame && same_frame && e->look_time == e->time_cur && e->look_launcher == launcher &&
+                            e->look_W == W && e->look_H == H && e->look_total == total && e->look_band == pp.band_rows &&
+                            e->look_parts == pp.parts && e->look_part == pp.part && e->look_scene == e->scene_gen + e->T &&
+                            e->look_split == fp.split_min_cost && e->look_split32 == fp.split32_min_cost &&
+                            e->look_tree == fp.tree_min_cost && e->look_group == fp.tree_group_max_cost && e->look_cih == fp.cost_is_history;
+        e->look_valid = false;
+        if (looked) {
+            set = e->look_set;
+            bind_sched(set);
+        } else {
+            set = 1 - e->set_cur;
+            bind_sched(set);
+            if (history_frame && !same_frame) CU(cudaMemsetAsync(e->tile_time[e->time_cur].p, 0, nt * 4 + 16, e->stream), "reset tile times"); /* history frames: tile_cost_history zeroes it */
+            fp.cost_prev = e->cost_hist_set >= 0 ? (const uint32_t*)e->tile_cost[e->cost_hist_set].p : nullptr;
+            if (!fp.cost_prev) fp.cost_is_history = 0u;
+            CU(tile_order_launcher(launcher)(fp, (uint32_t*)e->tile_cost[set].p, (uint32_t*)e->tile_hist[set].p, (uint32_t*)e->tile_order[set].p, e->stream),
+               "tile_order launch");
+            if (!(history_frame && same_frame) && e->cost_hist_set == set) e->cost_hist_set = -1; /* overwritten by skeleton costs */
+        }
+        e->set_cur = set;
+        if (history_frame) {
+            if (same_frame) e->cost_hist_set = set; /* this frame's costs come from measured times: the next one may lean on them */
+            else e->cost_hist_set = -1;
+            e->time_cur = (e->time_cur + 1) % 3;
             e->time_valid = true;
             e->tk_W = W; e->tk_H = H; e->tk_total = total; e->tk_band = pp.band_rows; e->tk_parts = pp.parts; e->tk_part = pp.part;
             e->tk_scene_gen = e->scene_gen + e->T;
-        } else if (mode == 0) {
-            e->time_valid = false;
-            e->cost_hist_valid = false;
-        } /* accounting / A-B launches (mode != 0) are scheduled by the skeleton trace and leave the history alone */
-        if (tri_all) { fp.split_min_cost = 64u; fp.split32_min_cost = 64u; fp.tree_min_cost = 64u; } /* whole tiles, all of them through render_tree */
-        CU((e->T ? (use_tacc ? rt_launch_tile_order_tacc : rt_launch_tile_order_tri) : (use_accel ? rt_launch_tile_order_acc : rt_launch_tile_order))(fp, (uint32_t*)e->tile_cost.p, (uint32_t*)e->tile_hist.p, (uint32_t*)e->tile_order.p,
-                                e->stream),
-           "tile_order launch");
-        fp.order = (const uint32_t*)e->tile_order.p;
-        fp.cost = (const uint32_t*)e->tile_cost.p;
-        fp.queue_len = (const uint32_t*)e->tile_hist.p + 128;
-        fp.n_split = (const uint32_t*)e->tile_hist.p + 129;
+        }
+        fp.order = (const uint32_t*)e->tile_order[set].p;
+        fp.cost = (const uint32_t*)e->tile_cost[set].p;
+        fp.queue_len = (const uint32_t*)e->tile_hist[set].p + 128;
+        fp.n_split = (const uint32_t*)e->tile_hist[set].p + 129;
     }
     /* level-wise pixel trees for the heavy queue entries (rt_trace_tree.cuh): production trace only, and only while a
      * node's 1 + 2L addition slots stay small.  One slab per CTA of the persistent grid. */
@@ -796,6 +861,30 @@ static int render_impl(rtb_engine* e, uint32_t W, uint32_t H, uint32_t total, co
     CU(cudaEventRecord(e->evk, e->stream), "event record");
     CU((e->T ? (use_tacc ? rt_launch_render_tacc : rt_launch_render_tri) : (use_accel ? rt_launch_render_acc : rt_launch_render))(fp, mode, e->sm_count, e->stream, &shape), "render_frame launch");
     CU(cudaEventRecord(e->ev1, e->stream), "event record");
+    /* schedule look-ahead: the NEXT frame's queue, from the PREVIOUS frame's tile times (this frame's are being measured),
+     * on the second stream while this frame renders: tile_cost_history + tile_order leave the critical path (they were
+     * ~25 us of a 0.48 ms frame on one of 8 GPUs).  The hints are one frame staler; pixels never depend on them. */
+    if (e->opt_lookahead && ordered && history_frame && same_frame && mode == 0 && !counters && !tri_all && fp.tile_time_prev) {
+        RtFrameParams fq = fp;
+        const int nset = 1 - set, tn = e->time_cur; /* the other set (last used by the frame before this one); the buffer the next frame writes */
+        fq.tile_time_sum = (unsigned long long*)e->tile_time[tn].p;
+        fq.tile_time = (uint32_t*)((char*)e->tile_time[tn].p + 16);
+        char* b = (char*)e->sched.p + 256 * nset;
+        fq.tile_counter = (unsigned int*)b;
+        fq.cost_prev = (const uint32_t*)e->tile_cost[set].p;
+        fq.cost_is_history = fp.cost_is_history; /* 1 in the pixel-tree regime (hysteresis on), else 0: what the next frame will ask for */
+        CU(cudaStreamWaitEvent(e->stream2, e->evk, 0), "look-ahead: after the frames before this one"); /* evk: recorded before this frame's kernels */
+        CU(tile_order_launcher(launcher)(fq, (uint32_t*)e->tile_cost[nset].p, (uint32_t*)e->tile_hist[nset].p, (uint32_t*)e->tile_order[nset].p, e->stream2),
+           "tile_order launch (look-ahead)");
+        CU(cudaEventRecord(e->ev_look, e->stream2), "event record");
+        e->look_pending = true;
+        e->look_valid = true;
+        e->look_set = nset; e->look_time = tn; e->look_launcher = launcher;
+        e->look_W = W; e->look_H = H; e->look_total = total; e->look_band = pp.band_rows; e->look_parts = pp.parts; e->look_part = pp.part;
+        e->look_scene = e->scene_gen + e->T;
+        e->look_cih = fq.cost_is_history;
+        e->look_split = fp.split_min_cost; e->look_split32 = fp.split32_min_cost; e->look_tree = fp.tree_min_cost; e->look_group = fp.tree_group_max_cost;
+    }
     e->timed = true;
     e->last.grid = shape.grid; e->last.block = shape.block; e->last.smem_bytes = shape.smem_bytes;
     e->last.resident_scene = shape.resident;
@@ -841,6 +930,7 @@ int rtb_set_option(rtb_engine* e, const char* name, int value) {
     if (!strcmp(name, "wide_min_records")) { e->opt_wide_min_records = value < 0 ? 0x7fffffff : value; return 0; }
     if (!strcmp(name, "wide_max_live")) { e->opt_wide_max_live = value > 32 ? 32 : value; return 0; }
     if (!strcmp(name, "tile_order")) { e->opt_tile_order = value ? 1 : 0; return 0; }
+    if (!strcmp(name, "lookahead")) { e->opt_lookahead = value ? 1 : 0; return 0; }
     if (!strcmp(name, "tree")) { e->opt_tree = value < 0 ? 0 : (value > 3 ? 3 : value); return 0; }
     if (!strcmp(name, "accel")) { e->opt_accel = value ? 1 : 0; e->time_valid = false; return 0; }
     if (!strcmp(name, "tri_tree_min")) { e->opt_tri_tree_min = value < 0 ? 0 : value; return 0; }
@@ -1055,7 +1145,7 @@ int rtb_debug_tri_accel_build(const float* records, uint32_t T, float* nodes, fl
 int rtb_debug_counters(rtb_engine* e, uint64_t out[RTB_NCOUNTERS]) {
     if (!e || !out) return fail(-1, "rtb_debug_counters: null argument");
     CU(cudaSetDevice(e->device), "cudaSetDevice");
-    CU(cudaMemcpyAsync(out, (char*)e->sched.p + 64, RTB_NCOUNTERS * 8, cudaMemcpyDeviceToHost, e->stream), "D2H counters");
+    CU(cudaMemcpyAsync(out, (char*)e->sched.p + e->last_sched_off + 64, RTB_NCOUNTERS * 8, cudaMemcpyDeviceToHost, e->stream), "D2H counters");
     CU(cudaStreamSynchronize(e->stream), "rtb_debug_counters");
     return 0;
 }

@@ -532,7 +532,8 @@ __global__ void tile_cost(const __grid_constant__ RtFrameParams fp, uint32_t* __
  * cost = 24 + 4*log2(t / mean), so the mean tile sits at 24, 16x the mean at 40, 64x at 48 -- whatever the scene's
  * absolute speed (render.map: mean 29 us; the 1,024-sphere grid: 4.5 ms).  Replaces the skeleton trace whenever a frame of the same geometry has just been rendered. ---- */
 __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsigned long long* __restrict__ prev_sum,
-                                  uint32_t* __restrict__ cost_out,
+                                  const uint32_t* cost_prev /* the costs the hysteresis looks back at: cost_out itself, or the other set's */,
+                                  uint32_t* cost_out,
                                   uint32_t* __restrict__ hist, uint32_t ntiles, uint32_t split_min_cost, uint32_t split32_min_cost,
                                   uint32_t sticky_cost, uint32_t* __restrict__ time_now /* 4 header words + ntiles: zeroed here instead of by a memset */) {
     __shared__ uint32_t shist[kCostBuckets];
@@ -553,7 +554,7 @@ __global__ void tile_cost_history(const uint32_t* __restrict__ prev, const unsig
          * is cheaper than its cooperative walk would otherwise change sides every frame; and the kept cost is what
          * orders the heavy tiles. */
         if (sticky_cost < kCostBuckets && c + 8u >= sticky_cost) {
-            const uint32_t old = cost_out[tile];
+            const uint32_t old = cost_prev[tile];
             if (old >= sticky_cost && old < kCostBuckets) c = old;
         }
         cost_out[tile] = c;
@@ -830,7 +831,7 @@ cudaError_t RT_EXPORT(rt_launch_tile_order)(const RtFrameParams& fp, uint32_t* d
      * every tile_order.  fp.tile_time (history frames) and the 256-byte sched block are zeroed by these kernels too. */
     cudaError_t e = cudaSuccess;
     const uint32_t groups = ((fp.tiles_x + 1) / 2) * ((fp.tiles_y + 1) / 2);
-    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost,
+    if (fp.tile_time_prev) tile_cost_history<<<(ntiles + 255) / 256, 256, 0, st>>>(fp.tile_time_prev, fp.tile_time_sum_prev, fp.cost_prev ? fp.cost_prev : d_cost, d_cost, d_hist_cursor, ntiles, fp.split_min_cost, fp.split32_min_cost,
                                                                                   fp.cost_is_history ? fp.tree_min_cost : kCostBuckets,
                                                                                   fp.tile_time ? reinterpret_cast<uint32_t*>(fp.tile_time_sum) : nullptr);
     else tile_cost<<<(groups + 127) / 128, 128, 0, st>>>(fp, d_cost, d_hist_cursor);

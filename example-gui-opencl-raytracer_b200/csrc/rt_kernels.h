@@ -127,6 +127,9 @@ struct RtFrameParams {
     const float4* tacc_rec;   /* [tacc_nc * RT_ACCEL_K * 3] {v0, e1, e2} in cluster order; padding records are all zero (det == 0: never hit) */
     const uint32_t* tacc_idx; /* [tacc_nc * RT_ACCEL_K] original triangle index */
     uint32_t tacc_nc, tacc_nl, tacc_ntop;
+    /* scheduling, launcher side only: the cost buffer the hysteresis of tile_cost_history looks back at when it is not the
+     * one being written (the engine keeps two sets of queue buffers, rt_engine.cu: schedule look-ahead); NULL = in place */
+    const uint32_t* cost_prev;
 };
 
 /* scene_prep: wire arrays -> blob. */

@@ -110,6 +110,10 @@ int rtb_assemble_bands(rtb_engine* e, const uint32_t* d_compact, size_t stride_w
  * (reference control flow; same pixels, slower), 2 = per-lane fast trace (same pixels; the previous production path).  "tile_order": 1 = cost-ordered tile queue (default), 0 = row-major queue.
  * "history": 1 (default) = a frame of the same size/partition/scene as the previous one is scheduled from that frame's
  * MEASURED per-tile times (4*log2 cost scale) instead of the skeleton trace; 0 = always the skeleton trace.
+ * "lookahead": 1 (default; environment RTB_LOOKAHEAD=0 turns it off for callers behind cl_wrap_*) = while a history
+ * frame renders, the NEXT frame's queue is built on a second stream from the frame before's times, so that the two
+ * scheduling kernels leave the frame's critical path; used when the next frame has the same size, partition, scene and
+ * thresholds, else that frame builds its own queue.  Pixels do not change.
  * "split_min_cost" (history frames only): tiles whose cost estimate reaches this value are dealt to four warps (one 8-pixel tile row each,
  * the other 24 lanes only run shadow tasks) so that no single warp owns a whole glass/mirror tile (64 = never, 0 = automatic: tiles longer than 0.75 x the queue's expected drain time).
  * "split32_min_cost": ... and from this value on to 32 warps, one pixel each (64 = never, 0 = automatic: tiles
