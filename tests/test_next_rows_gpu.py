@@ -185,3 +185,61 @@ def test_completion_word_and_wait_kernel(pkg, ref, scene, fresh):
     fresh.wait_flags(flags + 64 * 5, 16, 1, 7)         # nobody ever writes this word
     assert fresh.wait_timeouts() == 1
     fresh.dev_free(buf)
+
+
+def test_schedule_lookahead_never_changes_a_frame(pkg, ref, scene, host):
+    """r02, rt_engine.cu: while a history-scheduled frame renders, the next frame's queue is built on a second stream
+    into a second set of queue buffers.  A sequence that keeps breaking what the look-ahead assumed -- another size,
+    another partition, a counted (literal) frame, an option that moves the thresholds, a new scene, a frame through
+    rtb_render_noalloc, frames too small for the ordered queue -- must give, frame for frame, the words of the same
+    sequence rendered with the look-ahead off; and both must be the oracle's frame where one is at hand."""
+    s2, p2, l2, camp2 = host.sphere_grid_scene(5)
+    part_a, part_b = pkg.Partition(8, 2, 1), pkg.Partition(8, 4, 2)
+    seq = ([("render", 1024, 512, None)] * 5 + [("render", 768, 768, None)] * 2 + [("render", 1024, 512, None)] * 3 +
+           [("render", 1024, 1024, part_a)] * 4 + [("render", 1024, 1024, part_b)] * 3 + [("counted", 1024, 512, None)] +
+           [("render", 1024, 512, None)] * 3 + [("option", "tree", 0)] + [("render", 1024, 512, None)] * 3 + [("option", "tree", 1)] +
+           [("render", 1024, 512, None)] * 3 + [("noalloc", 1024, 512, None)] + [("render", 1024, 512, None)] * 2 +
+           [("render", 96, 64, None)] * 2 + [("render", 1024, 512, None)] * 3 + [("scene",)] + [("render", 1024, 512, None)] * 4)
+    out = {}
+    for la in (0, 1):
+        eng = pkg.Engine(0)
+        try:
+            eng.upload_images(0, scene.tex); eng.upload_images(1, scene.sky)
+            eng.upload_scene(scene.spheres, scene.planes, scene.lights)
+            eng.set_option("lookahead", la)
+            camp = dict(ref.RAYPNG_CAMERA)
+            scratch = eng.dev_alloc(1024 * 512 * 4)
+            frames = []
+            for k, step in enumerate(seq):
+                if step[0] == "option":
+                    eng.set_option(step[1], step[2])
+                    continue
+                if step[0] == "scene":
+                    eng.upload_scene(s2, p2, l2)
+                    camp = camp2
+                    continue
+                W, H, part = step[1], step[2], step[3]
+                o = np.array(camp["origin"], np.float64) + np.array([0.01 * k, 0.0, 0.0])      # the camera moves every frame
+                eng.set_camera(host.camera(W=W, H=H, **dict(camp, origin=tuple(o))))
+                if step[0] == "counted":
+                    eng.render_counted(W, H)
+                    frames.append(eng.read_frame(W * H))
+                elif step[0] == "noalloc":
+                    eng.render_noalloc(W, H, scratch.value)
+                    eng.sync()
+                    frames.append(eng.dev_read(scratch, W * H * 4).view(np.uint32).copy())
+                else:
+                    rgb, hit = eng.render_to_host(W, H, want_hit=True, part=part)
+                    frames.append(np.concatenate([rgb, hit]))
+            eng.dev_free(scratch)
+            out[la] = frames
+        finally:
+            eng.close()
+    assert len(out[0]) == len(out[1])
+    for k, (a, b) in enumerate(zip(out[0], out[1])):
+        assert np.array_equal(a, b), k
+    # one frame of the sequence against the reference text: the 5th (look-ahead queue in use), 1024x512
+    W, H = 1024, 512
+    o = np.array(ref.RAYPNG_CAMERA["origin"], np.float64) + np.array([0.04, 0.0, 0.0])
+    want_rgb, want_hit = ref.judge().render(scene, ref.camera(W=W, H=H, **dict(ref.RAYPNG_CAMERA, origin=tuple(o))), W, H)
+    judge_frame(ref, out[1][4][:W * H], out[1][4][W * H:], want_rgb, want_hit, W, H, "5th frame of the look-ahead sequence")
