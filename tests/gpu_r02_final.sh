@@ -1,6 +1,7 @@
 #!/bin/bash
 # r02 final evidence set on one B200: every GPU test, smoke, both bench arms at N=1 (with other_configs), launch list,
-# full ncu captures of render_frame (render.map), the WIDE variant (1,024-sphere grid) and render_tree (one N=8 part).
+# full ncu captures of render_frame (render.map), the WIDE variant (1,024-sphere grid), render_tree (one N=8 part) and the
+# N4-over-triangles build (49,928-triangle mesh).
 O=gpurun_out/r02f
 mkdir -p $O
 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 | tee $O/pytest_gpu.txt
@@ -13,5 +14,6 @@ ncu --set full --clock-control none --import-source on -k regex:render_frame -s 
 CMDW="python bench.py --steps 1 --warmup 3 --no-cpu --other-configs off --workload spheres1024_4k"
 ncu --set full --clock-control none --import-source on -k regex:render_frame -s 3 -c 1 -f -o $O/prof_wide $CMDW > $O/ncu_full_wide.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:render_tree -s 28 -c 1 -f -o $O/prof_tree python tools/exp/sweep_tree.py render_map_4k 1:0:0:0 > $O/ncu_full_tree.log 2>&1   # the 29th launch: an N=8 part
-tail -2 $O/ncu_full.log $O/ncu_full_wide.log $O/ncu_full_tree.log
+ncu --set full --clock-control none --import-source on -k regex:render_frame -s 5 -c 1 -f -o $O/prof_tacc python tools/exp/tacc_probe.py > $O/ncu_full_tacc.log 2>&1   # the mesh through the box hierarchy, a history frame
+tail -2 $O/ncu_full.log $O/ncu_full_wide.log $O/ncu_full_tree.log $O/ncu_full_tacc.log
 ls -la $O

@@ -12,7 +12,8 @@ O = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "r02f
 P = os.path.join(ROOT, "profiles")
 CAPS = (("prof", "render_frame", "render.map 3840x2160, history frame"),
         ("prof_wide", "render_frame_wide", "1,024-sphere grid 3840x2160"),
-        ("prof_tree", "render_tree", "one N=8 part of render.map 3840x2160, history frame"))
+        ("prof_tree", "render_tree", "one N=8 part of render.map 3840x2160, history frame"),
+        ("prof_tacc", "render_frame_tri_accel", "49,928-triangle mesh 3840x2160 through the N4 box hierarchy (rt_kernels_tri_accel.cu), history frame"))
 names = [l.split()[0] for l in open(os.path.join(P, "r01_v11_render_frame_key_metrics.txt")).read().split("\n") if l and not l.startswith("Kernel")]
 names += ["smsp__inst_executed.sum", "sm__inst_issued.avg.pct_of_peak_sustained_active", "smsp__thread_inst_executed_per_inst_executed.ratio",
           "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__grid_size"]
