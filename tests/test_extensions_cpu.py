@@ -218,3 +218,150 @@ def test_triangle_primary_hits_numpy_pin_vs_port(ref, scene, host):
         port.set_triangles(b"")
     assert (want > 0).sum() > 500
     assert np.array_equal(hit, want)
+
+
+# ---- N4 over the triangles (csrc/rt_trace_accel.cuh: tacc_cull / tacc_walk), replayed on the CPU ------------------------
+def _mt_all(o, d, v0, e1, e2):
+    """float32 Moeller-Trumbore of ONE ray against every record (the operation order of hit_triangle); -> (hit mask, t)."""
+    f = np.float32
+    dot = lambda a, b: (a[..., 0] * b[..., 0] + a[..., 1] * b[..., 1]) + a[..., 2] * b[..., 2]
+    cross = lambda a, b: np.stack([a[..., 1] * b[..., 2] - a[..., 2] * b[..., 1], a[..., 2] * b[..., 0] - a[..., 0] * b[..., 2],
+                                   a[..., 0] * b[..., 1] - a[..., 1] * b[..., 0]], axis=-1)
+    with np.errstate(all="ignore"):
+        p = cross(d[None, :], e2)
+        det = dot(e1, p)
+        inv = f(1.0) / det
+        s = o[None, :] - v0
+        u = dot(s, p) * inv
+        q = cross(s, e1)
+        v = dot(d[None, :], q) * inv
+        t = dot(e2, q) * inv
+        hit = (det != 0) & ~((u < 0) | (u > 1)) & ~((v < 0) | (u + v > 1)) & ~(t <= 0)
+    return hit, t
+
+
+class _Hierarchy:
+    def __init__(self, pkg, rec):
+        L_ = pkg.lib()
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        T = len(rec)
+        nc, nl, nn = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        off = (C.c_uint32 * 6)()
+        assert L_.rtb_debug_tri_accel_build(vp(rec), T, None, None, None, C.byref(nc), C.byref(nl), off, C.byref(nn)) == 1
+        self.nodes = np.zeros(8 * nn.value, np.float32); self.srt = np.zeros(12 * 8 * nc.value, np.float32); self.idx = np.zeros(8 * nc.value, np.uint32)
+        assert L_.rtb_debug_tri_accel_build(vp(rec), T, vp(self.nodes), vp(self.srt), vp(self.idx), C.byref(nc), C.byref(nl), off, C.byref(nn)) == 1
+        self.nodes = self.nodes.reshape(-1, 8); self.srt = self.srt.reshape(-1, 12)
+        self.nc, self.nl, self.off = nc.value, nl.value, list(off)
+
+    def cull(self, o, inv, ainv, nd, tmax):
+        """tacc_cull in float32 (the FMA of mu through float64: one rounding, as __fmaf_rn)."""
+        f = np.float32
+        with np.errstate(all="ignore"):
+            a = nd[0:3] - o
+            mu = f(np.float64((np.abs(a[0]) + np.abs(a[1])) + np.abs(a[2])) * np.float64(f(0.000244140625)) + np.float64(nd[7]))
+            c = a * inv
+            e = (nd[4:7] + mu) * ainv
+            tn = np.fmax(np.fmax(c[0] - e[0], c[1] - e[1]), c[2] - e[2])      # fmaxf / fminf: a NaN operand drops out
+            tf = np.fmin(np.fmin(c[0] + e[0], c[1] + e[1]), c[2] + e[2])
+            return bool(tn > tf or tf < 0 or tn > tmax)
+
+    def walk(self, o, d, tmax_fn, leaf):
+        """tacc_walk: cluster positions in order, one node per step; leaf(k) returns True to stop.  -> (node tests, leaves)"""
+        f = np.float32
+        with np.errstate(all="ignore"):
+            inv = f(1.0) / d
+        ainv = np.abs(inv)
+        top, k, l, tests, leaves = self.nl - 1, 0, self.nl - 1, 0, 0
+        up = lambda kk: min(((kk & -kk).bit_length() - 1) // 3, top)
+        while k < self.nc:
+            tests += 1
+            if self.cull(o, inv, ainv, self.nodes[self.off[l] + (k >> (3 * l))], tmax_fn()):
+                k += 1 << (3 * l)
+                if k < self.nc: l = up(k)
+            elif l:
+                l -= 1
+            else:
+                leaves += 1
+                if leaf(k): break
+                k += 1
+                if k < self.nc: l = up(k)
+        return tests, leaves
+
+
+def test_triangle_hierarchy_walk_replay_equals_brute_force(pkg, host):
+    """The device walk of rt_trace_accel.cuh restated here (same cull arithmetic in float32, same visiting order, same
+    closest-hit and any-hit rules) over the hierarchy the library builds, against the brute-force loop, for rays of the
+    kinds a frame produces: camera rays, shadow rays leaving the surface, rays from far away (the ground plane near the
+    horizon: origins hundreds to thousands of units out, where the cull's margin is widest) and rays along an axis (a zero
+    direction component: infinite slab bounds).  Closest hit = (t, original index) equal; any-hit equal; and the walk
+    must actually skip most of the mesh for the near rays."""
+    f = np.float32
+    rng = np.random.default_rng(424242)
+    _, _, _, tris, _ = host.heightfield_mesh_scene(n=24)                  # 1,152 triangles over [-8, 8] x [-4, 12]
+    T = len(tris) // 112
+    wire = np.frombuffer(tris, f).reshape(T, 28)
+    rec = np.zeros((T, 12), f)
+    rec[:, 0:3] = wire[:, 0:3]; rec[:, 4:7] = wire[:, 4:7] - wire[:, 0:3]; rec[:, 8:11] = wire[:, 8:11] - wire[:, 0:3]
+    h = _Hierarchy(pkg, rec)
+    v0, e1, e2 = rec[:, 0:3], rec[:, 4:7], rec[:, 8:11]
+    s0, s1, s2 = h.srt[:, 0:3], h.srt[:, 4:7], h.srt[:, 8:11]
+    centre = np.array([0.0, 0.6, 4.0])
+    rays = []
+    for _ in range(500):                                                   # camera-like
+        o = np.array([rng.normal() * 3, 4 + rng.random() * 4, -9 + rng.normal()])
+        rays.append((o, centre + rng.normal(size=3) * np.array([6, 0.5, 6]) - o))
+    for _ in range(500):                                                   # leaving the surface towards a light
+        k = rng.integers(T)
+        p = v0[k] + 0.3 * e1[k] + 0.3 * e2[k] + np.array([0, 1e-3, 0])
+        rays.append((p.astype(np.float64), np.array([rng.normal() * 8, 6 + rng.random() * 4, rng.normal() * 8 + 4]) - p))
+    for _ in range(400):                                                   # from far away, low over the ground
+        ang = rng.random() * 2 * np.pi
+        dist = 10 ** (2 + 2 * rng.random())                                # 100 .. 10,000
+        o = np.array([np.cos(ang) * dist, -0.6 + rng.random() * 0.01, 4 + np.sin(ang) * dist])
+        aim = (np.array([rng.normal() * 8, 6 + rng.random() * 4, rng.normal() * 8 + 4]) if rng.random() < 0.5      # a light above the mesh
+               else centre + rng.normal(size=3) * np.array([5, 0.3, 5]))                                             # the mesh itself
+        rays.append((o, aim - o))
+    for _ in range(100):                                                   # axis-parallel: a zero component
+        o = np.array([rng.normal() * 6, 5.0, 4 + rng.normal() * 6])
+        rays.append((o, np.array([0.0, -1.0, 0.0]) if rng.random() < 0.5 else np.array([0.0, -1.0, rng.normal() * 0.2])))
+    near_tests = near_leaves = n_near = hits = blocked_n = 0
+    for n, (o64, d64) in enumerate(rays):
+        o = o64.astype(f)
+        d = (d64 / np.linalg.norm(d64)).astype(f)
+        hit, t = _mt_all(o, d, v0, e1, e2)
+        assert not np.isnan(t[hit]).any()
+        if hit.any():
+            tb = t[hit].min()
+            want = (tb, int(np.flatnonzero(hit & (t == tb))[0]))           # first of equal t in index order
+        else:
+            want = (f(np.inf), -1)
+        best = [f(np.inf), -1]
+
+        def leaf(k):
+            hk, tk = _mt_all(o, d, s0[8 * k: 8 * k + 8], s1[8 * k: 8 * k + 8], s2[8 * k: 8 * k + 8])
+            for j in np.flatnonzero(hk):
+                orig = int(h.idx[8 * k + j])
+                if tk[j] < best[0] or (tk[j] == best[0] and best[1] >= 0 and orig < best[1]):
+                    best[0], best[1] = tk[j], orig
+            return False
+        tests, leaves = h.walk(o, d, lambda: f(best[0] * f(1.00001)), leaf)
+        assert (best[0], best[1]) == want, (n, best, want)
+        hits += want[1] >= 0
+        if n < 1000:
+            near_tests += tests; near_leaves += leaves; n_near += 1
+        # any-hit with a random length (a shadow ray): blocked iff some member has !(t >= len)
+        length = f(rng.random() * 30 if want[1] < 0 else want[0] * (0.5 + rng.random()))
+        want_blocked = bool((hit & ~(t >= length)).any())
+        got = [False]
+
+        def leaf_any(k):
+            hk, tk = _mt_all(o, d, s0[8 * k: 8 * k + 8], s1[8 * k: 8 * k + 8], s2[8 * k: 8 * k + 8])
+            got[0] = bool((hk & ~(tk >= length)).any())
+            return got[0]
+        h.walk(o, d, lambda: f(length * f(1.00001)), leaf_any)
+        assert got[0] == want_blocked, n
+        blocked_n += want_blocked
+    print("rays with a hit: %d of %d; blocked shadow rays: %d" % (hits, len(rays), blocked_n))
+    assert hits > 500 and blocked_n > 200
+    print("near rays: %.1f node tests and %.1f of %d clusters per closest-hit walk" % (near_tests / n_near, near_leaves / n_near, h.nc))
+    assert near_leaves / n_near < 0.1 * h.nc
