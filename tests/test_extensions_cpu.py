@@ -365,3 +365,51 @@ def test_triangle_hierarchy_walk_replay_equals_brute_force(pkg, host):
     assert hits > 500 and blocked_n > 200
     print("near rays: %.1f node tests and %.1f of %d clusters per closest-hit walk" % (near_tests / n_near, near_leaves / n_near, h.nc))
     assert near_leaves / n_near < 0.1 * h.nc
+
+
+def test_triangle_hierarchy_walk_replay_tie_rule_on_duplicates(pkg, host):
+    """Equal-t ties: a soup in which every third triangle is an exact duplicate of an earlier one (another index, the same
+    geometry) and some are the same triangle with the other winding.  The brute-force loop keeps the FIRST of equal t in
+    index order; the hierarchy visits in its own order and must still name that one."""
+    f = np.float32
+    rng = np.random.default_rng(777)
+    recs = []
+    while len(recs) < 400:
+        c = rng.normal(size=3) * np.array([3.0, 1.0, 3.0]) + np.array([0, 1.5, 4])
+        a, b = rng.normal(size=3) * 0.8, rng.normal(size=3) * 0.8
+        r = np.zeros(12, f); r[0:3] = c; r[4:7] = a; r[8:11] = b
+        recs.append(r)
+        if rng.random() < 0.5: recs.append(r.copy())                       # exact duplicate: equal t on every ray
+        if rng.random() < 0.2:
+            w = r.copy(); w[4:7], w[8:11] = r[8:11], r[4:7]                # other winding: the same plane and vertices
+            recs.append(w)
+    order = rng.permutation(len(recs))                                      # duplicates far apart in index order
+    rec = np.stack([recs[i] for i in order]).astype(f)
+    T = len(rec)
+    h = _Hierarchy(pkg, rec)
+    v0, e1, e2 = rec[:, 0:3], rec[:, 4:7], rec[:, 8:11]
+    s0, s1, s2 = h.srt[:, 0:3], h.srt[:, 4:7], h.srt[:, 8:11]
+    ties = 0
+    for n in range(600):
+        o = (rng.normal(size=3) * 2 + np.array([0, 1.5, -3])).astype(f)
+        d64 = np.array([0, 1.5, 4]) + rng.normal(size=3) * np.array([3, 1, 3]) - o
+        d = (d64 / np.linalg.norm(d64)).astype(f)
+        hit, t = _mt_all(o, d, v0, e1, e2)
+        if not hit.any():
+            continue
+        tb = t[hit].min()
+        at_tb = np.flatnonzero(hit & (t == tb))
+        ties += len(at_tb) > 1
+        want = (tb, int(at_tb[0]))
+        best = [f(np.inf), -1]
+
+        def leaf(k):
+            hk, tk = _mt_all(o, d, s0[8 * k: 8 * k + 8], s1[8 * k: 8 * k + 8], s2[8 * k: 8 * k + 8])
+            for j in np.flatnonzero(hk):
+                orig = int(h.idx[8 * k + j])
+                if tk[j] < best[0] or (tk[j] == best[0] and best[1] >= 0 and orig < best[1]):
+                    best[0], best[1] = tk[j], orig
+            return False
+        h.walk(o, d, lambda: f(best[0] * f(1.00001)), leaf)
+        assert (best[0], best[1]) == want, (n, best, want)
+    assert ties > 100                                                      # the rule was actually exercised
